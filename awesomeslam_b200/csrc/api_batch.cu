@@ -1,0 +1,521 @@
+// C-ABI layer for the batched filters (include/aslam_c.h): handle lifetime, device memory,
+// host<->device staging, state export. The filter math lives in ekf_batched.cu /
+// ukf_batched.cu; nothing here computes on the CPU.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "internal.hpp"
+
+namespace aslam {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+bool cuda_ok(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return true;
+    g_error = std::string(what) + ": " + cudaGetErrorString(e);
+    return false;
+}
+
+uint32_t batched_padded_dim(int32_t max_state_dim, int kind) {
+    // N is odd and must stay < max_state_dim (ekf.cpp:263), so N <= max_state_dim - 1.
+    const int nmax = max_state_dim - 1;
+    if (nmax < 3) return 0;
+    if (kind == ASLAM_KIND_UKF) {
+        if (nmax <= 29) return 30;
+        if (nmax <= 63) return 64;
+        return 0;
+    }
+    if (nmax <= 29) return 30;
+    if (nmax <= 35) return 36;
+    if (nmax <= 47) return 48;
+    if (nmax <= 63) return 64;
+    return 0;
+}
+
+// EKFSlam::initialize (ekf.cpp:49-71) / UKFSlam::initialize (ukf.cpp:49-67) for every filter.
+__global__ void batch_init_kernel(BatchState st, double kp_pose) {
+    const uint32_t f = blockIdx.x;
+    const uint32_t ld = st.ld;
+    for (uint32_t k = threadIdx.x; k < ld * ld; k += blockDim.x) {
+        const uint32_t i = k / ld, j = k % ld;
+        st.P[(size_t)f * ld * ld + k] = (i == j && i < 3) ? kp_pose : 0.0;
+    }
+    for (uint32_t k = threadIdx.x; k < ld; k += blockDim.x) {
+        st.X[(size_t)f * ld + k] = 0.0;
+        st.Z[(size_t)f * ld + k] = 0.0;
+    }
+    for (uint32_t k = threadIdx.x; k < ASLAM_MAX_WAIT; k += blockDim.x) {
+        st.wrange[(size_t)f * ASLAM_MAX_WAIT + k] = 0.f;
+        st.wbearing[(size_t)f * ASLAM_MAX_WAIT + k] = 0.f;
+        st.whits[(size_t)f * ASLAM_MAX_WAIT + k] = 0;
+    }
+    if (threadIdx.x == 0) {
+        st.N[f] = 3;
+        st.status[f] = 0;
+        st.flags[f] = FLAG_INIT_X;
+        st.wcount[f] = 0;
+        st.A[2 * (size_t)f] = 1.0;
+        st.A[2 * (size_t)f + 1] = 0.0;
+        st.llt_fail[f] = -1;
+    }
+}
+
+aslam_status launch_batch_init(const aslam_config& cfg, int kind, const BatchState& st, cudaStream_t stream) {
+    const double kp = kind == ASLAM_KIND_EKF ? (double)cfg.ekf_kp_robot_pose : (double)cfg.ukf_kp_robot_pose;
+    batch_init_kernel<<<st.batch, 128, 0, stream>>>(st, kp);
+    ASLAM_CUDA(cudaGetLastError());
+    return ASLAM_OK;
+}
+
+// out[f][j*ld + i] = in[f][i*ld + j]: device row-major P -> column-major export (and back).
+__global__ void batch_transpose_kernel(const double* in, double* out, uint32_t ld) {
+    const size_t base = (size_t)blockIdx.x * ld * ld;
+    for (uint32_t k = threadIdx.x; k < ld * ld; k += blockDim.x) {
+        const uint32_t i = k / ld, j = k % ld;
+        out[base + (size_t)j * ld + i] = in[base + k];
+    }
+}
+
+__global__ void batch_landmarks_kernel(BatchState st, double* lx, double* ly, uint32_t* count) {
+    const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= st.batch) return;
+    const uint32_t lmax = (st.ld - 3) / 2;
+    const uint32_t N = st.N[f];
+    const uint32_t L = (N - 3) / 2;
+    for (uint32_t l = 0; l < lmax; ++l) {  // common.h:98-102
+        lx[(size_t)f * lmax + l] = l < L ? st.X[(size_t)f * st.ld + 3 + 2 * l] : 0.0;
+        ly[(size_t)f * lmax + l] = l < L ? st.X[(size_t)f * st.ld + 4 + 2 * l] : 0.0;
+    }
+    count[f] = L;
+}
+
+}  // namespace aslam
+
+using namespace aslam;
+
+struct aslam_filter {
+    int kind = 0;
+    aslam_config cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    BatchState st;
+    // device staging for host-fed messages
+    double* d_odom64 = nullptr;  // [4][batch]: x, y, vx, az
+    float* d_odom32 = nullptr;   // [2][batch]: yaw, dt
+    float* d_range = nullptr;
+    float* d_bearing = nullptr;
+    uint32_t* d_offsets = nullptr;
+    size_t obs_capacity = 0;
+    // current observation list (own staging or caller's device arrays)
+    const float* cur_range = nullptr;
+    const float* cur_bearing = nullptr;
+    const uint32_t* cur_offsets = nullptr;
+    uint32_t cur_total = 0;
+    bool have_obs = false;
+    int32_t* d_assoc = nullptr;
+    size_t assoc_capacity = 0;
+    double* d_scratch = nullptr;  // export scratch, lazily sized
+    size_t scratch_bytes = 0;
+};
+
+namespace {
+
+template <typename T>
+aslam_status dev_alloc(T** p, size_t count) {
+    ASLAM_CUDA(cudaMalloc((void**)p, count * sizeof(T)));
+    return ASLAM_OK;
+}
+
+aslam_status ensure_scratch(aslam_filter* h, size_t bytes) {
+    if (h->scratch_bytes >= bytes) return ASLAM_OK;
+    if (h->d_scratch) cudaFree(h->d_scratch);
+    h->d_scratch = nullptr;
+    h->scratch_bytes = 0;
+    ASLAM_CUDA(cudaMalloc((void**)&h->d_scratch, bytes));
+    h->scratch_bytes = bytes;
+    return ASLAM_OK;
+}
+
+aslam_status ensure_assoc(aslam_filter* h, size_t count) {
+    if (h->assoc_capacity >= count) return ASLAM_OK;
+    if (h->d_assoc) cudaFree(h->d_assoc);
+    h->d_assoc = nullptr;
+    h->assoc_capacity = 0;
+    ASLAM_CUDA(cudaMalloc((void**)&h->d_assoc, count * sizeof(int32_t)));
+    h->assoc_capacity = count;
+    return ASLAM_OK;
+}
+
+aslam_status create_filter(int kind, const aslam_config* cfg, uint32_t batch, int32_t device, aslam_filter** out) {
+    if (!out || batch == 0) {
+        set_error("create: null out or empty batch");
+        return ASLAM_ERR_ARG;
+    }
+    *out = nullptr;
+    aslam_config c;
+    if (cfg)
+        c = *cfg;
+    else
+        aslam_config_default(&c);
+    const uint32_t ld = batched_padded_dim(c.max_state_dim, kind);
+    if (!ld) {
+        set_error("create: max_state_dim outside the batched kernels' range (use aslam_large_*)");
+        return ASLAM_ERR_UNSUPPORTED;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("create: no CUDA device (this library has no CPU path)");
+        return ASLAM_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) {
+        set_error("create: device index out of range");
+        return ASLAM_ERR_ARG;
+    }
+    ASLAM_CUDA(cudaSetDevice(device));
+    aslam_filter* h = new (std::nothrow) aslam_filter;
+    if (!h) return ASLAM_ERR_ARG;
+    h->kind = kind;
+    h->cfg = c;
+    h->device = device;
+    h->st.batch = batch;
+    h->st.ld = ld;
+    aslam_status rc = ASLAM_OK;
+    auto chk = [&](aslam_status s) {
+        if (rc == ASLAM_OK) rc = s;
+    };
+    if (!cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+    chk(dev_alloc(&h->st.X, (size_t)batch * ld));
+    chk(dev_alloc(&h->st.Z, (size_t)batch * ld));
+    chk(dev_alloc(&h->st.P, (size_t)batch * ld * ld));
+    chk(dev_alloc(&h->st.A, (size_t)batch * 2));
+    chk(dev_alloc(&h->st.N, batch));
+    chk(dev_alloc(&h->st.status, batch));
+    chk(dev_alloc(&h->st.flags, batch));
+    chk(dev_alloc(&h->st.wcount, batch));
+    chk(dev_alloc(&h->st.wrange, (size_t)batch * ASLAM_MAX_WAIT));
+    chk(dev_alloc(&h->st.wbearing, (size_t)batch * ASLAM_MAX_WAIT));
+    chk(dev_alloc(&h->st.whits, (size_t)batch * ASLAM_MAX_WAIT));
+    chk(dev_alloc(&h->st.llt_fail, batch));
+    chk(dev_alloc(&h->d_odom64, (size_t)batch * 4));
+    chk(dev_alloc(&h->d_odom32, (size_t)batch * 2));
+    chk(dev_alloc(&h->d_offsets, (size_t)batch + 1));
+    if (rc == ASLAM_OK) rc = launch_batch_init(c, kind, h->st, h->stream);
+    if (rc != ASLAM_OK) {
+        aslam_filter_destroy(h);
+        return rc;
+    }
+    *out = h;
+    return ASLAM_OK;
+}
+
+aslam_status run_kernel(aslam_filter* h, const BatchInput& in) {
+    if (h->kind == ASLAM_KIND_EKF) return launch_ekf_batched(h->cfg, h->st, in, h->stream);
+    return launch_ukf_batched(h->cfg, h->st, in, h->stream);
+}
+
+}  // namespace
+
+extern "C" {
+
+void aslam_config_default(aslam_config* c) {
+    if (!c) return;
+    c->pi = 3.141592654f;
+    c->min_dist_thresh = 0.5f;
+    c->min_landmark_occ = 10;
+    c->max_state_dim = 30;
+    c->ukf_std_a = 0.2f;
+    c->ukf_std_yaw = 0.2f;
+    c->ukf_kp_robot_pose = 0.001f;
+    c->ukf_kp_landmark_pose = 1.0f;
+    c->ukf_kr = 0.2f;
+    c->ukf_kq = 0.001f;
+    c->ekf_kp_robot_pose = 0.001f;
+    c->ekf_kp_landmark_pose = 10000.0f;
+    c->ekf_kr = 0.2f;
+    c->ekf_kq = 0.001f;
+}
+
+const char* aslam_last_error(void) { return g_error.c_str(); }
+const char* aslam_version(void) { return "aslam_b200 0.1 (sm_100a)"; }
+int32_t aslam_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+float aslam_quat2euler(double w, double x, double y, double z) {
+    const float fw = (float)w, fx = (float)x, fy = (float)y, fz = (float)z;
+    // tools.h:64: float arithmetic throughout, atan2f
+    const float num = 2 * (fw * fz + fx * fy);
+    const float den = 1 - 2 * (fz * fz + fy * fy);
+    return std::atan2(num, den);
+}
+
+aslam_status aslam_ekf_create(const aslam_config* cfg, uint32_t batch, int32_t device, aslam_filter** out) {
+    return create_filter(ASLAM_KIND_EKF, cfg, batch, device, out);
+}
+aslam_status aslam_ukf_create(const aslam_config* cfg, uint32_t batch, int32_t device, aslam_filter** out) {
+    return create_filter(ASLAM_KIND_UKF, cfg, batch, device, out);
+}
+
+aslam_status aslam_filter_destroy(aslam_filter* h) {
+    if (!h) return ASLAM_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    void* ptrs[] = {h->st.X,      h->st.Z,       h->st.P,     h->st.A,        h->st.N,    h->st.status,
+                    h->st.flags,  h->st.wcount,  h->st.wrange, h->st.wbearing, h->st.whits, h->st.llt_fail,
+                    h->d_odom64,  h->d_odom32,   h->d_range,  h->d_bearing,   h->d_offsets, h->d_assoc,
+                    h->d_scratch};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_sync(aslam_filter* h) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+void* aslam_filter_stream(aslam_filter* h) { return h ? (void*)h->stream : nullptr; }
+uint32_t aslam_filter_batch(const aslam_filter* h) { return h ? h->st.batch : 0; }
+uint32_t aslam_filter_ld(const aslam_filter* h) { return h ? h->st.ld : 0; }
+int32_t aslam_filter_kind(const aslam_filter* h) { return h ? h->kind : -1; }
+
+aslam_status aslam_filter_set_observations(aslam_filter* h, const float* range, const float* bearing,
+                                           const uint32_t* offsets) {
+    if (!h || !offsets) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const uint32_t B = h->st.batch;
+    const size_t total = offsets[B];
+    if (total && (!range || !bearing)) return ASLAM_ERR_ARG;
+    if (total > h->obs_capacity) {
+        ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+        if (h->d_range) cudaFree(h->d_range);
+        if (h->d_bearing) cudaFree(h->d_bearing);
+        h->d_range = h->d_bearing = nullptr;
+        h->obs_capacity = 0;
+        const size_t cap = total + total / 4 + 16;
+        ASLAM_CUDA(cudaMalloc((void**)&h->d_range, cap * sizeof(float)));
+        ASLAM_CUDA(cudaMalloc((void**)&h->d_bearing, cap * sizeof(float)));
+        h->obs_capacity = cap;
+    }
+    if (total) {
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_range, range, total * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_bearing, bearing, total * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    }
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_offsets, offsets, ((size_t)B + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                               h->stream));
+    h->cur_range = h->d_range;
+    h->cur_bearing = h->d_bearing;
+    h->cur_offsets = h->d_offsets;
+    h->cur_total = (uint32_t)total;
+    h->have_obs = true;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_set_observations_device(aslam_filter* h, const float* d_range, const float* d_bearing,
+                                                  const uint32_t* d_offsets) {
+    if (!h || !d_offsets) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    uint32_t total = 0;
+    ASLAM_CUDA(cudaMemcpyAsync(&total, d_offsets + h->st.batch, sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    h->cur_range = d_range;
+    h->cur_bearing = d_bearing;
+    h->cur_offsets = d_offsets;
+    h->cur_total = total;
+    h->have_obs = true;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_step_device(aslam_filter* h, const aslam_odom* o) {
+    if (!h || !o || !o->x || !o->y || !o->yaw || !o->vx || !o->az || !o->dt) return ASLAM_ERR_ARG;
+    if (!h->have_obs) {
+        set_error("step before the first set_observations (cbOdom returns while init_z, ekf.cpp:76)");
+        return ASLAM_ERR_NOT_READY;
+    }
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    aslam_status rc = ensure_assoc(h, h->cur_total ? h->cur_total : 1);
+    if (rc != ASLAM_OK) return rc;
+    BatchInput in;
+    in.ox = o->x;
+    in.oy = o->y;
+    in.yaw = o->yaw;
+    in.vx = o->vx;
+    in.az = o->az;
+    in.dt = o->dt;
+    in.range = h->cur_range;
+    in.bearing = h->cur_bearing;
+    in.offsets = h->cur_offsets;
+    in.assoc = h->d_assoc;
+    in.steps = 1;
+    return run_kernel(h, in);
+}
+
+aslam_status aslam_filter_step(aslam_filter* h, const aslam_odom* o) {
+    if (!h || !o || !o->x || !o->y || !o->yaw || !o->vx || !o->az || !o->dt) return ASLAM_ERR_ARG;
+    if (!h->have_obs) {
+        set_error("step before the first set_observations (cbOdom returns while init_z, ekf.cpp:76)");
+        return ASLAM_ERR_NOT_READY;
+    }
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t B = h->st.batch;
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_odom64 + 0 * B, o->x, B * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_odom64 + 1 * B, o->y, B * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_odom64 + 2 * B, o->vx, B * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_odom64 + 3 * B, o->az, B * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_odom32 + 0 * B, o->yaw, B * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_odom32 + 1 * B, o->dt, B * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    aslam_odom d;
+    d.x = h->d_odom64;
+    d.y = h->d_odom64 + B;
+    d.vx = h->d_odom64 + 2 * B;
+    d.az = h->d_odom64 + 3 * B;
+    d.yaw = h->d_odom32;
+    d.dt = h->d_odom32 + B;
+    return aslam_filter_step_device(h, &d);
+}
+
+aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const aslam_odom* o, const float* d_range,
+                                     const float* d_bearing, uint32_t obs_per_filter) {
+    if (!h || !o || !o->x || !o->y || !o->yaw || !o->vx || !o->az || !o->dt) return ASLAM_ERR_ARG;
+    if (steps == 0) return ASLAM_OK;
+    if (obs_per_filter && (!d_range || !d_bearing)) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t total = (size_t)h->st.batch * obs_per_filter;
+    aslam_status rc = ensure_assoc(h, total ? total : 1);
+    if (rc != ASLAM_OK) return rc;
+    BatchInput in;
+    in.ox = o->x;
+    in.oy = o->y;
+    in.yaw = o->yaw;
+    in.vx = o->vx;
+    in.az = o->az;
+    in.dt = o->dt;
+    in.range = d_range;
+    in.bearing = d_bearing;
+    in.offsets = nullptr;
+    in.obs_per_filter = obs_per_filter;
+    in.assoc = h->d_assoc;
+    in.steps = steps;
+    rc = run_kernel(h, in);
+    if (rc != ASLAM_OK) return rc;
+    // the last message stays "current" (ekf.cpp:105: the list persists until replaced)
+    h->cur_range = d_range + (size_t)(steps - 1) * total;
+    h->cur_bearing = d_bearing + (size_t)(steps - 1) * total;
+    h->cur_offsets = nullptr;
+    h->cur_total = (uint32_t)total;
+    h->have_obs = false;  // no offsets array for it: a later step() needs a fresh set_observations
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_get_state(aslam_filter* h, double* X, double* P, uint32_t* N, int32_t* assoc,
+                                    uint32_t* status) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t B = h->st.batch, ld = h->st.ld;
+    if (X) ASLAM_CUDA(cudaMemcpyAsync(X, h->st.X, B * ld * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (P) {
+        aslam_status rc = ensure_scratch(h, B * ld * ld * sizeof(double));
+        if (rc != ASLAM_OK) return rc;
+        batch_transpose_kernel<<<(unsigned)B, 128, 0, h->stream>>>(h->st.P, h->d_scratch, (uint32_t)ld);
+        ASLAM_CUDA(cudaGetLastError());
+        ASLAM_CUDA(cudaMemcpyAsync(P, h->d_scratch, B * ld * ld * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (N) ASLAM_CUDA(cudaMemcpyAsync(N, h->st.N, B * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (status) ASLAM_CUDA(cudaMemcpyAsync(status, h->st.status, B * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (assoc && h->cur_total)
+        ASLAM_CUDA(cudaMemcpyAsync(assoc, h->d_assoc, (size_t)h->cur_total * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                   h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_get_aux(aslam_filter* h, double* Z, double* a00, double* a10) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t B = h->st.batch, ld = h->st.ld;
+    if (Z) ASLAM_CUDA(cudaMemcpyAsync(Z, h->st.Z, B * ld * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (a00 || a10) {
+        std::vector<double> a(2 * B);
+        ASLAM_CUDA(cudaMemcpyAsync(a.data(), h->st.A, 2 * B * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+        for (size_t b = 0; b < B; ++b) {
+            if (a00) a00[b] = a[2 * b];
+            if (a10) a10[b] = a[2 * b + 1];
+        }
+    }
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_get_wait(aslam_filter* h, uint32_t* count, float* range, float* bearing, uint32_t* hits) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t B = h->st.batch, W = ASLAM_MAX_WAIT;
+    if (count) ASLAM_CUDA(cudaMemcpyAsync(count, h->st.wcount, B * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (range) ASLAM_CUDA(cudaMemcpyAsync(range, h->st.wrange, B * W * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (bearing)
+        ASLAM_CUDA(cudaMemcpyAsync(bearing, h->st.wbearing, B * W * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (hits) ASLAM_CUDA(cudaMemcpyAsync(hits, h->st.whits, B * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_get_landmarks(aslam_filter* h, double* x, double* y, uint32_t* count) {
+    if (!h || !x || !y || !count) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t B = h->st.batch, lmax = (h->st.ld - 3) / 2;
+    const size_t bytes = 2 * B * lmax * sizeof(double) + B * sizeof(uint32_t);
+    aslam_status rc = ensure_scratch(h, bytes);
+    if (rc != ASLAM_OK) return rc;
+    double* dx = h->d_scratch;
+    double* dy = dx + B * lmax;
+    uint32_t* dc = reinterpret_cast<uint32_t*>(dy + B * lmax);
+    batch_landmarks_kernel<<<(unsigned)((B + 127) / 128), 128, 0, h->stream>>>(h->st, dx, dy, dc);
+    ASLAM_CUDA(cudaGetLastError());
+    ASLAM_CUDA(cudaMemcpyAsync(x, dx, B * lmax * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(y, dy, B * lmax * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(count, dc, B * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_device_state(aslam_filter* h, const double** d_X, const uint32_t** d_N) {
+    if (!h) return ASLAM_ERR_ARG;
+    if (d_X) *d_X = h->st.X;
+    if (d_N) *d_N = h->st.N;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_load_state(aslam_filter* h, const uint32_t* N, const double* X, const double* Z,
+                                     const double* P) {
+    if (!h || !N || !X || !Z || !P) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t B = h->st.batch, ld = h->st.ld;
+    for (size_t b = 0; b < B; ++b)
+        if (N[b] < 3 || N[b] > ld || (int32_t)N[b] >= h->cfg.max_state_dim || (N[b] & 1u) == 0) {
+            set_error("load_state: N must be odd, >= 3 and < max_state_dim");
+            return ASLAM_ERR_ARG;
+        }
+    aslam_status rc = ensure_scratch(h, B * ld * ld * sizeof(double));
+    if (rc != ASLAM_OK) return rc;
+    ASLAM_CUDA(cudaMemcpyAsync(h->st.N, N, B * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->st.X, X, B * ld * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->st.Z, Z, B * ld * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_scratch, P, B * ld * ld * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    batch_transpose_kernel<<<(unsigned)B, 128, 0, h->stream>>>(h->d_scratch, h->st.P, (uint32_t)ld);
+    ASLAM_CUDA(cudaGetLastError());
+    ASLAM_CUDA(cudaMemsetAsync(h->st.flags, 0, B * sizeof(uint32_t), h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+}  // extern "C"

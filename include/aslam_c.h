@@ -1,0 +1,205 @@
+/*
+ * aslam_c.h -- C ABI of the B200-native EKF/UKF-SLAM filter core (libaslam_b200.so).
+ *
+ * This is the drop-in boundary for the filter hot path of iamarkaj/AwesomeSLAM. The
+ * reference has no FFI layer: its "API" is two ROS node classes whose private methods are
+ * driven by callbacks. Each entry point below names the reference member it replaces
+ * (paths relative to awesome_slam/ in the reference tree).
+ *
+ *   aslam_config                 <-> include/awesome_slam/config.h:39-65 (compile-time consts)
+ *   aslam_{ekf,ukf}_create       <-> EKFSlam::EKFSlam + initialize   src/ekf/ekf.cpp:38-71
+ *                                    UKFSlam::UKFSlam + initialize   src/ukf/ukf.cpp:38-67
+ *   aslam_filter_set_observations<-> cbSensorLandmark                ekf.cpp:102-114, ukf.cpp:98-110
+ *   aslam_filter_step            <-> cbOdom (updateZandA/updateZ, X=Z once, slam)
+ *                                                                    ekf.cpp:74-99,  ukf.cpp:70-95
+ *   aslam_filter_get_state       <-> param.X / param.P / N / corr_id ekf.h:56-67, ukf.h:56-82
+ *   aslam_filter_get_landmarks   <-> convertToLandmarkMsg            include/awesome_slam/common.h:93-108
+ *   aslam_large_*                <-> the same slam() math (ekf.cpp:293-311, ukf.cpp:260-392) for
+ *                                    one filter whose map is too large for the batched kernels
+ *
+ * Conventions
+ *   - Plain C types only; no exceptions cross the boundary. Every call returns aslam_status.
+ *   - Host pointers unless the name ends in _device. Matrices are COLUMN-MAJOR (Eigen's
+ *     MatrixXd layout) with an explicit leading dimension.
+ *   - A handle owns its device memory and one CUDA stream; calls are enqueued in order and
+ *     are asynchronous unless they return data to host memory. A handle is not thread-safe;
+ *     distinct handles may be used from distinct threads.
+ *   - There is NO CPU fallback: without a usable CUDA device create() fails with
+ *     ASLAM_ERR_CUDA.
+ */
+#ifndef ASLAM_C_H
+#define ASLAM_C_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t aslam_status;
+enum {
+    ASLAM_OK = 0,
+    ASLAM_ERR_ARG = -1,         /* null pointer / size out of range */
+    ASLAM_ERR_CUDA = -2,        /* CUDA runtime error: see aslam_last_error() */
+    ASLAM_ERR_UNSUPPORTED = -3, /* e.g. max_state_dim too large for the batched kernels */
+    ASLAM_ERR_NOT_READY = -4    /* step before the first set_observations (ekf.cpp:76) */
+};
+
+/* Per-filter status bits (reference failure modes that are silent there) */
+enum {
+    ASLAM_ST_CAP_REJECTED = 1u << 0,  /* updateNewLandmark dropped a batch (ekf.cpp:263-268) */
+    ASLAM_ST_LLT_FAILED = 1u << 1,    /* UKF: Paug not positive definite this step (ukf.cpp:280) */
+    ASLAM_ST_NONFINITE = 1u << 2,     /* X or P holds a NaN/Inf */
+    ASLAM_ST_WAIT_OVERFLOW = 1u << 3, /* wait-list exceeded ASLAM_MAX_WAIT (reference: unbounded) */
+    ASLAM_ST_OBS_OVERFLOW = 1u << 4   /* more than ASLAM_MAX_OBS observations in one message */
+};
+
+#define ASLAM_MAX_WAIT 48u /* capacity of the per-filter new-landmark wait-list */
+#define ASLAM_MAX_OBS 64u  /* observations per filter per message */
+#define ASLAM_BATCH_MAX_DIM 64 /* largest max_state_dim the batched kernels accept */
+
+/* config.h:39-65. Defaults (aslam_config_default) equal the reference's constants. */
+typedef struct aslam_config {
+    float pi;                   /* PI 3.141592654f                    config.h:39 */
+    float min_dist_thresh;      /* MIN_DIST_THRESH 0.5                config.h:43 */
+    int32_t min_landmark_occ;   /* MIN_LANDMARK_OCC 10                config.h:44 */
+    int32_t max_state_dim;      /* MAX_LANDMARK_COUNT 30 (compared with the STATE dim N) :45 */
+    float ukf_std_a;            /* config.h:54 */
+    float ukf_std_yaw;          /* config.h:55 */
+    float ukf_kp_robot_pose;    /* config.h:56 */
+    float ukf_kp_landmark_pose; /* config.h:57 */
+    float ukf_kr;               /* config.h:58 */
+    float ukf_kq;               /* config.h:59 */
+    float ekf_kp_robot_pose;    /* config.h:62 */
+    float ekf_kp_landmark_pose; /* config.h:63 (dead in the reference) */
+    float ekf_kr;               /* config.h:64 */
+    float ekf_kq;               /* config.h:65 */
+} aslam_config;
+
+/* One nav_msgs/Odometry per filter, structure-of-arrays over the batch. Only the fields the
+ * reference reads (ekf.cpp:94,139-142,206-209). `yaw` is quat2euler(w,x,y,z) (tools.h:62-66)
+ * evaluated by the caller -- aslam_quat2euler() does it -- and `dt` is delta_time of
+ * ekf.cpp:80, both already rounded to float as in the reference. */
+typedef struct aslam_odom {
+    const double* x;   /* pose.pose.position.x   [batch] */
+    const double* y;   /* pose.pose.position.y   [batch] */
+    const float* yaw;  /* quat2euler(orientation) [batch] */
+    const double* vx;  /* twist.twist.linear.x   [batch] */
+    const double* az;  /* twist.twist.angular.z  [batch] */
+    const float* dt;   /* delta_time             [batch] */
+} aslam_odom;
+
+typedef struct aslam_filter aslam_filter; /* batched EKF or UKF filters */
+typedef struct aslam_large aslam_large;   /* one large-map filter */
+
+enum { ASLAM_KIND_EKF = 0, ASLAM_KIND_UKF = 1 };
+
+void aslam_config_default(aslam_config* cfg);
+const char* aslam_last_error(void);
+const char* aslam_version(void);
+int32_t aslam_device_count(void);
+
+/* tools.h:62-66 quat2euler: arguments rounded to float, atan2f. Host-side helper. */
+float aslam_quat2euler(double w, double x, double y, double z);
+
+/* ---------------------------------------------------------------- batched filters -------- */
+aslam_status aslam_ekf_create(const aslam_config* cfg, uint32_t batch, int32_t device, aslam_filter** out);
+aslam_status aslam_ukf_create(const aslam_config* cfg, uint32_t batch, int32_t device, aslam_filter** out);
+aslam_status aslam_filter_destroy(aslam_filter* h);
+aslam_status aslam_filter_sync(aslam_filter* h);
+/* cudaStream_t of the handle, for callers that enqueue their own copies around the calls */
+void* aslam_filter_stream(aslam_filter* h);
+uint32_t aslam_filter_batch(const aslam_filter* h);
+uint32_t aslam_filter_ld(const aslam_filter* h); /* padded state dim used for X/P export */
+int32_t aslam_filter_kind(const aslam_filter* h);
+
+/* cbSensorLandmark. offsets has batch+1 entries; filter b owns observations
+ * [offsets[b], offsets[b+1]) of range[] / bearing[]. The list persists until replaced. */
+aslam_status aslam_filter_set_observations(aslam_filter* h, const float* range, const float* bearing,
+                                           const uint32_t* offsets);
+/* Same with device-resident arrays (no copy; they must stay valid until the next call). */
+aslam_status aslam_filter_set_observations_device(aslam_filter* h, const float* d_range,
+                                                  const float* d_bearing, const uint32_t* d_offsets);
+
+/* cbOdom for every filter of the batch: association, wait-list, growth, predict, update. */
+aslam_status aslam_filter_step(aslam_filter* h, const aslam_odom* odom);
+aslam_status aslam_filter_step_device(aslam_filter* h, const aslam_odom* d_odom);
+
+/* Replay `steps` consecutive messages that are already resident in HBM, step-major:
+ * odometry arrays [steps][batch], observations [steps][batch][obs_per_filter] (every filter
+ * sees obs_per_filter observations per step). Equivalent to `steps` x (set_observations_device
+ * + step_device) but keeps each filter's covariance on-chip between steps. */
+aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const aslam_odom* d_odom,
+                                     const float* d_range, const float* d_bearing, uint32_t obs_per_filter);
+
+/* State export. Any pointer may be NULL. ld = aslam_filter_ld().
+ *   X [batch][ld], P [batch][ld*ld] column-major with leading dimension ld, entries beyond a
+ *   filter's N are zero; N [batch]; status [batch];
+ *   assoc [total observations of the last message]: landmark slot j (0,2,4,.. as corr_id in
+ *   ekf.cpp:160-173) the observation was written to, or -1 when it went to the wait-list. */
+aslam_status aslam_filter_get_state(aslam_filter* h, double* X, double* P, uint32_t* N, int32_t* assoc,
+                                    uint32_t* status);
+/* Z [batch][ld]; EKF only: a00/a10 [batch] = A(0,0), A(1,0) (ekf.cpp:210-211) */
+aslam_status aslam_filter_get_aux(aslam_filter* h, double* Z, double* a00, double* a10);
+/* wait-list export: count [batch]; range/bearing/hits [batch][ASLAM_MAX_WAIT] */
+aslam_status aslam_filter_get_wait(aslam_filter* h, uint32_t* count, float* range, float* bearing,
+                                   uint32_t* hits);
+/* convertToLandmarkMsg: x,y [batch][(ld-3)/2]; count [batch] */
+aslam_status aslam_filter_get_landmarks(aslam_filter* h, double* x, double* y, uint32_t* count);
+/* Device pointers of the live state for zero-copy consumers: X [batch][ld], N [batch] */
+aslam_status aslam_filter_device_state(aslam_filter* h, const double** d_X, const uint32_t** d_N);
+
+/* Checkpoint / start from a supplied state (the reference has none).
+ * Sets N, X, Z, P for every filter; marks it initialised (init_x = init_z = false). */
+aslam_status aslam_filter_load_state(aslam_filter* h, const uint32_t* N, const double* X, const double* Z,
+                                     const double* P);
+
+/* ---------------------------------------------------------------- large-map filter ------- */
+/* One filter with n = 3 + 2 * landmarks state entries; P is n x n FP64 in HBM.
+ * Sharding: this handle owns covariance rows [row_begin, row_end) (pass 0, n for one GPU). */
+aslam_status aslam_large_ekf_create(const aslam_config* cfg, uint32_t n, uint32_t row_begin, uint32_t row_end,
+                                    int32_t device, aslam_large** out);
+aslam_status aslam_large_ukf_create(const aslam_config* cfg, uint32_t n, int32_t device, aslam_large** out);
+aslam_status aslam_large_destroy(aslam_large* h);
+aslam_status aslam_large_sync(aslam_large* h);
+void* aslam_large_stream(aslam_large* h);
+/* X [n], Z [n] (may be NULL: taken as h(X)), P column-major n x n with leading dimension ldp
+ * (the handle copies its own rows). */
+aslam_status aslam_large_load_state(aslam_large* h, const double* X, const double* Z, const double* P, size_t ldp);
+aslam_status aslam_large_get_state(aslam_large* h, double* X, double* P, size_t ldp);
+/* cbSensorLandmark + cbOdom for one message pair. m observations; assoc_out[m] (may be NULL)
+ * receives the landmark slot or -1. EKF: row-subset joint update over the pose rows and the
+ * rows of the landmarks observed in THIS message; with every
+ * landmark observed it equals ekf.cpp:300-310. UKF: the full ukf.cpp:260-392 step. */
+aslam_status aslam_large_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                              const float* range, const float* bearing, uint32_t m, int32_t* assoc_out);
+/* Sharded EKF only (row_end - row_begin < n): the step is split around the one exchange.
+ *   phase1: association, predict, local slices of P H^T and of the observed rows of P;
+ *           writes this rank's contribution (q x n doubles, zeros outside owned rows /
+ *           q = rows in use, <= 3 + 2*ASLAM_MAX_OBS) into the device buffer returned by
+ *           aslam_large_exchange_buffer(); the caller sums the buffers of all ranks in place
+ *           (NCCL all-reduce over NVLink; every element has exactly one non-zero owner).
+ *   phase2: S, K for the owned rows, X update, P_local -= K_local * (H P). */
+aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az,
+                                     float dt, const float* range, const float* bearing, uint32_t m,
+                                     uint32_t* q_out);
+aslam_status aslam_large_exchange_buffer(aslam_large* h, double** d_buf, size_t* count);
+aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out);
+
+/* ---------------------------------------------------------------- synthetic replay ------- */
+/* Deterministic replay generator of SURVEY.md sec. 8d (host code, no GPU needed):
+ * map (lm_x, lm_y)[L]; `warm` stationary steps then vx, az constant, dt = 1.0f;
+ * noise sigma: odom x,y,yaw = 0.01, range = 0.01, bearing = 0.005; per-filter RNG
+ * mt19937_64(seed0 + filter) + Box-Muller. Output is step-major:
+ *   ox, oy, vx, az: double [steps][batch]; yaw, dt: float [steps][batch];
+ *   range, bearing: float [steps][batch][L] listed in increasing true bearing. */
+aslam_status aslam_replay_generate(const double* lm_x, const double* lm_y, uint32_t L, uint32_t batch,
+                                   uint32_t steps, uint32_t warm, double vx, double az, uint64_t seed0,
+                                   uint32_t first_filter, double* ox, double* oy, float* yaw, double* ovx,
+                                   double* oaz, float* dt, float* range, float* bearing);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ASLAM_C_H */
