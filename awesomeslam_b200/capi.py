@@ -1,0 +1,158 @@
+"""ctypes binding of libaslam_b200.so (include/aslam_c.h).
+
+This is the same stub a maintainer of the reference would add on their side of the boundary
+(INTEGRATION.md shows the C++ one). There is NO CPU path behind it: if the CUDA library has
+not been built, `lib()` raises; if no CUDA device is usable, the create calls return
+ASLAM_ERR_CUDA and `check` raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libaslam_b200.so")
+
+ASLAM_OK = 0
+ASLAM_ERR_ARG = -1
+ASLAM_ERR_CUDA = -2
+ASLAM_ERR_UNSUPPORTED = -3
+ASLAM_ERR_NOT_READY = -4
+
+ST_CAP_REJECTED = 1 << 0
+ST_LLT_FAILED = 1 << 1
+ST_NONFINITE = 1 << 2
+ST_WAIT_OVERFLOW = 1 << 3
+ST_OBS_OVERFLOW = 1 << 4
+
+MAX_WAIT = 48
+MAX_OBS = 64
+KIND_EKF = 0
+KIND_UKF = 1
+
+
+class AslamError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__("aslam status %d: %s" % (status, msg))
+        self.status = status
+
+
+class Config(C.Structure):
+    """aslam_config == include/awesome_slam/config.h:39-65 of the reference."""
+    _fields_ = [
+        ("pi", C.c_float), ("min_dist_thresh", C.c_float),
+        ("min_landmark_occ", C.c_int32), ("max_state_dim", C.c_int32),
+        ("ukf_std_a", C.c_float), ("ukf_std_yaw", C.c_float),
+        ("ukf_kp_robot_pose", C.c_float), ("ukf_kp_landmark_pose", C.c_float),
+        ("ukf_kr", C.c_float), ("ukf_kq", C.c_float),
+        ("ekf_kp_robot_pose", C.c_float), ("ekf_kp_landmark_pose", C.c_float),
+        ("ekf_kr", C.c_float), ("ekf_kq", C.c_float),
+    ]
+
+
+class Odom(C.Structure):
+    """aslam_odom: SoA pointers (host or device, depending on the call)."""
+    _fields_ = [("x", C.c_void_p), ("y", C.c_void_p), ("yaw", C.c_void_p),
+                ("vx", C.c_void_p), ("az", C.c_void_p), ("dt", C.c_void_p)]
+
+
+_vp = C.c_void_p
+_u32 = C.c_uint32
+_i32 = C.c_int32
+_f64 = C.c_double
+_f32 = C.c_float
+_sz = C.c_size_t
+
+# name -> (restype, argtypes); every symbol include/aslam_c.h declares
+SIGNATURES = {
+    "aslam_config_default": (None, [C.POINTER(Config)]),
+    "aslam_last_error": (C.c_char_p, []),
+    "aslam_version": (C.c_char_p, []),
+    "aslam_device_count": (_i32, []),
+    "aslam_quat2euler": (_f32, [_f64, _f64, _f64, _f64]),
+    "aslam_ekf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
+    "aslam_ukf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
+    "aslam_filter_destroy": (_i32, [_vp]),
+    "aslam_filter_sync": (_i32, [_vp]),
+    "aslam_filter_stream": (_vp, [_vp]),
+    "aslam_filter_batch": (_u32, [_vp]),
+    "aslam_filter_ld": (_u32, [_vp]),
+    "aslam_filter_kind": (_i32, [_vp]),
+    "aslam_filter_set_observations": (_i32, [_vp, _vp, _vp, _vp]),
+    "aslam_filter_set_observations_device": (_i32, [_vp, _vp, _vp, _vp]),
+    "aslam_filter_step": (_i32, [_vp, C.POINTER(Odom)]),
+    "aslam_filter_step_device": (_i32, [_vp, C.POINTER(Odom)]),
+    "aslam_filter_run_device": (_i32, [_vp, _u32, C.POINTER(Odom), _vp, _vp, _u32]),
+    "aslam_filter_run_host": (_i32, [_vp, _u32, C.POINTER(Odom), _vp, _vp, _u32]),
+    "aslam_filter_get_state": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "aslam_filter_get_aux": (_i32, [_vp, _vp, _vp, _vp]),
+    "aslam_filter_get_wait": (_i32, [_vp, _vp, _vp, _vp, _vp]),
+    "aslam_filter_get_landmarks": (_i32, [_vp, _vp, _vp, _vp]),
+    "aslam_filter_get_llt_fail": (_i32, [_vp, _vp]),
+    "aslam_filter_device_state": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
+    "aslam_filter_load_state": (_i32, [_vp, _vp, _vp, _vp, _vp]),
+    "aslam_filter_launch_count": (C.c_uint64, [_vp]),
+    "aslam_large_ekf_create": (_i32, [C.POINTER(Config), _u32, _u32, _u32, _i32, C.POINTER(_vp)]),
+    "aslam_large_ukf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
+    "aslam_large_destroy": (_i32, [_vp]),
+    "aslam_large_sync": (_i32, [_vp]),
+    "aslam_large_stream": (_vp, [_vp]),
+    "aslam_large_load_state": (_i32, [_vp, _vp, _vp, _vp, _sz]),
+    "aslam_large_get_state": (_i32, [_vp, _vp, _vp, _sz]),
+    "aslam_large_step": (_i32, [_vp, _f64, _f64, _f32, _f64, _f64, _f32, _vp, _vp, _u32, _vp]),
+    "aslam_large_step_phase1": (_i32, [_vp, _f64, _f64, _f32, _f64, _f64, _f32, _vp, _vp, _u32, C.POINTER(_u32)]),
+    "aslam_large_exchange_buffer": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
+    "aslam_large_step_phase2": (_i32, [_vp, _vp]),
+    "aslam_large_launch_count": (C.c_uint64, [_vp]),
+    "aslam_large_last_kernel_ms": (_i32, [_vp, C.POINTER(_f32)]),
+    "aslam_large_status": (_i32, [_vp, C.POINTER(_u32), C.POINTER(_i32)]),
+    "aslam_replay_generate": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, _f64, _f64, C.c_uint64, _u32,
+                                     _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+}
+
+_lib = None
+
+
+def lib():
+    """Loads the CUDA library; raises (never falls back) when it is not there."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "%s is missing: build it with `python -m awesomeslam_b200.build` "
+            "(there is no CPU implementation behind this package)" % LIB_PATH)
+    l = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(l, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = l
+    return l
+
+
+def check(status):
+    if status != ASLAM_OK:
+        raise AslamError(status, lib().aslam_last_error().decode("utf-8", "replace"))
+
+
+def default_config(**overrides):
+    cfg = Config()
+    lib().aslam_config_default(C.byref(cfg))
+    for k, v in overrides.items():
+        if not hasattr(cfg, k):
+            raise AttributeError(k)
+        setattr(cfg, k, v)
+    return cfg
+
+
+def ptr(a):
+    """void* of a numpy array (must be C-contiguous) or None."""
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def as_np(a, dtype):
+    return np.ascontiguousarray(a, dtype=dtype)

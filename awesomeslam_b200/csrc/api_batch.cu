@@ -121,6 +121,9 @@ struct aslam_filter {
     size_t assoc_capacity = 0;
     double* d_scratch = nullptr;  // export scratch, lazily sized
     size_t scratch_bytes = 0;
+    unsigned char* d_replay = nullptr;  // run_host staging: [steps] messages
+    size_t replay_bytes = 0;
+    uint64_t launches = 0;  // filter-step kernels launched so far
 };
 
 namespace {
@@ -214,6 +217,7 @@ aslam_status create_filter(int kind, const aslam_config* cfg, uint32_t batch, in
 }
 
 aslam_status run_kernel(aslam_filter* h, const BatchInput& in) {
+    h->launches += 1;
     if (h->kind == ASLAM_KIND_EKF) return launch_ekf_batched(h->cfg, h->st, in, h->stream);
     return launch_ukf_batched(h->cfg, h->st, in, h->stream);
 }
@@ -270,7 +274,7 @@ aslam_status aslam_filter_destroy(aslam_filter* h) {
     void* ptrs[] = {h->st.X,      h->st.Z,       h->st.P,     h->st.A,        h->st.N,    h->st.status,
                     h->st.flags,  h->st.wcount,  h->st.wrange, h->st.wbearing, h->st.whits, h->st.llt_fail,
                     h->d_odom64,  h->d_odom32,   h->d_range,  h->d_bearing,   h->d_offsets, h->d_assoc,
-                    h->d_scratch};
+                    h->d_scratch, h->d_replay};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -413,6 +417,59 @@ aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const asla
     h->cur_offsets = nullptr;
     h->cur_total = (uint32_t)total;
     h->have_obs = false;  // no offsets array for it: a later step() needs a fresh set_observations
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_run_host(aslam_filter* h, uint32_t steps, const aslam_odom* o, const float* range,
+                                   const float* bearing, uint32_t obs_per_filter) {
+    if (!h || !o || !o->x || !o->y || !o->yaw || !o->vx || !o->az || !o->dt) return ASLAM_ERR_ARG;
+    if (steps == 0) return ASLAM_OK;
+    if (obs_per_filter && (!range || !bearing)) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t n = (size_t)steps * h->st.batch, no = n * obs_per_filter;
+    // one staging block: 4 double arrays, then 2 + 2*obs float arrays (all 8-byte aligned starts)
+    const size_t bytes = n * 4 * sizeof(double) + (n * 2 + no * 2) * sizeof(float) + 64;
+    if (bytes > h->replay_bytes) {
+        ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+        if (h->d_replay) cudaFree(h->d_replay);
+        h->d_replay = nullptr;
+        h->replay_bytes = 0;
+        ASLAM_CUDA(cudaMalloc((void**)&h->d_replay, bytes));
+        h->replay_bytes = bytes;
+    }
+    double* d64 = reinterpret_cast<double*>(h->d_replay);
+    float* d32 = reinterpret_cast<float*>(d64 + 4 * n);
+    const cudaMemcpyKind k = cudaMemcpyHostToDevice;
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 0 * n, o->x, n * sizeof(double), k, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 1 * n, o->y, n * sizeof(double), k, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 2 * n, o->vx, n * sizeof(double), k, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 3 * n, o->az, n * sizeof(double), k, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(d32 + 0 * n, o->yaw, n * sizeof(float), k, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(d32 + 1 * n, o->dt, n * sizeof(float), k, h->stream));
+    float* dr = d32 + 2 * n;
+    float* db = dr + no;
+    if (no) {
+        ASLAM_CUDA(cudaMemcpyAsync(dr, range, no * sizeof(float), k, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(db, bearing, no * sizeof(float), k, h->stream));
+    }
+    aslam_odom d;
+    d.x = d64;
+    d.y = d64 + n;
+    d.vx = d64 + 2 * n;
+    d.az = d64 + 3 * n;
+    d.yaw = d32;
+    d.dt = d32 + n;
+    return aslam_filter_run_device(h, steps, &d, dr, db, obs_per_filter);
+}
+
+uint64_t aslam_filter_launch_count(aslam_filter* h) { return h ? h->launches : 0; }
+
+aslam_status aslam_filter_get_llt_fail(aslam_filter* h, int32_t* fail_k) {
+    if (!h || !fail_k) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    ASLAM_CUDA(cudaMemcpyAsync(fail_k, h->st.llt_fail, (size_t)h->st.batch * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                               h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
     return ASLAM_OK;
 }
 

@@ -68,6 +68,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
     const bool live = f < kp.st.batch;
     EkfSlot<NP>& s = slots[fs];
     const int j0 = ct * CPT;  // first owned column
+    __shared__ int s_lcta;    // landmark blocks any filter of this CTA needs this step
 
     double p[CPT][NP];
     {
@@ -103,6 +104,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
         const size_t si = (size_t)step * kp.st.batch + f;
         // ---- cbOdom gate (ekf.cpp:76): nothing happens before the first observation message
         const bool gated = !live || (s.fr.flags & FLAG_INIT_Z);
+        if (threadIdx.x == 0) s_lcta = 0;
         // ---- updateZandA, ekf.cpp:139-142
         if (ct == 0 && !gated) {
             s.fr.ox = kp.in.ox[si];
@@ -147,17 +149,23 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
             s.X[0] = x;
             s.X[1] = y;
             s.X[2] = (double)normalize_angle((float)th, kp.fp.pi);
+            atomicMax(&s_lcta, (int)(s.fr.N - 3) / 2);
         }
         __syncthreads();
         const uint32_t N = s.fr.N;
+        const int lcta = s_lcta;
         // ---- growth of P (ekf.cpp:277): new diagonal entries, the rest of the new rows/cols is 0
         if (s.fr.grew_from && !gated) {
             const uint32_t g0 = s.fr.grew_from;
+            // (arithmetic mask, not `if (i == j) p[i] = ..`: the latter is turned into a dynamically
+            // indexed store, which would move the whole register tile to local memory)
 #pragma unroll
-            for (int c = 0; c < CPT; ++c)
+            for (int c = 0; c < CPT; ++c) {
+                const uint32_t j = j0 + c;
+                const double dj = (j >= g0 && j < N) ? kp.kp_lm : 0.0;
 #pragma unroll
-                for (int i = 0; i < NP; ++i)
-                    if (i == j0 + c && (uint32_t)i >= g0 && (uint32_t)i < N) p[c][i] = kp.kp_lm;
+                for (int i = 0; i < NP; ++i) p[c][i] = fma((double)((uint32_t)i == j), dj, p[c][i]);
+            }
         }
         // ---- P = A P A' + Q (ekf.cpp:297); A = I except A(0,0), A(1,0)
         if (!gated) {
@@ -293,7 +301,8 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                     s.dl[buf][j0 + c] = dl[c];
                 }
             }
-            if (!__syncthreads_or(act)) break;  // no filter of this CTA has landmark l
+            if (l >= lcta) break;  // no filter of this CTA has landmark l (CTA-uniform)
+            __syncthreads();
             if (act) {
                 const double2 w0 = *reinterpret_cast<const double2*>(&s.V[buf][0]);
                 const double2 w1 = *reinterpret_cast<const double2*>(&s.V[buf][2]);

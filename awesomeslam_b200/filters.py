@@ -1,0 +1,246 @@
+"""Host-side mirror of the reference's filter classes over the C ABI.
+
+The reference's "API" is two ROS node classes, aslam::EKFSlam (src/ekf/ekf.h:71-132) and
+aslam::UKFSlam (src/ukf/ukf.h:86-144), whose callbacks are
+
+    cbSensorLandmark(Landmarks{x=range[], y=bearing[]})      ekf.cpp:102-114, ukf.cpp:98-110
+    cbOdom(Odometry)  -> publishes Landmarks{x[], y[]}        ekf.cpp:74-99,   ukf.cpp:70-95
+
+`EKFSlam` / `UKFSlam` below keep those names and argument meanings for ONE filter (batch = 1);
+`BatchedFilter` is the same thing for B independent filters (structure-of-arrays messages).
+All arithmetic happens in the CUDA library; this file only marshals buffers.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+
+class Odometry:
+    """The nav_msgs/Odometry fields the reference reads (ekf.cpp:94,139-142,206-209)."""
+
+    __slots__ = ("x", "y", "qw", "qx", "qy", "qz", "vx", "az")
+
+    def __init__(self, x=0.0, y=0.0, qw=1.0, qx=0.0, qy=0.0, qz=0.0, vx=0.0, az=0.0):
+        self.x, self.y = x, y
+        self.qw, self.qx, self.qy, self.qz = qw, qx, qy, qz
+        self.vx, self.az = vx, az
+
+
+class BatchedFilter:
+    """B independent EKF- or UKF-SLAM filters on one GPU (aslam_filter handle)."""
+
+    def __init__(self, kind="ekf", batch=1, device=0, config=None, **cfg_overrides):
+        self._h = C.c_void_p()
+        self._lib = capi.lib()
+        self.config = config if config is not None else capi.default_config(**cfg_overrides)
+        self.kind = kind
+        create = {"ekf": self._lib.aslam_ekf_create, "ukf": self._lib.aslam_ukf_create}[kind]
+        capi.check(create(C.byref(self.config), batch, device, C.byref(self._h)))
+        self.batch = batch
+        self.device = device
+        self.ld = self._lib.aslam_filter_ld(self._h)
+        self._keep = []  # host arrays referenced by in-flight async copies
+        self._obs_total = 0
+
+    # -- lifetime -------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.aslam_filter_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def stream(self):
+        return self._lib.aslam_filter_stream(self._h)
+
+    def sync(self):
+        capi.check(self._lib.aslam_filter_sync(self._h))
+        self._keep.clear()
+
+    # -- cbSensorLandmark -----------------------------------------------------------------
+    def set_observations(self, rng, brg, offsets=None):
+        """rng/brg: float32 [total]; offsets: uint32 [batch+1] (None: equal split)."""
+        rng = capi.as_np(rng, np.float32).ravel()
+        brg = capi.as_np(brg, np.float32).ravel()
+        if offsets is None:
+            per = rng.size // self.batch
+            assert per * self.batch == rng.size
+            offsets = np.arange(self.batch + 1, dtype=np.uint32) * np.uint32(per)
+        offsets = capi.as_np(offsets, np.uint32)
+        assert offsets.size == self.batch + 1 and int(offsets[-1]) == rng.size == brg.size
+        self._keep += [rng, brg, offsets]
+        self._obs_total = int(rng.size)
+        capi.check(self._lib.aslam_filter_set_observations(self._h, capi.ptr(rng), capi.ptr(brg), capi.ptr(offsets)))
+
+    # -- cbOdom ---------------------------------------------------------------------------
+    def step(self, x, y, yaw, vx, az, dt):
+        """One odometry message per filter. yaw: float32 quat2euler result; dt: float32."""
+        arrs = [capi.as_np(x, np.float64).ravel(), capi.as_np(y, np.float64).ravel(),
+                capi.as_np(yaw, np.float32).ravel(), capi.as_np(vx, np.float64).ravel(),
+                capi.as_np(az, np.float64).ravel(), capi.as_np(dt, np.float32).ravel()]
+        for a in arrs:
+            assert a.size == self.batch
+        self._keep += arrs
+        od = capi.Odom(*[capi.ptr(a) for a in arrs])
+        capi.check(self._lib.aslam_filter_step(self._h, C.byref(od)))
+
+    def run_host(self, steps, x, y, yaw, vx, az, dt, rng, brg, obs_per_filter):
+        """`steps` messages from HOST buffers (step-major [steps][batch](...[obs])): copies them to
+        the device and replays them in one launch. Asynchronous; call sync()/get_state()."""
+        arrs = [capi.as_np(x, np.float64), capi.as_np(y, np.float64), capi.as_np(yaw, np.float32),
+                capi.as_np(vx, np.float64), capi.as_np(az, np.float64), capi.as_np(dt, np.float32)]
+        rng = capi.as_np(rng, np.float32)
+        brg = capi.as_np(brg, np.float32)
+        for a in arrs:
+            assert a.size == steps * self.batch
+        assert rng.size == brg.size == steps * self.batch * obs_per_filter
+        self._keep += arrs + [rng, brg]
+        od = capi.Odom(*[capi.ptr(a) for a in arrs])
+        self._obs_total = self.batch * obs_per_filter
+        capi.check(self._lib.aslam_filter_run_host(self._h, steps, C.byref(od), capi.ptr(rng), capi.ptr(brg),
+                                                   obs_per_filter))
+
+    def run_device(self, steps, d_x, d_y, d_yaw, d_vx, d_az, d_dt, d_rng, d_brg, obs_per_filter):
+        """Same with device pointers (ints), e.g. torch tensors' data_ptr(). No copies."""
+        od = capi.Odom(d_x, d_y, d_yaw, d_vx, d_az, d_dt)
+        self._obs_total = self.batch * obs_per_filter
+        capi.check(self._lib.aslam_filter_run_device(self._h, steps, C.byref(od), d_rng, d_brg, obs_per_filter))
+
+    # -- state export ---------------------------------------------------------------------
+    def get_state(self, want_P=True, want_assoc=True):
+        B, ld = self.batch, self.ld
+        X = np.zeros((B, ld), np.float64)
+        P = np.zeros((B, ld, ld), np.float64) if want_P else None
+        N = np.zeros(B, np.uint32)
+        st = np.zeros(B, np.uint32)
+        assoc = np.full(max(self._obs_total, 1), -2, np.int32) if want_assoc else None
+        capi.check(self._lib.aslam_filter_get_state(self._h, capi.ptr(X), capi.ptr(P), capi.ptr(N),
+                                                    capi.ptr(assoc), capi.ptr(st)))
+        self._keep.clear()
+        if P is not None:
+            P = P.transpose(0, 2, 1)  # exported column-major -> index as P[b, i, j]
+        if assoc is not None:
+            assoc = assoc[:self._obs_total]
+        return {"X": X, "P": P, "N": N, "status": st, "assoc": assoc}
+
+    def get_aux(self):
+        B, ld = self.batch, self.ld
+        Z = np.zeros((B, ld), np.float64)
+        a00 = np.zeros(B, np.float64)
+        a10 = np.zeros(B, np.float64)
+        capi.check(self._lib.aslam_filter_get_aux(self._h, capi.ptr(Z), capi.ptr(a00), capi.ptr(a10)))
+        return {"Z": Z, "a00": a00, "a10": a10}
+
+    def get_wait(self):
+        B, W = self.batch, capi.MAX_WAIT
+        cnt = np.zeros(B, np.uint32)
+        r = np.zeros((B, W), np.float32)
+        b = np.zeros((B, W), np.float32)
+        h = np.zeros((B, W), np.uint32)
+        capi.check(self._lib.aslam_filter_get_wait(self._h, capi.ptr(cnt), capi.ptr(r), capi.ptr(b), capi.ptr(h)))
+        return {"count": cnt, "range": r, "bearing": b, "hits": h}
+
+    def get_llt_fail(self):
+        out = np.zeros(self.batch, np.int32)
+        capi.check(self._lib.aslam_filter_get_llt_fail(self._h, capi.ptr(out)))
+        return out
+
+    def get_landmarks(self):
+        """convertToLandmarkMsg (common.h:93-108): per filter the mapped landmark x[], y[]."""
+        B, lmax = self.batch, (self.ld - 3) // 2
+        x = np.zeros((B, lmax), np.float64)
+        y = np.zeros((B, lmax), np.float64)
+        c = np.zeros(B, np.uint32)
+        capi.check(self._lib.aslam_filter_get_landmarks(self._h, capi.ptr(x), capi.ptr(y), capi.ptr(c)))
+        return x, y, c
+
+    def load_state(self, N, X, Z, P):
+        """P given as [B, i, j]; padded to ld."""
+        B, ld = self.batch, self.ld
+        N = capi.as_np(N, np.uint32)
+        Xp = np.zeros((B, ld)); Zp = np.zeros((B, ld)); Pp = np.zeros((B, ld, ld))
+        for b in range(B):
+            n = int(N[b])
+            Xp[b, :n] = X[b][:n]
+            Zp[b, :n] = Z[b][:n]
+            Pp[b, :n, :n] = np.asarray(P[b])[:n, :n].T  # column-major on the wire
+        capi.check(self._lib.aslam_filter_load_state(self._h, capi.ptr(N), capi.ptr(Xp), capi.ptr(Zp), capi.ptr(Pp)))
+
+    @property
+    def launch_count(self):
+        return int(self._lib.aslam_filter_launch_count(self._h))
+
+
+class _SingleFilter:
+    """One filter with the reference's callback names."""
+
+    KIND = "ekf"
+
+    def __init__(self, device=0, config=None, **cfg_overrides):
+        self._f = BatchedFilter(self.KIND, 1, device, config, **cfg_overrides)
+        self._last_time = None
+
+    def close(self):
+        self._f.close()
+
+    def cbSensorLandmark(self, x, y):
+        """msg.x = ranges, msg.y = bearings (float64 on the wire, stored as float: ekf.cpp:111)."""
+        self._f.set_observations(np.asarray(x, np.float64).astype(np.float32),
+                                 np.asarray(y, np.float64).astype(np.float32))
+
+    def cbOdom(self, msg, delta_time=1.0):
+        """msg: Odometry. delta_time replaces the wall-clock difference of ekf.cpp:80 (capped at 1).
+        Returns the Landmarks message (x[], y[]) the reference publishes, or None while gated."""
+        lib = capi.lib()
+        yaw = lib.aslam_quat2euler(msg.qw, msg.qx, msg.qy, msg.qz)
+        dt = np.float32(min(float(delta_time), 1.0))
+        try:
+            self._f.step([msg.x], [msg.y], [yaw], [msg.vx], [msg.az], [dt])
+        except capi.AslamError as e:
+            if e.status == capi.ASLAM_ERR_NOT_READY:  # `if (init_z) return;` ekf.cpp:76
+                return None
+            raise
+        lx, ly, c = self._f.get_landmarks()
+        n = int(c[0])
+        return lx[0, :n].copy(), ly[0, :n].copy()
+
+    # state accessors (param.X / param.P / N of the reference)
+    def state(self):
+        s = self._f.get_state()
+        n = int(s["N"][0])
+        return {"N": n, "X": s["X"][0, :n].copy(), "P": s["P"][0, :n, :n].copy(),
+                "status": int(s["status"][0]), "assoc": s["assoc"].copy()}
+
+    @property
+    def batched(self):
+        return self._f
+
+
+class EKFSlam(_SingleFilter):
+    """aslam::EKFSlam (src/ekf/ekf.h:71-132)."""
+    KIND = "ekf"
+
+
+class UKFSlam(_SingleFilter):
+    """aslam::UKFSlam (src/ukf/ukf.h:86-144)."""
+    KIND = "ukf"
+
+    def llt_fail(self):
+        return int(self._f.get_llt_fail()[0])

@@ -133,6 +133,16 @@ aslam_status aslam_filter_step_device(aslam_filter* h, const aslam_odom* d_odom)
 aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const aslam_odom* d_odom,
                                      const float* d_range, const float* d_bearing, uint32_t obs_per_filter);
 
+/* Same replay from HOST buffers (the end-to-end entry point): copies the `steps` messages to the
+ * device on the handle's stream, then runs them as one launch. Asynchronous. */
+aslam_status aslam_filter_run_host(aslam_filter* h, uint32_t steps, const aslam_odom* odom, const float* range,
+                                   const float* bearing, uint32_t obs_per_filter);
+/* Number of filter-step kernels this handle has launched (bench.py's gpu_launches). */
+uint64_t aslam_filter_launch_count(aslam_filter* h);
+/* UKF: fail_k [batch] = first non-positive pivot column of Paug in the LAST step, -1 if it
+ * factorised (Eigen's silent LLT failure, ukf.cpp:280). */
+aslam_status aslam_filter_get_llt_fail(aslam_filter* h, int32_t* fail_k);
+
 /* State export. Any pointer may be NULL. ld = aslam_filter_ld().
  *   X [batch][ld], P [batch][ld*ld] column-major with leading dimension ld, entries beyond a
  *   filter's N are zero; N [batch]; status [batch];

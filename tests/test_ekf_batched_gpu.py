@@ -1,0 +1,162 @@
+"""Parity of the batched EKF CUDA path (through the C ABI) against the CPU oracle.
+
+configs 1 and 3 of BASELINE.json. Tolerance: norm-wise relative error <= 1e-9 on X and on P
+(FP64 path); N, association indices, wait-list and status must be EQUAL.
+"""
+import numpy as np
+import pytest
+
+from util import TOL_F64, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_single(aslam, orc, kind, steps, cfg_over=None, lm=None, check_every=1, vx=0.05, az=0.1, warm=15, seed=1):
+    cfg_over = cfg_over or {}
+    lmx, lmy = lm if lm is not None else aslam.map_cfg1()
+    rp = aslam.Replay(lmx, lmy, 1, steps, warm=warm, vx=vx, az=az, seed0=seed)
+    f = aslam.BatchedFilter(kind, 1, 0, **cfg_over)
+    o = orc.Filter(kind, **cfg_over)
+    worst = {"X": 0.0, "P": 0.0}
+    for t in range(steps):
+        f.set_observations(rp.range[t, 0], rp.bearing[t, 0])
+        o.set_observations(rp.range[t, 0], rp.bearing[t, 0])
+        f.step(rp.x[t], rp.y[t], rp.yaw[t], rp.vx[t], rp.az[t], rp.dt[t])
+        o.step(rp.x[t, 0], rp.y[t, 0], rp.yaw[t, 0], rp.vx[t, 0], rp.az[t, 0], rp.dt[t, 0])
+        if t % check_every and t != steps - 1:
+            continue
+        s = f.get_state()
+        X, Z, P = o.state()
+        n = o.N
+        assert int(s["N"][0]) == n, "state dim differs at step %d" % t
+        assert np.array_equal(s["assoc"], o.assoc()), "association differs at step %d" % t
+        ex, ep = relerr(s["X"][0, :n], X), relerr(s["P"][0, :n, :n], P)
+        worst["X"] = max(worst["X"], ex)
+        worst["P"] = max(worst["P"], ep)
+        assert ex <= TOL_F64 and ep <= TOL_F64, "step %d: relerr X %.3e P %.3e" % (t, ex, ep)
+        assert not np.any(s["X"][0, n:]) and not np.any(s["P"][0, n:, :]) and not np.any(s["P"][0, :, n:])
+        w = f.get_wait()
+        wr, wb, wc = o.wait()
+        k = int(w["count"][0])
+        assert k == wr.size
+        assert np.array_equal(w["range"][0, :k], wr) and np.array_equal(w["bearing"][0, :k], wb)
+        assert np.array_equal(w["hits"][0, :k], wc)
+        if kind == "ekf":
+            aux = f.get_aux()
+            a00, a10 = o.a_entries()
+            assert relerr(aux["Z"][0, :n], Z) <= 1e-15
+            assert abs(aux["a00"][0] - a00) <= 1e-12 and abs(aux["a10"][0] - a10) <= 1e-12
+        else:
+            assert int(f.get_llt_fail()[0]) == o.llt_fail(), "LLT failure column differs at step %d" % t
+    f.close()
+    return worst, o
+
+
+def test_cfg1_single_ekf_1000_steps(aslam, orc):
+    worst, o = _run_single(aslam, orc, "ekf", 1000)
+    assert o.N == 19  # all 8 cylinders of landmarks.yaml mapped
+    print("cfg1 worst relerr", worst)
+
+
+def test_ekf_reference_cap_rejects_batch(aslam, orc):
+    """16 landmarks against the reference's cap of 30 (config.h:45): the whole promotion batch is
+    dropped (ekf.cpp:263-268) and never retried."""
+    worst, o = _run_single(aslam, orc, "ekf", 60, lm=aslam.map_cfg3())
+    assert o.N == 3 and o.cap_rejected()
+
+
+def test_ekf_gated_before_first_observation(aslam):
+    f = aslam.BatchedFilter("ekf", 1, 0)
+    with pytest.raises(aslam.capi.AslamError) as e:
+        f.step([0.0], [0.0], [0.0], [0.0], [0.0], [1.0])
+    assert e.value.status == aslam.capi.ASLAM_ERR_NOT_READY
+    f.close()
+
+
+def test_ekf_empty_and_ragged_observations(aslam, orc):
+    """Filters of one batch with 0, 3 and 8 observations; empty messages leave the map untouched."""
+    lmx, lmy = aslam.map_cfg1()
+    steps, B = 40, 3
+    rp = aslam.Replay(lmx, lmy, B, steps, seed0=7)
+    counts = [0, 3, 8]
+    f = aslam.BatchedFilter("ekf", B, 0)
+    os_ = [orc.Filter("ekf") for _ in range(B)]
+    for t in range(steps):
+        rr = [rp.range[t, b, :counts[b]] for b in range(B)]
+        bb = [rp.bearing[t, b, :counts[b]] for b in range(B)]
+        off = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+        f.set_observations(np.concatenate(rr), np.concatenate(bb), off)
+        f.step(rp.x[t], rp.y[t], rp.yaw[t], rp.vx[t], rp.az[t], rp.dt[t])
+        for b in range(B):
+            os_[b].set_observations(rr[b], bb[b])
+            os_[b].step(rp.x[t, b], rp.y[t, b], rp.yaw[t, b], rp.vx[t, b], rp.az[t, b], rp.dt[t, b])
+    s = f.get_state()
+    for b in range(B):
+        X, Z, P = os_[b].state()
+        n = os_[b].N
+        assert int(s["N"][b]) == n == 3 + 2 * counts[b]
+        assert relerr(s["X"][b, :n], X) <= TOL_F64 and relerr(s["P"][b, :n, :n], P) <= TOL_F64
+        assert np.array_equal(s["assoc"][off[b]:off[b + 1]], os_[b].assoc())
+    f.close()
+
+
+def test_cfg3_batched_ekf_subset(aslam, orc):
+    """config 3 at a size the oracle finishes in seconds: 256 filters x 16 landmarks x 150 steps,
+    per-filter seeds 0x5EED0000 + id, replayed from host buffers in ONE launch (covariance stays
+    on-chip between steps)."""
+    lmx, lmy = aslam.map_cfg3()
+    B, T, L = 256, 150, 16
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=0x5EED0000)
+    f = aslam.BatchedFilter("ekf", B, 0, max_state_dim=64)
+    f.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+    s = f.get_state()
+    cfg = orc.default_config(max_state_dim=64)
+    sec, X, P, N = orc.run_batch("ekf", cfg, B, T, L, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range,
+                                 rp.bearing, 0, f.ld)
+    assert np.array_equal(s["N"], N) and np.all(N == 35)
+    assert not np.any(s["status"])
+    ex = [relerr(s["X"][b], X[b]) for b in range(B)]
+    ep = [relerr(s["P"][b], P[b]) for b in range(B)]
+    print("cfg3 subset worst relerr X %.3e P %.3e" % (max(ex), max(ep)))
+    assert max(ex) <= TOL_F64 and max(ep) <= TOL_F64
+    f.close()
+
+
+def test_batched_split_launch_equals_one_launch(aslam):
+    """Replaying 40 steps as 1 launch or as 4 x 10 gives bit-identical state (idempotent staging)."""
+    lmx, lmy = aslam.map_cfg3()
+    B, T, L = 64, 40, 16
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=99)
+    a = aslam.BatchedFilter("ekf", B, 0, max_state_dim=64)
+    b = aslam.BatchedFilter("ekf", B, 0, max_state_dim=64)
+    a.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+    for k in range(0, T, 10):
+        sl = slice(k, k + 10)
+        b.run_host(10, rp.x[sl], rp.y[sl], rp.yaw[sl], rp.vx[sl], rp.az[sl], rp.dt[sl], rp.range[sl],
+                   rp.bearing[sl], L)
+        b.sync()
+    sa, sb = a.get_state(), b.get_state()
+    assert np.array_equal(sa["X"], sb["X"]) and np.array_equal(sa["P"], sb["P"]) and np.array_equal(sa["N"], sb["N"])
+    a.close(); b.close()
+
+
+def test_single_filter_class_mirror(aslam, orc):
+    """The reference-named class: cbSensorLandmark / cbOdom, Landmarks out (common.h:93-108)."""
+    lmx, lmy = aslam.map_cfg1()
+    rp = aslam.Replay(lmx, lmy, 1, 30, seed0=3)
+    e = aslam.EKFSlam()
+    o = orc.Filter("ekf")
+    assert e.cbOdom(aslam.Odometry()) is None  # gated until the first sensor message (ekf.cpp:76)
+    for t in range(30):
+        e.cbSensorLandmark(rp.range[t, 0].astype(np.float64), rp.bearing[t, 0].astype(np.float64))
+        yaw = float(rp.yaw[t, 0])
+        msg = aslam.Odometry(rp.x[t, 0], rp.y[t, 0], np.cos(yaw / 2), 0.0, 0.0, np.sin(yaw / 2), rp.vx[t, 0], rp.az[t, 0])
+        out = e.cbOdom(msg, 1.0)
+        o.set_observations(rp.range[t, 0], rp.bearing[t, 0])
+        yaw32 = aslam.capi.lib().aslam_quat2euler(msg.qw, 0.0, 0.0, msg.qz)
+        o.step(msg.x, msg.y, yaw32, msg.vx, msg.az, 1.0)
+    X, Z, P = o.state()
+    lx, ly = out
+    assert lx.size == (o.N - 3) // 2 == 8
+    assert relerr(lx, X[3::2]) <= TOL_F64 and relerr(ly, X[4::2]) <= TOL_F64
+    e.close()
