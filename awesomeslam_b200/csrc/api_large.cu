@@ -1,0 +1,247 @@
+// C-ABI layer of the large-map filters (include/aslam_c.h, aslam_large_*): handle lifetime,
+// device memory, state import/export and the per-step call sequence. All arithmetic is in
+// ekf_large.cu / ukf_large.cu.
+#include <cuda_runtime.h>
+
+#include <cstdlib>
+#include <new>
+#include <vector>
+
+#include "large.hpp"
+
+namespace aslam {
+aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m);
+aslam_status large_ekf_phase2(aslam_large* h);
+aslam_status large_ukf_create(aslam_large* h);
+void large_ukf_destroy(aslam_large* h);
+aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m);
+aslam_status large_ukf_load_z(aslam_large* h, const double* Z);
+aslam_status large_ukf_status(aslam_large* h, uint32_t* status, int32_t* llt_fail);
+}  // namespace aslam
+
+using namespace aslam;
+
+namespace {
+
+aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_t rb, uint32_t re, int32_t device,
+                          aslam_large** out) {
+    if (!out) return ASLAM_ERR_ARG;
+    *out = nullptr;
+    if (n < 5 || (n & 1u) == 0 || rb >= re || re > n || (rb != 0 && rb < 3)) {
+        set_error("large create: n must be odd >= 5 and 0 <= row_begin < row_end <= n (a shard that starts after row 0 "
+                  "starts at row >= 3)");
+        return ASLAM_ERR_ARG;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("large create: no CUDA device (this library has no CPU path)");
+        return ASLAM_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) {
+        set_error("large create: device index out of range");
+        return ASLAM_ERR_ARG;
+    }
+    ASLAM_CUDA(cudaSetDevice(device));
+    aslam_large* h = new (std::nothrow) aslam_large;
+    if (!h) return ASLAM_ERR_ARG;
+    h->kind = kind;
+    if (cfg)
+        h->cfg = *cfg;
+    else
+        aslam_config_default(&h->cfg);
+    h->device = device;
+    h->n = n;
+    h->row_begin = rb;
+    h->row_end = re;
+    h->ldp = (((size_t)(re - rb) + 15) / 16) * 16;
+    aslam_status rc = ASLAM_OK;
+    auto A = [&](void** p, size_t bytes) {
+        if (rc == ASLAM_OK && !cuda_ok(cudaMalloc(p, bytes), "cudaMalloc")) rc = ASLAM_ERR_CUDA;
+    };
+    if (!cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+    A((void**)&h->P, (size_t)n * h->ldp * sizeof(double));
+    A((void**)&h->X, (size_t)n * sizeof(double));
+    A((void**)&h->A, 2 * sizeof(double));
+    A((void**)&h->ctx, sizeof(LargeCtx));
+    A((void**)&h->d_obs, 2 * ASLAM_MAX_OBS * sizeof(float));
+    if (kind == ASLAM_KIND_EKF) {
+        A((void**)&h->exch, (size_t)2 * LARGE_QMAX * n * sizeof(double));
+        A((void**)&h->hp, (size_t)n * 132 * sizeof(double));
+        A((void**)&h->K, (size_t)132 * n * sizeof(double));
+    }
+    if (rc == ASLAM_OK && !cuda_ok(cudaEventCreate(&h->ev0), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK && !cuda_ok(cudaEventCreate(&h->ev1), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK) {
+        const double a[2] = {1.0, 0.0};  // A = I (ekf.cpp:60)
+        if (!cuda_ok(cudaMemcpyAsync(h->A, a, sizeof(a), cudaMemcpyHostToDevice, h->stream), "init A")) rc = ASLAM_ERR_CUDA;
+        if (!cuda_ok(cudaMemsetAsync(h->P, 0, (size_t)n * h->ldp * sizeof(double), h->stream), "init P")) rc = ASLAM_ERR_CUDA;
+        if (!cuda_ok(cudaMemsetAsync(h->X, 0, (size_t)n * sizeof(double), h->stream), "init X")) rc = ASLAM_ERR_CUDA;
+        if (!cuda_ok(cudaMemsetAsync(h->ctx, 0, sizeof(LargeCtx), h->stream), "init ctx")) rc = ASLAM_ERR_CUDA;
+        if (!cuda_ok(cudaStreamSynchronize(h->stream), "init sync")) rc = ASLAM_ERR_CUDA;
+    }
+    if (rc == ASLAM_OK && kind == ASLAM_KIND_UKF) rc = large_ukf_create(h);
+    if (rc != ASLAM_OK) {
+        aslam_large_destroy(h);
+        return rc;
+    }
+    h->timed = std::getenv("ASLAM_LARGE_NO_TIMING") == nullptr;
+    *out = h;
+    return ASLAM_OK;
+}
+
+aslam_status stage_obs(aslam_large* h, const float* range, const float* bearing, uint32_t m) {
+    if (m > ASLAM_MAX_OBS) {
+        set_error("large step: more than ASLAM_MAX_OBS observations in one message");
+        return ASLAM_ERR_ARG;
+    }
+    if (m && (!range || !bearing)) return ASLAM_ERR_ARG;
+    if (m) {
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs, range, m * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs + ASLAM_MAX_OBS, bearing, m * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    }
+    h->m_last = m;
+    return ASLAM_OK;
+}
+
+aslam_status fetch_assoc(aslam_large* h, int32_t* assoc_out) {
+    if (!assoc_out || !h->m_last) return ASLAM_OK;
+    ASLAM_CUDA(cudaMemcpyAsync(assoc_out, (const char*)h->ctx + offsetof(LargeCtx, assoc), h->m_last * sizeof(int32_t),
+                               cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+aslam_status aslam_large_ekf_create(const aslam_config* cfg, uint32_t n, uint32_t row_begin, uint32_t row_end,
+                                    int32_t device, aslam_large** out) {
+    return create_large(ASLAM_KIND_EKF, cfg, n, row_begin, row_end, device, out);
+}
+
+aslam_status aslam_large_ukf_create(const aslam_config* cfg, uint32_t n, int32_t device, aslam_large** out) {
+    return create_large(ASLAM_KIND_UKF, cfg, n, 0, n, device, out);
+}
+
+aslam_status aslam_large_destroy(aslam_large* h) {
+    if (!h) return ASLAM_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->ukf) large_ukf_destroy(h);
+    void* ptrs[] = {h->P, h->X, h->A, h->ctx, h->d_obs, h->exch, h->hp, h->K};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_sync(aslam_large* h) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+void* aslam_large_stream(aslam_large* h) { return h ? (void*)h->stream : nullptr; }
+uint64_t aslam_large_launch_count(aslam_large* h) { return h ? h->launches : 0; }
+
+aslam_status aslam_large_load_state(aslam_large* h, const double* X, const double* Z, const double* P, size_t ldp) {
+    if (!h || !X || !P || ldp < h->n) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t n = h->n, rows = h->row_end - h->row_begin;
+    ASLAM_CUDA(cudaMemcpyAsync(h->X, X, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    ASLAM_CUDA(cudaMemcpy2DAsync(h->P, h->ldp * sizeof(double), P + h->row_begin, ldp * sizeof(double),
+                                 rows * sizeof(double), n, cudaMemcpyHostToDevice, h->stream));
+    if (h->kind == ASLAM_KIND_UKF) {
+        aslam_status rc = large_ukf_load_z(h, Z);
+        if (rc != ASLAM_OK) return rc;
+    }
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_get_state(aslam_large* h, double* X, double* P, size_t ldp) {
+    if (!h || (P && ldp < (size_t)(h->row_end - h->row_begin))) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t n = h->n, rows = h->row_end - h->row_begin;
+    if (X) ASLAM_CUDA(cudaMemcpyAsync(X, h->X, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    // P receives this handle's rows only: column j at P + j*ldp, rows row_begin..row_end-1
+    if (P)
+        ASLAM_CUDA(cudaMemcpy2DAsync(P, ldp * sizeof(double), h->P, h->ldp * sizeof(double), rows * sizeof(double), n,
+                                     cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                              const float* range, const float* bearing, uint32_t m, int32_t* assoc_out) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    aslam_status rc = stage_obs(h, range, bearing, m);
+    if (rc != ASLAM_OK) return rc;
+    if (h->kind == ASLAM_KIND_UKF) {
+        rc = large_ukf_step(h, x, y, yaw, vx, az, dt, m);
+        if (rc != ASLAM_OK) return rc;
+        return fetch_assoc(h, assoc_out);
+    }
+    if (h->row_begin != 0 || h->row_end != h->n) {
+        set_error("large step: a sharded handle must use step_phase1 / exchange / step_phase2");
+        return ASLAM_ERR_UNSUPPORTED;
+    }
+    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m);
+    if (rc != ASLAM_OK) return rc;
+    rc = large_ekf_phase2(h);
+    if (rc != ASLAM_OK) return rc;
+    return fetch_assoc(h, assoc_out);
+}
+
+aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                                     const float* range, const float* bearing, uint32_t m, uint32_t* q_out) {
+    if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    aslam_status rc = stage_obs(h, range, bearing, m);
+    if (rc != ASLAM_OK) return rc;
+    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m);
+    if (q_out) *q_out = h->q_host;
+    return rc;
+}
+
+aslam_status aslam_large_exchange_buffer(aslam_large* h, double** d_buf, size_t* count) {
+    if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
+    if (d_buf) *d_buf = h->exch;
+    if (count) *count = (size_t)2 * h->q_host * h->n;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out) {
+    if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    aslam_status rc = large_ekf_phase2(h);
+    if (rc != ASLAM_OK) return rc;
+    return fetch_assoc(h, assoc_out);
+}
+
+aslam_status aslam_large_last_kernel_ms(aslam_large* h, float* ms) {
+    if (!h || !ms || !h->timed) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaEventSynchronize(h->ev1));
+    ASLAM_CUDA(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_status(aslam_large* h, uint32_t* status, int32_t* llt_fail) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    if (h->kind == ASLAM_KIND_UKF) return large_ukf_status(h, status, llt_fail);
+    if (status) {
+        ASLAM_CUDA(cudaMemcpyAsync(status, (const char*)h->ctx + offsetof(LargeCtx, status), sizeof(uint32_t),
+                                   cudaMemcpyDeviceToHost, h->stream));
+        ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    if (llt_fail) *llt_fail = -1;
+    return ASLAM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,499 @@
+// Large-map EKF-SLAM step (kernels K3-K5): one filter whose covariance
+// P (n x n FP64, n = 3 + 2 L) lives in HBM. Same formulas as EKFSlam::slam (src/ekf/ekf.cpp:293-311)
+// and updateZandA (ekf.cpp:137-213), with H restricted to the rows in use this step -- the three
+// odometry rows and the two rows of every landmark observed in THIS message (row-subset joint
+// update; with every landmark observed it is ekf.cpp:300-310 verbatim):
+//     S = H_o P H_o' + R_o (q x q),  K = P H_o' S^-1 (n x q),  X += K y,  P -= K (H_o P)
+// A = I except A(0,0), A(1,0) (ekf.cpp:210-211) and H_o has <= 5 non-zeros per row, so everything
+// but the last product is O(q n); the last one streams P once: read + write 2*8*n^2 bytes.
+//
+// Kernels, in launch order
+//   large_front_kernel    1 CTA   association (float math, first-minimum ties), pose predict, A, H_o, y
+//   large_predict_kernel  n thr   P = A P A' + Q on rows/cols 0,1 (ekf.cpp:297)
+//   large_gather_kernel   n thr   raw rows rows[k] of P and the local slice of P H_o'  -> exchange buffer
+//   (sharded: the caller sums the exchange buffers of all ranks; every element has one owner)
+//   large_gain_kernel             S, S^-1 (per CTA, in smem), H_o P, K, X += K y
+//   large_update_kernel           P_local -= K_local (H_o P): the HBM-bound streaming kernel
+#include <cuda_runtime.h>
+
+#include "device_math.cuh"
+#include "large.hpp"
+
+namespace aslam {
+
+namespace {
+
+__device__ __forceinline__ unsigned long long umin64(unsigned long long a, unsigned long long b) {
+    return a < b ? a : b;
+}
+
+// ------------------------------------------------------------------------------------------
+// Front: ekf.cpp:139-187 (association against the supplied map; growth is outside the
+// large-map contract), :206-212 (A), :295-296 (pose predict), :117-134 (H rows), :302-307 (y).
+// ------------------------------------------------------------------------------------------
+struct FrontArgs {
+    double ox, oy, vx, az;
+    float yaw, dt;
+    uint32_t m;
+    uint32_t q_ub;  // 3 + 2 m: rows the exchange / gain buffers are laid out for
+    float pi, thresh;
+    double kr_pose, kr_lm;
+};
+
+__global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t n, double* X, double* A,
+                                                          const float* obs, LargeCtx* ctx) {
+    __shared__ unsigned long long red[32];
+    __shared__ float s_nb[ASLAM_MAX_OBS];
+    __shared__ int s_corr[ASLAM_MAX_OBS];
+    __shared__ float s_mind[ASLAM_MAX_OBS];
+    const int tid = threadIdx.x;
+    const uint32_t L = (n - 3) / 2;
+    const double z0 = a.ox, z1 = a.oy, z2 = (double)a.yaw;
+    for (uint32_t o = 0; o < a.m; ++o) {
+        const float r = obs[o];
+        const float b = normalize_angle(obs[ASLAM_MAX_OBS + o], a.pi);  // ekf.cpp:150
+        const float2 pt = to_point(r, b, z0, z1, z2);                   // structures.h:104-111
+        unsigned long long best = ~0ull;
+        for (uint32_t l = tid; l < L; l += blockDim.x) {
+            const float d = euler_distance(pt.x, pt.y, (float)X[3 + 2 * l], (float)X[4 + 2 * l]);
+            // d >= 0: its bit pattern orders like the value; the low word breaks ties toward the
+            // lowest landmark, which is what the strict `<` of ekf.cpp:168 keeps
+            const unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | l;
+            best = umin64(best, key);
+        }
+        for (int off = 16; off; off >>= 1) best = umin64(best, __shfl_xor_sync(0xffffffffu, best, off));
+        if ((tid & 31) == 0) red[tid >> 5] = best;
+        __syncthreads();
+        if (tid < 32) {
+            unsigned long long v = tid < (int)(blockDim.x >> 5) ? red[tid] : ~0ull;
+            for (int off = 16; off; off >>= 1) v = umin64(v, __shfl_xor_sync(0xffffffffu, v, off));
+            if (tid == 0) {
+                s_nb[o] = b;
+                s_corr[o] = (int)(v & 0xffffffffu) * 2;  // corr_id counts state entries (ekf.cpp:170)
+                s_mind[o] = __uint_as_float((unsigned)(v >> 32));
+            }
+        }
+        __syncthreads();
+    }
+    if (tid != 0) return;
+
+    // ---- sequential part: which landmark keeps which observation (later messages overwrite Z)
+    int lm[ASLAM_MAX_OBS], ob[ASLAM_MAX_OBS];
+    int cnt = 0;
+    for (uint32_t o = 0; o < a.m; ++o) {
+        if (L > 0 && s_mind[o] < a.thresh) {  // ekf.cpp:175
+            ctx->assoc[o] = s_corr[o];
+            int k = 0;
+            while (k < cnt && lm[k] != s_corr[o]) ++k;
+            if (k == cnt) {
+                lm[cnt] = s_corr[o];
+                ob[cnt] = (int)o;
+                ++cnt;
+            } else {
+                ob[k] = (int)o;
+            }
+        } else {
+            ctx->assoc[o] = -1;
+        }
+    }
+    for (int i = 1; i < cnt; ++i) {  // ascending landmark order, as the oracle walks the map
+        const int l = lm[i], o = ob[i];
+        int k = i - 1;
+        while (k >= 0 && lm[k] > l) {
+            lm[k + 1] = lm[k];
+            ob[k + 1] = ob[k];
+            --k;
+        }
+        lm[k + 1] = l;
+        ob[k + 1] = o;
+    }
+    // ---- A (ekf.cpp:206-212) and the pose predict (ekf.cpp:295-296)
+    double a00 = A[0], a10 = A[1];
+    motion_jacobian(a.vx, a.az, a.dt, z2, a00, a10);
+    A[0] = a00;
+    A[1] = a10;
+    double x = X[0], y = X[1], th = X[2];
+    motion_model(x, y, th, (float)a.vx, (float)a.az, a.dt);
+    th = (double)normalize_angle((float)th, a.pi);
+    X[0] = x;
+    X[1] = y;
+    X[2] = th;
+    // ---- rows of H in use
+    const int q = 3 + 2 * cnt;
+    ctx->q = q;
+    for (int k = 0; k < 3; ++k) {
+        ctx->rows[k] = k;
+        ctx->hnnz[k] = 1;
+        ctx->hcol[k][0] = k;
+        ctx->hk[k][0] = k;
+        ctx->hval[k][0] = 1.0;
+        ctx->rdiag[k] = a.kr_pose;
+    }
+    ctx->y[0] = a.ox - x;
+    ctx->y[1] = a.oy - y;
+    ctx->y[2] = (double)normalize_angle((float)(z2 - th), a.pi);
+    for (int c = 0; c < cnt; ++c) {
+        const int i = lm[c];
+        const double lx = X[3 + i], ly = X[4 + i];
+        const HEntries h = jacobian_entries(x, y, lx, ly);
+        const int kr = 3 + 2 * c, kb = kr + 1;
+        ctx->rows[kr] = 3 + i;
+        ctx->rows[kb] = 4 + i;
+        ctx->hnnz[kr] = 4;
+        ctx->hcol[kr][0] = 0;      ctx->hk[kr][0] = 0;   ctx->hval[kr][0] = h.a;
+        ctx->hcol[kr][1] = 1;      ctx->hk[kr][1] = 1;   ctx->hval[kr][1] = h.c;
+        ctx->hcol[kr][2] = 3 + i;  ctx->hk[kr][2] = kr;  ctx->hval[kr][2] = -h.a;
+        ctx->hcol[kr][3] = 4 + i;  ctx->hk[kr][3] = kb;  ctx->hval[kr][3] = -h.c;
+        ctx->hnnz[kb] = 5;
+        ctx->hcol[kb][0] = 0;      ctx->hk[kb][0] = 0;   ctx->hval[kb][0] = h.b;
+        ctx->hcol[kb][1] = 1;      ctx->hk[kb][1] = 1;   ctx->hval[kb][1] = h.d;
+        ctx->hcol[kb][2] = 2;      ctx->hk[kb][2] = 2;   ctx->hval[kb][2] = -1.0;
+        ctx->hcol[kb][3] = 3 + i;  ctx->hk[kb][3] = kr;  ctx->hval[kb][3] = -h.b;
+        ctx->hcol[kb][4] = 4 + i;  ctx->hk[kb][4] = kb;  ctx->hval[kb][4] = -h.d;
+        ctx->rdiag[kr] = a.kr_lm;
+        ctx->rdiag[kb] = a.kr_lm;
+        double rg, br;
+        measure_landmark(x, y, th, lx, ly, rg, br);
+        ctx->y[kr] = (double)obs[ob[c]] - rg;                                          // Z - h(X)
+        ctx->y[kb] = (double)normalize_angle((float)((double)s_nb[ob[c]] - br), a.pi);  // ekf.cpp:306
+    }
+    for (int k = q; k < (int)a.q_ub; ++k) {  // unused rows: harmless identity padding
+        ctx->rows[k] = -1;
+        ctx->hnnz[k] = 0;
+        ctx->y[k] = 0.0;
+        ctx->rdiag[k] = 1.0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// P = A P A' + Q (ekf.cpp:297) with A = I + (a00-1) e0 e0' + a10 e1 e0'. (A P) changes rows 0,1;
+// (.) A' then changes columns 0,1. Thread t >= 2 owns P(0..1, t) and P(t, 0..1); thread 0 owns
+// the 2x2 corner, where the column pass reads the row pass's results, and the Q diagonal.
+// ------------------------------------------------------------------------------------------
+__global__ void large_predict_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp, double* P, const double* A,
+                                     double kq) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const double a00 = A[0], a10 = A[1];
+    const bool own01 = rb == 0;  // the shard with row 0 also has rows 1, 2
+    if (t >= 2) {
+        if (own01) {  // rows 0,1 of column t
+            double* c = P + (size_t)t * ldp;
+            const double p0 = c[0], p1 = c[1];
+            c[0] = a00 * p0;
+            c[1] = a10 * p0 + p1;
+        }
+        if (t >= rb && t < re) {  // row t of columns 0,1
+            const double p0 = P[t - rb], p1 = P[ldp + (t - rb)];
+            P[t - rb] = p0 * a00;
+            P[ldp + (t - rb)] = p0 * a10 + p1;
+        }
+        if (t == 2 && own01) P[2 * ldp + 2] += kq;
+    } else if (t == 0 && own01) {
+        double p00 = P[0], p10 = P[1], p01 = P[ldp], p11 = P[ldp + 1];
+        // rows: row0 *= a00; row1 = a10*row0 + row1 (old row0)
+        const double r00 = a00 * p00, r01 = a00 * p01;
+        const double r10 = a10 * p00 + p10, r11 = a10 * p01 + p11;
+        // cols: col0 *= a00; col1 = col0*a10 + col1
+        p00 = r00 * a00;
+        p01 = r00 * a10 + r01;
+        p10 = r10 * a00;
+        p11 = r10 * a10 + r11;
+        P[0] = p00 + kq;
+        P[1] = p10;
+        P[ldp] = p01;
+        P[ldp + 1] = p11 + kq;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Exchange buffer: E[k][j], k < q_ub: row rows[k] of P when this shard owns it (else 0);
+// E[q_ub + k][i]: (P H_o')[i][k] for the owned rows i (else 0). Sums follow the oracle's order.
+// ------------------------------------------------------------------------------------------
+__global__ void large_gather_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp, const double* P,
+                                    const LargeCtx* ctx, uint32_t q_ub, double* E) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int q = ctx->q;
+    const bool mine = t >= rb && t < re;
+    for (uint32_t k = 0; k < q_ub; ++k) {
+        double raw = 0.0, pht = 0.0;
+        if ((int)k < q) {
+            const uint32_t r = (uint32_t)ctx->rows[k];
+            if (r >= rb && r < re) raw = P[(size_t)t * ldp + (r - rb)];
+            if (mine) {
+                const int nnz = ctx->hnnz[k];
+                for (int e = 0; e < nnz; ++e) pht += P[(size_t)ctx->hcol[k][e] * ldp + (t - rb)] * ctx->hval[k][e];
+            }
+        }
+        E[(size_t)k * n + t] = raw;
+        E[(size_t)(q_ub + k) * n + t] = pht;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Gain. Every CTA rebuilds S = H_o P H_o' + R_o and inverts it in shared memory (Gauss-Jordan with
+// partial pivoting, in place; q <= 131), then produces its slice of H_o P (layout [j][QT], rows
+// >= q zero), of K = (P H_o') S^-1 (layout [QT][n]) and of X += K y.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) large_gain_kernel(uint32_t n, const LargeCtx* ctx, uint32_t q_ub,
+                                                        const double* E, uint32_t QT, double* hp, double* K,
+                                                        double* X) {
+    extern __shared__ double sm[];
+    const int q = ctx->q;
+    double* S = sm;  // q x q, row-major
+    __shared__ int piv[LARGE_QMAX];
+    __shared__ int s_p;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    // S(a,b) = sum_e (H_o P)[a][col_b[e]] * v_b[e] + R;  (H_o P)[a][j] = sum_e' v_a[e'] * row_{hk[a][e']}[j]
+    for (int idx = tid; idx < q * q; idx += nt) {
+        const int a = idx / q, b = idx % q;
+        double s = 0.0;
+        for (int e = 0; e < ctx->hnnz[b]; ++e) {
+            const int j = ctx->hcol[b][e];
+            double hpaj = 0.0;
+            for (int f = 0; f < ctx->hnnz[a]; ++f) hpaj += ctx->hval[a][f] * E[(size_t)ctx->hk[a][f] * n + j];
+            s += hpaj * ctx->hval[b][e];
+        }
+        S[idx] = s + (a == b ? ctx->rdiag[a] : 0.0);
+    }
+    __syncthreads();
+    for (int k = 0; k < q; ++k) {
+        if (tid == 0) {
+            int p = k;
+            double best = fabs(S[k * q + k]);
+            for (int i = k + 1; i < q; ++i) {
+                const double v = fabs(S[i * q + k]);
+                if (v > best) {
+                    best = v;
+                    p = i;
+                }
+            }
+            s_p = p;
+            piv[k] = p;
+        }
+        __syncthreads();
+        const int p = s_p;
+        if (p != k)
+            for (int j = tid; j < q; j += nt) {
+                const double t = S[k * q + j];
+                S[k * q + j] = S[p * q + j];
+                S[p * q + j] = t;
+            }
+        __syncthreads();
+        const double d = 1.0 / S[k * q + k];
+        __syncthreads();
+        for (int j = tid; j < q; j += nt) S[k * q + j] = (j == k ? 1.0 : S[k * q + j]) * d;
+        __syncthreads();
+        for (int idx = tid; idx < q * q; idx += nt) {
+            const int i = idx / q, j = idx % q;
+            if (i == k) continue;
+            const double f = S[i * q + k];
+            if (j == k) continue;
+            S[idx] = fma(-f, S[k * q + j], S[idx]);
+        }
+        __syncthreads();
+        for (int i = tid; i < q; i += nt)
+            if (i != k) S[i * q + k] = -S[i * q + k] * S[k * q + k];
+        __syncthreads();
+    }
+    for (int k = q - 1; k >= 0; --k) {  // undo the row swaps as column swaps
+        const int p = piv[k];
+        if (p != k)
+            for (int i = tid; i < q; i += nt) {
+                const double t = S[i * q + k];
+                S[i * q + k] = S[i * q + p];
+                S[i * q + p] = t;
+            }
+        __syncthreads();
+    }
+    // ---- slices
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    for (int k = 0; k < (int)QT; ++k) {  // H_o P column t
+        double s = 0.0;
+        if (k < q)
+            for (int e = 0; e < ctx->hnnz[k]; ++e) s += ctx->hval[k][e] * E[(size_t)ctx->hk[k][e] * n + t];
+        hp[(size_t)t * QT + k] = s;
+    }
+    double dx = 0.0;
+    for (int k = 0; k < (int)QT; ++k) {  // K row t
+        double s = 0.0;
+        if (k < q) {
+            for (int e = 0; e < q; ++e) s += E[(size_t)(q_ub + e) * n + t] * S[e * q + k];
+            dx += s * ctx->y[k];
+        }
+        K[(size_t)k * n + t] = s;
+    }
+    X[t] += dx;  // ekf.cpp:309
+}
+
+// ------------------------------------------------------------------------------------------
+// K5: P_local -= K_local (H_o P). Thread owns R consecutive rows; its R x Q slice of -K sits in
+// registers for the whole tile. A CTA (256 threads, 256 R rows) walks a range of columns; the
+// Q-vector (H_o P)[:, j] of each column is staged in shared memory and read as a broadcast.
+// Per column and thread: one 16-byte load, R*Q DFMA, one 16-byte store -- P is read once and
+// written once: 16 n^2 bytes per step against 2 q n^2 flop (HBM-bound for q <~ 40).
+// ------------------------------------------------------------------------------------------
+template <int R, int Q, int U>
+__global__ void __launch_bounds__(256) large_update_kernel(uint32_t n, uint32_t rb, uint32_t nrows, size_t ldp,
+                                                          double* __restrict__ P, const double* __restrict__ K,
+                                                          const double* __restrict__ hp, uint32_t cols_per_cta) {
+    constexpr int ROWS = 256 * R;
+    constexpr int CW = 64;  // columns staged per smem refill
+    __shared__ __align__(16) double s_hp[CW][Q];
+    const uint32_t rblk = blockIdx.y;
+    const uint32_t i0 = rblk * ROWS + threadIdx.x * R;  // local row
+    const uint32_t c_begin = blockIdx.x * cols_per_cta;
+    const uint32_t c_end = min(n, c_begin + cols_per_cta);
+    double nk[Q][R];
+#pragma unroll
+    for (int k = 0; k < Q; ++k)
+#pragma unroll
+        for (int r = 0; r < R; ++r) nk[k][r] = (i0 + r < nrows) ? -K[(size_t)k * n + rb + i0 + r] : 0.0;
+    const bool full = i0 + R <= nrows;
+    for (uint32_t c0 = c_begin; c0 < c_end; c0 += CW) {
+        const uint32_t cw = min((uint32_t)CW, c_end - c0);
+        __syncthreads();
+        {
+            const double* src = hp + (size_t)c0 * Q;
+            double* dst = &s_hp[0][0];
+            for (uint32_t i = threadIdx.x; i < cw * Q; i += 256) dst[i] = src[i];
+        }
+        __syncthreads();
+        if (i0 >= nrows) continue;
+        double* col = P + (size_t)c0 * ldp + i0;
+        uint32_t jj = 0;
+        if (full) {
+            for (; jj + U <= cw; jj += U) {
+                double v[U][R];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if constexpr (R == 2) {
+                        const double2 t = __ldcs(reinterpret_cast<const double2*>(col + (size_t)(jj + u) * ldp));
+                        v[u][0] = t.x;
+                        v[u][1] = t.y;
+                    } else {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) v[u][r] = __ldcs(col + (size_t)(jj + u) * ldp + r);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+#pragma unroll
+                    for (int k = 0; k < Q; k += 2) {
+                        const double2 h = *reinterpret_cast<const double2*>(&s_hp[jj + u][k]);
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            v[u][r] = fma(nk[k][r], h.x, v[u][r]);
+                            v[u][r] = fma(nk[k + 1][r], h.y, v[u][r]);
+                        }
+                    }
+                    if constexpr (R == 2) {
+                        __stcs(reinterpret_cast<double2*>(col + (size_t)(jj + u) * ldp), make_double2(v[u][0], v[u][1]));
+                    } else {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) __stcs(col + (size_t)(jj + u) * ldp + r, v[u][r]);
+                    }
+                }
+            }
+        }
+        for (; jj < cw; ++jj) {  // column tail and the ragged last rows
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (i0 + r >= nrows) continue;
+                double v = col[(size_t)jj * ldp + r];
+#pragma unroll
+                for (int k = 0; k < Q; ++k) v = fma(nk[k][r], s_hp[jj][k], v);
+                col[(size_t)jj * ldp + r] = v;
+            }
+        }
+    }
+}
+
+// Any q (up to LARGE_QMAX): K read from global (L2-resident), FP64-bound for large q anyway.
+__global__ void __launch_bounds__(256) large_update_generic_kernel(uint32_t n, uint32_t rb, uint32_t nrows,
+                                                                  size_t ldp, double* __restrict__ P,
+                                                                  const double* __restrict__ K,
+                                                                  const double* __restrict__ hp, uint32_t QT,
+                                                                  const LargeCtx* ctx) {
+    const int q = ctx->q;
+    const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+    const uint32_t j0 = blockIdx.y * 32;
+    if (i >= nrows) return;
+    for (uint32_t j = j0; j < min(n, j0 + 32); ++j) {
+        double v = P[(size_t)j * ldp + i];
+        for (int k = 0; k < q; ++k) v = fma(-K[(size_t)k * n + rb + i], hp[(size_t)j * QT + k], v);
+        P[(size_t)j * ldp + i] = v;
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------- host side
+uint32_t large_ekf_qt(uint32_t q_ub) { return q_ub <= 20 ? 20u : (q_ub <= 40 ? 40u : 132u); }
+
+aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                              uint32_t m) {
+    FrontArgs a;
+    a.ox = x; a.oy = y; a.vx = vx; a.az = az; a.yaw = yaw; a.dt = dt;
+    a.m = m;
+    a.q_ub = 3 + 2 * m;
+    a.pi = h->cfg.pi;
+    a.thresh = h->cfg.min_dist_thresh;
+    a.kr_pose = (double)h->cfg.ekf_kr;
+    a.kr_lm = (double)h->cfg.ukf_kr;  // ekf.cpp:278 (UKF constant, as written)
+    const uint32_t n = h->n, nb = (n + 255) / 256;
+    large_front_kernel<<<1, 1024, 0, h->stream>>>(a, n, h->X, h->A, h->d_obs, h->ctx);
+    large_predict_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A,
+                                                    (double)h->cfg.ekf_kq);
+    large_gather_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub, h->exch);
+    ASLAM_CUDA(cudaGetLastError());
+    h->launches += 3;
+    h->q_host = a.q_ub;
+    return ASLAM_OK;
+}
+
+aslam_status large_ekf_phase2(aslam_large* h) {
+    const uint32_t n = h->n, nb = (n + 255) / 256, q_ub = h->q_host;
+    const uint32_t QT = large_ekf_qt(q_ub);
+    const size_t smem = (size_t)q_ub * q_ub * sizeof(double);
+    static size_t smem_set = 0;
+    if (smem > 48 * 1024 && smem > smem_set) {
+        ASLAM_CUDA(cudaFuncSetAttribute(large_gain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set = smem;
+    }
+    large_gain_kernel<<<nb, 256, smem, h->stream>>>(n, h->ctx, q_ub, h->exch, QT, h->hp, h->K, h->X);
+    const uint32_t nrows = h->row_end - h->row_begin;
+    if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
+    if (QT == 20 || QT == 40) {
+        // grid: (column ranges) x (row blocks); 2 CTAs per SM, sized so full row blocks fill whole waves
+        const uint32_t rows_per_cta = QT == 20 ? 512u : 256u;
+        const uint32_t rblocks = (nrows + rows_per_cta - 1) / rows_per_cta;
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+        const uint32_t target = (uint32_t)sms * 2 * 4;  // about 4 waves of 2 CTAs/SM
+        uint32_t cx = (target + rblocks - 1) / rblocks;
+        if (cx < 1) cx = 1;
+        uint32_t cols_per_cta = (n + cx - 1) / cx;
+        cols_per_cta = ((cols_per_cta + 63) / 64) * 64;
+        cx = (n + cols_per_cta - 1) / cols_per_cta;
+        dim3 grid(cx, rblocks);
+        if (QT == 20)
+            large_update_kernel<2, 20, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp,
+                                                                      cols_per_cta);
+        else
+            large_update_kernel<1, 40, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp,
+                                                                      cols_per_cta);
+    } else {
+        dim3 grid((nrows + 255) / 256, (n + 31) / 32);
+        large_update_generic_kernel<<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp, QT,
+                                                               h->ctx);
+    }
+    if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, h->stream));
+    ASLAM_CUDA(cudaGetLastError());
+    h->launches += 2;
+    return ASLAM_OK;
+}
+
+}  // namespace aslam

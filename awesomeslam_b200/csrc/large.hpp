@@ -1,0 +1,52 @@
+// Large-map filter (one filter, thousands of landmarks): shared definitions of the C-ABI
+// handle and the per-step context that the small kernels hand to the streaming kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "internal.hpp"
+
+namespace aslam {
+
+constexpr int LARGE_QMAX = 3 + 2 * (int)ASLAM_MAX_OBS;  // rows of H in use: pose + 2 per observed landmark
+
+// Written by large_front_kernel each step, read by the later kernels of the step.
+struct LargeCtx {
+    int32_t q;                      // H rows in use this step
+    int32_t rows[LARGE_QMAX];       // state index of each row (0,1,2, then 3+2l, 4+2l ascending l)
+    int32_t hnnz[LARGE_QMAX];       // non-zeros of the row (1 pose, 4 range, 5 bearing: ekf.cpp:124-132)
+    int32_t hcol[LARGE_QMAX][5];    // their state columns ...
+    int32_t hk[LARGE_QMAX][5];      // ... and the H-row index k with rows[k] == that column
+    double hval[LARGE_QMAX][5];
+    double y[LARGE_QMAX];           // innovation, theta/bearing rows wrapped (ekf.cpp:302-307)
+    double rdiag[LARGE_QMAX];       // diagonal of R for these rows
+    int32_t assoc[ASLAM_MAX_OBS];
+    uint32_t status;
+};
+
+}  // namespace aslam
+
+struct aslam_large {
+    int kind = 0;
+    aslam_config cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    uint32_t n = 0;                  // state dimension 3 + 2 L
+    uint32_t row_begin = 0, row_end = 0;
+    size_t ldp = 0;                  // leading dimension of the local column-major P (rows, padded to 16)
+    double* P = nullptr;             // [n][ldp]: column j at P + j*ldp holds rows row_begin..row_end-1
+    double* X = nullptr;             // [n]
+    double* A = nullptr;             // [2]: A(0,0), A(1,0) (ekf.cpp:210-211)
+    aslam::LargeCtx* ctx = nullptr;
+    float* d_obs = nullptr;          // [2][ASLAM_MAX_OBS] range, bearing
+    double* exch = nullptr;          // [2*LARGE_QMAX][n] raw rows of P, then P H^T slices
+    double* hp = nullptr;            // [n][QP]   H P, k contiguous per column
+    double* K = nullptr;             // [QP][n]   gain, row k contiguous
+    uint32_t q_host = 0;             // rows in use of the step in flight (after phase1)
+    uint32_t m_last = 0;
+    uint64_t launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the streaming update kernel of the last step
+    bool timed = false;
+    // UKF large-map state lives in ukf_large.cu's own struct, reached through `ukf`
+    void* ukf = nullptr;
+};

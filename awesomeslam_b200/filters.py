@@ -244,3 +244,108 @@ class UKFSlam(_SingleFilter):
 
     def llt_fail(self):
         return int(self._f.get_llt_fail()[0])
+
+
+class LargeFilter:
+    """One large-map filter (aslam_large handle): n = 3 + 2 L, P is n x n FP64 in HBM.
+
+    EKF: rows [row_begin, row_end) of P live on this handle's GPU (a full handle has 0, n).
+    """
+
+    def __init__(self, kind, n, device=0, row_begin=0, row_end=None, config=None, **cfg_overrides):
+        self._h = C.c_void_p()
+        self._lib = capi.lib()
+        self.config = config if config is not None else capi.default_config(**cfg_overrides)
+        self.kind, self.n, self.device = kind, int(n), device
+        self.row_begin = int(row_begin)
+        self.row_end = int(n if row_end is None else row_end)
+        if kind == "ekf":
+            capi.check(self._lib.aslam_large_ekf_create(C.byref(self.config), self.n, self.row_begin, self.row_end,
+                                                        device, C.byref(self._h)))
+        else:
+            capi.check(self._lib.aslam_large_ukf_create(C.byref(self.config), self.n, device, C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.aslam_large_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return self._lib.aslam_large_stream(self._h)
+
+    def sync(self):
+        capi.check(self._lib.aslam_large_sync(self._h))
+
+    def load_state(self, X, P, Z=None):
+        """X [n]; P [n, n] indexed P[i, j] (any layout: it is sent column-major); Z [n] (UKF)."""
+        X = capi.as_np(X, np.float64)
+        Pc = np.ascontiguousarray(np.asarray(P, np.float64).T)  # Pc[j, i] = P[i, j]: column-major
+        Zc = None if Z is None else capi.as_np(Z, np.float64)
+        capi.check(self._lib.aslam_large_load_state(self._h, capi.ptr(X), capi.ptr(Zc), capi.ptr(Pc), self.n))
+
+    def load_state_colmajor(self, X, Pc, Z=None):
+        """Pc: C array with Pc[j, i] = P[i, j] (no transpose copy)."""
+        X = capi.as_np(X, np.float64)
+        assert Pc.flags["C_CONTIGUOUS"] and Pc.dtype == np.float64
+        Zc = None if Z is None else capi.as_np(Z, np.float64)
+        capi.check(self._lib.aslam_large_load_state(self._h, capi.ptr(X), capi.ptr(Zc), capi.ptr(Pc), self.n))
+
+    def get_state(self, want_P=True):
+        """Returns X [n] and this handle's rows of P as an array [rows, n] (P[i - row_begin, j])."""
+        X = np.zeros(self.n, np.float64)
+        rows = self.row_end - self.row_begin
+        Pc = np.zeros((self.n, rows), np.float64) if want_P else None
+        capi.check(self._lib.aslam_large_get_state(self._h, capi.ptr(X), capi.ptr(Pc), rows))
+        return X, (Pc.T if want_P else None)
+
+    def step(self, x, y, yaw, vx, az, dt, rng, brg, want_assoc=True):
+        rng = capi.as_np(rng, np.float32)
+        brg = capi.as_np(brg, np.float32)
+        assoc = np.zeros(max(rng.size, 1), np.int32) if want_assoc else None
+        capi.check(self._lib.aslam_large_step(self._h, x, y, np.float32(yaw), vx, az, np.float32(dt), capi.ptr(rng),
+                                              capi.ptr(brg), rng.size, capi.ptr(assoc)))
+        return None if assoc is None else assoc[:rng.size]
+
+    # sharded EKF: phase1 -> (caller all-reduces exchange buffer) -> phase2
+    def step_phase1(self, x, y, yaw, vx, az, dt, rng, brg):
+        rng = capi.as_np(rng, np.float32)
+        brg = capi.as_np(brg, np.float32)
+        q = C.c_uint32()
+        capi.check(self._lib.aslam_large_step_phase1(self._h, x, y, np.float32(yaw), vx, az, np.float32(dt),
+                                                     capi.ptr(rng), capi.ptr(brg), rng.size, C.byref(q)))
+        self._m = rng.size
+        return int(q.value)
+
+    def exchange_buffer(self):
+        """(device pointer, count of doubles) of the buffer the ranks must sum."""
+        p = C.c_void_p()
+        cnt = C.c_size_t()
+        capi.check(self._lib.aslam_large_exchange_buffer(self._h, C.byref(p), C.byref(cnt)))
+        return int(p.value), int(cnt.value)
+
+    def step_phase2(self, want_assoc=True):
+        assoc = np.zeros(max(self._m, 1), np.int32) if want_assoc else None
+        capi.check(self._lib.aslam_large_step_phase2(self._h, capi.ptr(assoc)))
+        return None if assoc is None else assoc[:self._m]
+
+    def last_kernel_ms(self):
+        ms = C.c_float()
+        capi.check(self._lib.aslam_large_last_kernel_ms(self._h, C.byref(ms)))
+        return float(ms.value)
+
+    def status(self):
+        st = C.c_uint32()
+        fk = C.c_int32()
+        capi.check(self._lib.aslam_large_status(self._h, C.byref(st), C.byref(fk)))
+        return int(st.value), int(fk.value)
+
+    @property
+    def launch_count(self):
+        return int(self._lib.aslam_large_launch_count(self._h))

@@ -72,3 +72,47 @@ class Replay:
 
 SEED_CFG1 = 1
 SEED_CFG3 = 0x5EED0000
+
+
+def large_map_state(L_side, pitch=2.0, seed=4, pose=(0.0, 0.0, 0.0)):
+    """Initial state of the large-map configs: landmarks on an
+    L_side x L_side grid with `pitch` metres spacing centred on the origin (offset by half a pitch so
+    the robot is not on a landmark); X = truth + N(0, 0.05^2); P = 0.01 I + G G' with G n x 8 ~ N(0, 0.02^2),
+    pose block 1e-3 I. Returns (truth_x, truth_y, X, G, d) with P = diag(d) + G G' left implicit -- use
+    dense_P() to materialise it."""
+    rng = np.random.default_rng(seed)
+    L = L_side * L_side
+    n = 3 + 2 * L
+    gx, gy = np.meshgrid(np.arange(L_side), np.arange(L_side), indexing="ij")
+    tx = (gx.ravel() - (L_side - 1) / 2.0) * pitch + pitch / 2
+    ty = (gy.ravel() - (L_side - 1) / 2.0) * pitch + pitch / 2
+    X = np.zeros(n)
+    X[0:3] = pose
+    X[3::2] = tx + 0.05 * rng.standard_normal(L)
+    X[4::2] = ty + 0.05 * rng.standard_normal(L)
+    G = 0.02 * rng.standard_normal((n, 8))
+    G[:3] = 0.0
+    d = np.full(n, 0.01)
+    d[:3] = 1e-3
+    return tx, ty, X, G, d
+
+
+def dense_P(G, d):
+    P = G @ G.T
+    P[np.diag_indices_from(P)] += d
+    return P
+
+
+def large_observations(tx, ty, pose, m=8, seed=0, sigma_r=0.01, sigma_b=0.005):
+    """(range, bearing) float32 of the m landmarks nearest to `pose`, increasing bearing order."""
+    rng = np.random.default_rng(seed)
+    dx, dy = tx - pose[0], ty - pose[1]
+    dist = np.hypot(dx, dy)
+    idx = np.argsort(dist, kind="stable")[:m]
+    br = np.arctan2(dy[idx], dx[idx]) - pose[2]
+    br = (br + np.pi) % (2 * np.pi) - np.pi
+    order = np.argsort(br, kind="stable")
+    idx, br = idx[order], br[order]
+    r = dist[idx] + sigma_r * rng.standard_normal(m)
+    b = br + sigma_b * rng.standard_normal(m)
+    return r.astype(np.float32), b.astype(np.float32), idx

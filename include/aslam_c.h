@@ -185,17 +185,25 @@ aslam_status aslam_large_get_state(aslam_large* h, double* X, double* P, size_t 
 aslam_status aslam_large_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
                               const float* range, const float* bearing, uint32_t m, int32_t* assoc_out);
 /* Sharded EKF only (row_end - row_begin < n): the step is split around the one exchange.
- *   phase1: association, predict, local slices of P H^T and of the observed rows of P;
- *           writes this rank's contribution (q x n doubles, zeros outside owned rows /
- *           q = rows in use, <= 3 + 2*ASLAM_MAX_OBS) into the device buffer returned by
- *           aslam_large_exchange_buffer(); the caller sums the buffers of all ranks in place
- *           (NCCL all-reduce over NVLink; every element has exactly one non-zero owner).
+ *   phase1: association, predict, then this rank's contribution to the exchange buffer
+ *           [2q][n] doubles (q = 3 + 2m rows laid out, returned in q_out): rows 0..q-1 hold the
+ *           rows of P named by H (pose + observed landmarks) where this rank owns them, rows
+ *           q..2q-1 its slice of P H^T; everything it does not own is zero. The caller sums the
+ *           buffers (aslam_large_exchange_buffer) of all ranks in place -- NCCL all-reduce over
+ *           NVLink; every element has exactly one non-zero owner, so the sum is exact.
  *   phase2: S, K for the owned rows, X update, P_local -= K_local * (H P). */
 aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az,
                                      float dt, const float* range, const float* bearing, uint32_t m,
                                      uint32_t* q_out);
 aslam_status aslam_large_exchange_buffer(aslam_large* h, double** d_buf, size_t* count);
 aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out);
+/* Kernels this handle has launched so far. */
+uint64_t aslam_large_launch_count(aslam_large* h);
+/* Device time (CUDA events on the handle's stream) of the dominant kernel of the LAST step: the
+ * streaming covariance update (EKF) / the whole step's GEMM chain (UKF). Waits for that kernel. */
+aslam_status aslam_large_last_kernel_ms(aslam_large* h, float* ms);
+/* status bits of the filter (ASLAM_ST_*), and for the UKF the first failing LLT pivot or -1. */
+aslam_status aslam_large_status(aslam_large* h, uint32_t* status, int32_t* llt_fail);
 
 /* ---------------------------------------------------------------- synthetic replay ------- */
 /* Deterministic replay generator of SURVEY.md sec. 8d (host code, no GPU needed):

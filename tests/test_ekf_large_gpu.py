@@ -1,0 +1,140 @@
+"""Parity of the large-map EKF (row-subset joint update, streaming covariance kernel) through the
+C ABI against the CPU oracle. Tolerance: norm-wise relative error <= 1e-9 on X and P (FP64);
+association indices EQUAL."""
+import numpy as np
+import pytest
+
+from util import TOL_F64, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+def _trajectory(steps):
+    """A few odometry messages: stationary first, then the cfg arc (v=0.05, w=0.1, dt=1)."""
+    x = y = th = 0.0
+    out = []
+    for t in range(steps):
+        v, w = (0.0, 0.0) if t < 1 else (0.05, 0.1)
+        if w:
+            x += v / w * (np.sin(th + w) - np.sin(th))
+            y -= v / w * (np.cos(th + w) - np.cos(th))
+            th += w
+        out.append((x, y, th, v, w))
+    return out
+
+
+def _run_large(aslam, orc, L_side, m, steps, seed=4):
+    tx, ty, X0, G, d = aslam.large_map_state(L_side, seed=seed)
+    P0 = aslam.dense_P(G, d)  # exactly symmetric: row-major == column-major
+    n = X0.size
+    f = aslam.LargeFilter("ekf", n)
+    f.load_state_colmajor(X0, P0)
+    Xo, Po = X0.copy(), P0.copy()
+    cfg = orc.default_config()
+    a00, a10 = 1.0, 0.0
+    worst = [0.0, 0.0]
+    rs = np.random.default_rng(11)
+    for t, (px, py, pth, v, w) in enumerate(_trajectory(steps)):
+        rng, brg, idx = aslam.large_observations(tx, ty, (px, py, pth), m=m, seed=100 + t)
+        ox, oy = px + 0.01 * rs.standard_normal(), py + 0.01 * rs.standard_normal()
+        yaw = np.float32(pth + 0.01 * rs.standard_normal())
+        assoc = f.step(ox, oy, yaw, v, w, 1.0, rng, brg)
+        q, assoc_o, a00, a10 = orc.ekf_large_step(cfg, Xo, Po, a00, a10, ox, oy, yaw, v, w, 1.0, rng, brg)
+        assert np.array_equal(assoc, assoc_o), "association differs at step %d" % t
+        assert np.array_equal(assoc // 2, idx), "synthetic observations should hit their own landmarks"
+        X, P = f.get_state()
+        ex, ep = relerr(X, Xo), relerr(P, Po.T)  # Po is column-major: Po[j, i] = P[i, j]
+        worst = [max(worst[0], ex), max(worst[1], ep)]
+        assert ex <= TOL_F64 and ep <= TOL_F64, "step %d: relerr X %.3e P %.3e" % (t, ex, ep)
+    f.close()
+    return worst
+
+
+def test_large_ekf_small_map_q19(aslam, orc):
+    """n = 131 (8x8 landmarks), 8 observed per step -> q = 19: the register-tiled streaming kernel."""
+    print("worst", _run_large(aslam, orc, 8, 8, 6))
+
+
+def test_large_ekf_ragged_sizes(aslam, orc):
+    """n not a multiple of anything: 5x5 (n=53), 13x13 (n=341), 23x23 (n=1061); m = 0, 1, 3, 17, 40."""
+    print(_run_large(aslam, orc, 5, 3, 3))
+    print(_run_large(aslam, orc, 13, 17, 3))   # q = 37 -> the 1-row x 40 variant
+    print(_run_large(aslam, orc, 23, 40, 2))   # q = 83 -> generic variant
+    print(_run_large(aslam, orc, 13, 1, 2))
+    print(_run_large(aslam, orc, 5, 0, 2))     # no observation: odometry-only update, q = 3
+
+
+def test_large_ekf_all_observed_equals_verbatim_dense_slam(aslam, orc):
+    """With every landmark observed the row-subset update IS ekf.cpp:300-310: compare with the
+    oracle's verbatim dense EKFSlam::slam (7x7 landmarks, n = 101, q = 101)."""
+    tx, ty, X0, G, d = aslam.large_map_state(7, seed=5)
+    P0 = aslam.dense_P(G, d)
+    n = X0.size
+    f = aslam.LargeFilter("ekf", n)
+    f.load_state_colmajor(X0, P0)
+    o = orc.Filter("ekf", max_state_dim=n + 1)
+    o.load_state(X0, X0.copy(), P0)
+    for t, (px, py, pth, v, w) in enumerate(_trajectory(4)):
+        rng, brg, idx = aslam.large_observations(tx, ty, (px, py, pth), m=49, seed=7 + t)
+        assoc = f.step(px, py, np.float32(pth), v, w, 1.0, rng, brg)
+        o.set_observations(rng, brg)
+        o.step(px, py, np.float32(pth), v, w, 1.0)
+        assert np.array_equal(assoc, o.assoc())
+        X, P = f.get_state()
+        Xo, Zo, Po = o.state()
+        assert o.N == n
+        ex, ep = relerr(X, Xo), relerr(P, Po)
+        assert ex <= TOL_F64 and ep <= TOL_F64, "step %d: relerr X %.3e P %.3e" % (t, ex, ep)
+    f.close()
+
+
+class _DevArray:
+    """CUDA array interface view of a device pointer (so torch can wrap library-owned memory)."""
+
+    def __init__(self, ptr, count):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+def test_large_ekf_row_sharded_two_handles_one_gpu(aslam, orc):
+    """Row-block sharding emulated on ONE GPU: two handles own rows [0,k) and
+    [k,n); their exchange buffers are summed (the all-reduce) and phase 2 runs on each. Every
+    exchanged element has one owner, so the result is BIT-IDENTICAL to the unsharded handle."""
+    import torch
+    tx, ty, X0, G, d = aslam.large_map_state(9, seed=6)
+    P0 = aslam.dense_P(G, d)
+    n = X0.size
+    k = 70
+    full = aslam.LargeFilter("ekf", n)
+    lo = aslam.LargeFilter("ekf", n, row_begin=0, row_end=k)
+    hi = aslam.LargeFilter("ekf", n, row_begin=k, row_end=n)
+    for f in (full, lo, hi):
+        f.load_state_colmajor(X0, P0)
+    for t, (px, py, pth, v, w) in enumerate(_trajectory(4)):
+        rng, brg, idx = aslam.large_observations(tx, ty, (px, py, pth), m=8, seed=50 + t)
+        a_full = full.step(px, py, np.float32(pth), v, w, 1.0, rng, brg)
+        bufs = []
+        for f in (lo, hi):
+            f.step_phase1(px, py, np.float32(pth), v, w, 1.0, rng, brg)
+            f.sync()
+            p, c = f.exchange_buffer()
+            bufs.append(torch.as_tensor(_DevArray(p, c), device="cuda"))
+        total = bufs[0] + bufs[1]
+        bufs[0].copy_(total)
+        bufs[1].copy_(total)
+        torch.cuda.synchronize()
+        a_lo, a_hi = lo.step_phase2(), hi.step_phase2()
+        assert np.array_equal(a_full, a_lo) and np.array_equal(a_full, a_hi)
+        X, P = full.get_state()
+        Xl, Pl = lo.get_state()
+        Xh, Ph = hi.get_state()
+        assert np.array_equal(X, Xl) and np.array_equal(X, Xh)
+        assert np.array_equal(P[:k], Pl) and np.array_equal(P[k:], Ph)
+    for f in (full, lo, hi):
+        f.close()
+
+
+def test_cfg4_full_size_one_step(aslam, orc):
+    """config 4 at BASELINE size: 4096 landmarks, n = 8195, 8 observed (q = 19), two steps against
+    the oracle (O(q n^2) on the host cores), plus the symmetry property of the updated P."""
+    worst = _run_large(aslam, orc, 64, 8, 2)
+    print("cfg4 worst relerr", worst)
