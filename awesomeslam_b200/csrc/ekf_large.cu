@@ -16,6 +16,9 @@
 //   large_update_kernel           P_local -= K_local (H_o P): the HBM-bound streaming kernel
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
+#include "bulk_copy.cuh"
 #include "device_math.cuh"
 #include "large.hpp"
 
@@ -411,6 +414,132 @@ __global__ void __launch_bounds__(256) large_update_kernel(uint32_t n, uint32_t 
     }
 }
 
+// K5, bulk-copy form (the one launched for q <= 40). The covariance tile never passes through
+// registers on its way in or out: one elected thread drives the copy engine (cp.async.bulk, SASS
+// UBLKCP) to pull 256*R rows x CS columns of P -- CS contiguous column segments -- plus the matching
+// CS x Q block of H_o P into one of NST shared-memory stages, the CTA updates the stage in place
+// (thread t: rows R t .. R t + R - 1 of every column, -K slice in registers, H_o P read as a
+// broadcast), and the same thread streams the stage back with bulk stores. Loads run NST-2 stages
+// ahead, so the bytes in flight per SM are set by shared memory (up to ~190 KB), not by registers.
+template <int R, int Q, int CS, int NST>
+struct BulkGeo {
+    static constexpr int ROWS = 256 * R;
+    static constexpr size_t P_BYTES = (size_t)CS * ROWS * sizeof(double);
+    static constexpr size_t H_BYTES = (size_t)CS * Q * sizeof(double);
+    static constexpr size_t STAGE = P_BYTES + H_BYTES;
+    static constexpr size_t SMEM = NST * STAGE + NST * sizeof(uint64_t) + 16;
+};
+
+template <int R, int Q, int CS, int NST>
+__global__ void __launch_bounds__(256, 1) large_update_bulk_kernel(uint32_t n, uint32_t rb, uint32_t nrows, size_t ldp,
+                                                                  double* __restrict__ P,
+                                                                  const double* __restrict__ K,
+                                                                  const double* __restrict__ hp,
+                                                                  uint32_t cols_per_cta) {
+    using G = BulkGeo<R, Q, CS, NST>;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + NST * G::STAGE);
+    const int tid = threadIdx.x;
+    const uint32_t r0 = blockIdx.y * G::ROWS;                          // first local row of the tile
+    const uint32_t rows_here = min((uint32_t)G::ROWS, (uint32_t)ldp - r0);  // ldp is a multiple of 16 rows
+    const uint32_t seg_bytes = rows_here * sizeof(double);
+    const uint32_t c_begin = blockIdx.x * cols_per_cta;
+    const uint32_t c_end = min(n, c_begin + cols_per_cta);
+    if (c_begin >= c_end) return;
+    const uint32_t nchunks = (c_end - c_begin + CS - 1) / CS;
+
+    auto stage_p = [&](int st) { return reinterpret_cast<double*>(smem_raw + st * G::STAGE); };
+    auto stage_h = [&](int st) { return reinterpret_cast<double*>(smem_raw + st * G::STAGE + G::P_BYTES); };
+    auto issue_load = [&](uint32_t chunk) {  // elected thread only
+        const int st = chunk % NST;
+        const uint32_t c0 = c_begin + chunk * CS;
+        const uint32_t cw = min((uint32_t)CS, c_end - c0);
+        bulk::mbar_expect_tx(&full[st], cw * seg_bytes + cw * Q * (uint32_t)sizeof(double));
+        double* dp = stage_p(st);
+        for (uint32_t c = 0; c < cw; ++c)
+            bulk::g2s(dp + c * G::ROWS, P + (size_t)(c0 + c) * ldp + r0, seg_bytes, &full[st]);
+        bulk::g2s(stage_h(st), hp + (size_t)c0 * Q, cw * Q * (uint32_t)sizeof(double), &full[st]);
+    };
+
+    if (tid == 0) {
+        for (int s = 0; s < NST; ++s) bulk::mbar_init(&full[s], 1);
+        bulk::fence_barrier_init();
+    }
+    __syncthreads();
+    if (tid == 0)
+        for (uint32_t c = 0; c < (uint32_t)(NST - 1) && c < nchunks; ++c) issue_load(c);
+
+    // this thread's R x Q slice of -K
+    const uint32_t i0 = r0 + tid * R;
+    double nk[Q][R];
+#pragma unroll
+    for (int k = 0; k < Q; ++k)
+#pragma unroll
+        for (int r = 0; r < R; ++r) nk[k][r] = (i0 + r < nrows) ? -K[(size_t)k * n + rb + i0 + r] : 0.0;
+    const bool active = (uint32_t)(tid * R) < rows_here;
+
+    for (uint32_t chunk = 0; chunk < nchunks; ++chunk) {
+        const int st = chunk % NST;
+        const uint32_t c0 = c_begin + chunk * CS;
+        const uint32_t cw = min((uint32_t)CS, c_end - c0);
+        bulk::mbar_wait(&full[st], (chunk / NST) & 1u);
+        if (active) {
+            double* sp = stage_p(st) + tid * R;
+            const double* sh = stage_h(st);
+            if (cw == CS) {
+#pragma unroll
+                for (int c = 0; c < CS; ++c) {
+                    double v[R];
+                    if constexpr (R == 2) {
+                        const double2 t = *reinterpret_cast<const double2*>(sp + c * G::ROWS);
+                        v[0] = t.x;
+                        v[1] = t.y;
+                    } else {
+                        v[0] = sp[c * G::ROWS];
+                    }
+#pragma unroll
+                    for (int k = 0; k < Q; k += 2) {
+                        const double2 h = *reinterpret_cast<const double2*>(sh + c * Q + k);
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            v[r] = fma(nk[k][r], h.x, v[r]);
+                            v[r] = fma(nk[k + 1][r], h.y, v[r]);
+                        }
+                    }
+                    if constexpr (R == 2) {
+                        *reinterpret_cast<double2*>(sp + c * G::ROWS) = make_double2(v[0], v[1]);
+                    } else {
+                        sp[c * G::ROWS] = v[0];
+                    }
+                }
+            } else {
+                for (uint32_t c = 0; c < cw; ++c)
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        double v = sp[c * G::ROWS + r];
+#pragma unroll
+                        for (int k = 0; k < Q; ++k) v = fma(nk[k][r], sh[c * Q + k], v);
+                        sp[c * G::ROWS + r] = v;
+                    }
+            }
+            bulk::fence_proxy_async();
+        }
+        __syncthreads();
+        if (tid == 0) {
+            const double* sp = stage_p(st);
+            for (uint32_t c = 0; c < cw; ++c) bulk::s2g(P + (size_t)(c0 + c) * ldp + r0, sp + c * G::ROWS, seg_bytes);
+            bulk::commit_group();
+            // refill the stage drained one iteration ago: its store group is the second newest
+            const uint32_t nxt = chunk + NST - 1;
+            if (nxt < nchunks) {
+                bulk::wait_group_read<1>();
+                issue_load(nxt);
+            }
+        }
+    }
+    if (tid == 0) bulk::wait_group<0>();
+}
+
 // Any q (up to LARGE_QMAX): K read from global (L2-resident), FP64-bound for large q anyway.
 __global__ void __launch_bounds__(256) large_update_generic_kernel(uint32_t n, uint32_t rb, uint32_t nrows,
                                                                   size_t ldp, double* __restrict__ P,
@@ -467,24 +596,52 @@ aslam_status large_ekf_phase2(aslam_large* h) {
     const uint32_t nrows = h->row_end - h->row_begin;
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
     if (QT == 20 || QT == 40) {
-        // grid: (column ranges) x (row blocks); 2 CTAs per SM, sized so full row blocks fill whole waves
-        const uint32_t rows_per_cta = QT == 20 ? 512u : 256u;
-        const uint32_t rblocks = (nrows + rows_per_cta - 1) / rows_per_cta;
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
-        const uint32_t target = (uint32_t)sms * 2 * 4;  // about 4 waves of 2 CTAs/SM
-        uint32_t cx = (target + rblocks - 1) / rblocks;
+        static const char* variant = std::getenv("ASLAM_LARGE_UPDATE");  // "ldg": register-path kernel
+        static const char* waves_env = std::getenv("ASLAM_LARGE_WAVES");
+        const bool use_ldg = variant && variant[0] == 'l';
+        const uint32_t rows_per_cta = QT == 20 ? 512u : 256u;
+        const uint32_t rblocks = (nrows + rows_per_cta - 1) / rows_per_cta;
+        const uint32_t full_rblocks = nrows / rows_per_cta ? nrows / rows_per_cta : 1;
+        // column ranges: the full row blocks fill `waves` whole waves of the resident CTAs
+        const uint32_t resident = (uint32_t)sms * (use_ldg ? 2u : 1u);
+        const uint32_t waves = waves_env ? (uint32_t)std::atoi(waves_env) : 4u;
+        uint32_t cx = (waves * resident + full_rblocks / 2) / full_rblocks;
         if (cx < 1) cx = 1;
+        const uint32_t cs = QT == 20 ? 8u : 16u;
         uint32_t cols_per_cta = (n + cx - 1) / cx;
-        cols_per_cta = ((cols_per_cta + 63) / 64) * 64;
+        cols_per_cta = ((cols_per_cta + cs - 1) / cs) * cs;
         cx = (n + cols_per_cta - 1) / cols_per_cta;
         dim3 grid(cx, rblocks);
-        if (QT == 20)
-            large_update_kernel<2, 20, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp,
-                                                                      cols_per_cta);
-        else
-            large_update_kernel<1, 40, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp,
-                                                                      cols_per_cta);
+        if (use_ldg) {
+            if (QT == 20)
+                large_update_kernel<2, 20, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K,
+                                                                          h->hp, cols_per_cta);
+            else
+                large_update_kernel<1, 40, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K,
+                                                                          h->hp, cols_per_cta);
+        } else if (QT == 20) {
+            using G = BulkGeo<2, 20, 8, 5>;
+            static bool set = false;
+            if (!set) {
+                ASLAM_CUDA(cudaFuncSetAttribute(large_update_bulk_kernel<2, 20, 8, 5>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
+                set = true;
+            }
+            large_update_bulk_kernel<2, 20, 8, 5><<<grid, 256, G::SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
+                                                                                    h->K, h->hp, cols_per_cta);
+        } else {
+            using G = BulkGeo<1, 40, 16, 5>;
+            static bool set = false;
+            if (!set) {
+                ASLAM_CUDA(cudaFuncSetAttribute(large_update_bulk_kernel<1, 40, 16, 5>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
+                set = true;
+            }
+            large_update_bulk_kernel<1, 40, 16, 5><<<grid, 256, G::SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
+                                                                                     h->K, h->hp, cols_per_cta);
+        }
     } else {
         dim3 grid((nrows + 255) / 256, (n + 31) / 32);
         large_update_generic_kernel<<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp, QT,

@@ -61,7 +61,7 @@ def test_cfg1_single_ekf_1000_steps(aslam, orc):
 def test_ekf_reference_cap_rejects_batch(aslam, orc):
     """16 landmarks against the reference's cap of 30 (config.h:45): the whole promotion batch is
     dropped (ekf.cpp:263-268) and never retried."""
-    worst, o = _run_single(aslam, orc, "ekf", 24, lm=aslam.map_cfg3())
+    worst, o = _run_single(aslam, orc, "ekf", 16, lm=aslam.map_cfg3())
     assert o.N == 3 and o.cap_rejected()
 
 
