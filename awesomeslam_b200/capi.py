@@ -70,6 +70,8 @@ SIGNATURES = {
     "aslam_version": (C.c_char_p, []),
     "aslam_device_count": (_i32, []),
     "aslam_quat2euler": (_f32, [_f64, _f64, _f64, _f64]),
+    "aslam_probe_fp64_tflops": (_i32, [_i32, C.POINTER(_f64)]),
+    "aslam_filter_read_state": (_i32, [_vp, _vp]),
     "aslam_ekf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
     "aslam_ukf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
     "aslam_filter_destroy": (_i32, [_vp]),

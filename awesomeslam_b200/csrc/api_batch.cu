@@ -94,6 +94,18 @@ __global__ void batch_landmarks_kernel(BatchState st, double* lx, double* ly, ui
     count[f] = L;
 }
 
+// FP64 FMA-pipe probe: 8 independent DFMA chains per thread, enough threads to fill the chip.
+__global__ void fp64_probe_kernel(double* out, int iters) {
+    double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6,
+           a7 = a0 + 7;
+    const double m = 0.999999, c = 1e-7;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+        a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+    }
+    if (a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7 == 12345.678) out[0] = a0;
+}
+
 }  // namespace aslam
 
 using namespace aslam;
@@ -250,6 +262,47 @@ int32_t aslam_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
     return n;
+}
+
+/* Measured peak of the FP64 FMA pipe (TFLOP/s, 2 flop per DFMA): the denominator of the batched
+ * kernels' compute roofline (MEASURED_PEAKS.json records none). */
+aslam_status aslam_probe_fp64_tflops(int32_t device, double* tflops) {
+    if (!tflops) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(device));
+    int sms = 0;
+    ASLAM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    double* d = nullptr;
+    ASLAM_CUDA(cudaMalloc((void**)&d, 8));
+    cudaEvent_t e0, e1;
+    ASLAM_CUDA(cudaEventCreate(&e0));
+    ASLAM_CUDA(cudaEventCreate(&e1));
+    const int iters = 20000, blocks = sms * 8, threads = 256;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {
+        ASLAM_CUDA(cudaEventRecord(e0));
+        fp64_probe_kernel<<<blocks, threads>>>(d, iters);
+        ASLAM_CUDA(cudaEventRecord(e1));
+        ASLAM_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ASLAM_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double tf = 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    *tflops = best;
+    return ASLAM_OK;
+}
+
+/* X only, into a caller buffer [batch][ld] (e.g. pinned memory); synchronises the stream. */
+aslam_status aslam_filter_read_state(aslam_filter* h, double* X) {
+    if (!h || !X) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    ASLAM_CUDA(cudaMemcpyAsync(X, h->st.X, (size_t)h->st.batch * h->st.ld * sizeof(double), cudaMemcpyDeviceToHost,
+                               h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
 }
 
 float aslam_quat2euler(double w, double x, double y, double z) {

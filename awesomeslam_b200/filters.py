@@ -140,6 +140,12 @@ class BatchedFilter:
             assoc = assoc[:self._obs_total]
         return {"X": X, "P": P, "N": N, "status": st, "assoc": assoc}
 
+    def read_state_into(self, X_out):
+        """param.X of every filter into a caller array [batch, ld] (may be pinned). Synchronises."""
+        assert X_out.dtype == np.float64 and X_out.size == self.batch * self.ld and X_out.flags["C_CONTIGUOUS"]
+        capi.check(self._lib.aslam_filter_read_state(self._h, capi.ptr(X_out)))
+        self._keep.clear()
+
     def get_aux(self):
         B, ld = self.batch, self.ld
         Z = np.zeros((B, ld), np.float64)

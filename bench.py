@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""bench.py -- EKF-SLAM filter updates/s of the B200 path (BASELINE.json metric), one JSON line.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  (N > 1: python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...)
+
+Workload (config.workload = "cfg3"): 65,536 independent EKF-SLAM filters x 16 landmarks PER GPU
+(weak scaling; the filters are independent, so the batch shards with no collective), synthetic
+replay of SURVEY.md section 8d, per-filter seeds, every filter already at N = 35 when the timed region
+starts. One bench "step" = one launch that replays FUSE consecutive messages for every filter of
+the batch (the covariance stays on-chip between them); updates = filters x FUSE per step.
+
+  value     updates/s, messages resident in HBM (aslam_filter_run_device)
+  e2e       same through the host-buffer entry point (aslam_filter_run_host from pinned memory +
+            a device->host read of param.X every step)
+  roofline  the HBM-bound kernel north_star sets a roofline target for: the large-map (cfg4,
+            n = 8195) streaming covariance update, timed live with CUDA events on its own stream in
+            this same run (second leg, rank 0 / sharded over the ranks when N > 1)
+  roofline_batched   the cfg3 kernel against the measured FP64-pipe peak and against HBM
+  cpu_baseline       the CPU oracle (port of the reference math) on the host cores, bounded sample
+
+The reference arm (--impl reference) times that same oracle with all host threads on the same
+config; the reference itself needs ROS + Eigen and cannot be built here.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_PER_GPU = 65536
+L_CFG3 = 16
+FUSE = 8               # messages per launch
+WARM_MSGS = 24         # replayed before timing: 15 stationary + promotion on the 10th + settle
+FLOP_PER_UPDATE = 6 * 35 ** 3          # SURVEY.md section 8d convention (6 n^3), fixed
+BYTES_PER_UPDATE = 20888               # X, Z, P read + written, inputs
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=B_PER_GPU, help="filters per GPU")
+    ap.add_argument("--no-large", action="store_true", help="skip the cfg4 large-map leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU-baseline leg")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device = device
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except ValueError:
+                continue
+            for k, nme in enumerate(names):
+                if r[5 + k].lower().startswith("active"):
+                    reasons.add(nme)
+        sm_sorted = sorted(sm)
+        # samples taken while the GPU was busy are the upper part of the distribution
+        load = sm_sorted[len(sm_sorted) // 2:] if sm_sorted else []
+        return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------ CPU legs
+def cpu_leg(sample_filters, msgs, threads=0):
+    """The CPU oracle (oracle/, a port of the reference math) on `sample_filters` cfg3 filters x `msgs`
+    messages from reset, all host threads. Returns (updates/s, threads, seconds)."""
+    import awesomeslam_b200 as A
+    from oracle import oracle as O
+    O.build()
+    lmx, lmy = A.map_cfg3()
+    rp = A.Replay(lmx, lmy, sample_filters, msgs, seed0=A.replay.SEED_CFG3)
+    cfg = O.default_config(max_state_dim=64)
+    nthr = threads or (os.cpu_count() or 1)
+    sec, X, P, N = O.run_batch("ekf", cfg, sample_filters, msgs, L_CFG3, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt,
+                               rp.range, rp.bearing, nthr, 36, want_P=False)
+    assert np.all(N == 35), "oracle filters did not reach N = 35"
+    return sample_filters * msgs / sec, nthr, sec
+
+
+def reference_arm(args):
+    """--impl reference: the reference's own CPU implementation of the path is not buildable here
+    (ROS + Eigen absent), so the oracle port is timed, with all host threads, on the cfg3 workload.
+    One step = FUSE messages for a bounded sample of the batch."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import awesomeslam_b200 as A
+    from oracle import oracle as O
+    O.build()
+    sample = 256
+    lmx, lmy = A.map_cfg3()
+    total_msgs = WARM_MSGS + (args.warmup + args.steps) * FUSE
+    rp = A.Replay(lmx, lmy, sample, total_msgs, seed0=A.replay.SEED_CFG3)
+    cfg = O.default_config(max_state_dim=64)
+    nthr = os.cpu_count() or 1
+    # the oracle's batch runner starts every filter from reset: time the whole replay, subtract nothing,
+    # and attribute the time to the timed steps in proportion to their messages (the warm-up messages
+    # at N = 3 are cheaper, so this slightly FAVOURS the CPU)
+    sec, X, P, N = O.run_batch("ekf", cfg, sample, total_msgs, L_CFG3, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt,
+                               rp.range, rp.bearing, nthr, 36, want_P=False)
+    ups = sample * total_msgs / sec
+    ms_per_step = 1e3 * sec * (FUSE / total_msgs)
+    line = {
+        "impl": "reference", "metric": "ekf_slam_filter_updates_per_s", "value": ups, "unit": "updates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "cfg3: 65,536 EKF-SLAM filters x 16 landmarks per GPU (n=35)",
+                   "sample": "%d filters x %d messages" % (sample, total_msgs), "fuse": FUSE},
+        "cpu_baseline": {"value": ups, "unit": "updates/s", "cores": nthr, "kind": "port",
+                         "sample": "%d of 65,536 filters x %d messages from reset, OpenMP over filters" % (sample, total_msgs)},
+        "e2e": {"value": ups, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference (ROS1 + Eigen3) cannot be built in this image; this is the CPU oracle port of its filter math",
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------ GPU legs
+class _DevArray:
+    """CUDA-array-interface view of library-owned device memory (for torch.as_tensor)."""
+
+    def __init__(self, ptr, count):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+def batched_leg(args, torch, dist, rank, world, dev):
+    import awesomeslam_b200 as A
+    B = args.batch
+    K, W = args.steps, args.warmup
+    lmx, lmy = A.map_cfg3()
+    total_msgs = WARM_MSGS + (W + K) * FUSE
+    # per-filter seeds 0x5EED0000 + global filter id (rank-major)
+    rp = A.Replay(lmx, lmy, B, total_msgs, seed0=A.replay.SEED_CFG3, first_filter=rank * B)
+    host = [rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing]
+    dev_t = [torch.from_numpy(a).to(dev) for a in host]
+    pinned = [torch.from_numpy(a).pin_memory() for a in host]
+
+    def dptrs(msg0):
+        out = []
+        for t in dev_t:
+            per = t[0].numel() * t.element_size()
+            out.append(t.data_ptr() + msg0 * per)
+        return out
+
+    def run_resident(f, msg0, nmsg):
+        p = dptrs(msg0)
+        f.run_device(nmsg, p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], L_CFG3)
+
+    def run_hostbuf(f, msg0, nmsg):
+        sl = slice(msg0, msg0 + nmsg)
+        a = [t[sl].numpy() for t in pinned]
+        f.run_host(nmsg, a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], L_CFG3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    results = {}
+    for mode in ("resident", "e2e"):
+        f = A.BatchedFilter("ekf", B, dev.index, max_state_dim=64)
+        stream = torch.cuda.ExternalStream(f.stream, device=dev)
+        xout = torch.empty((B, f.ld), dtype=torch.float64).pin_memory()
+        run_resident(f, 0, WARM_MSGS)  # bring every filter to N = 35 (not timed)
+        f.sync()
+        st = f.get_state(want_P=False, want_assoc=False)
+        assert np.all(st["N"] == 35) and not np.any(st["status"]), "warm-up did not map all 16 landmarks"
+        runner = run_resident if mode == "resident" else run_hostbuf
+        msg = WARM_MSGS
+        for _ in range(W):
+            runner(f, msg, FUSE)
+            if mode == "e2e":
+                f.read_state_into(xout.numpy())
+            msg += FUSE
+        l0 = f.launch_count
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler = ClockSampler(dev.index)
+        if mode == "resident" and rank == 0:
+            sampler.start()
+        barrier()
+        with torch.cuda.stream(stream):
+            e0.record()
+            for _ in range(K):
+                runner(f, msg, FUSE)
+                if mode == "e2e":
+                    f.read_state_into(xout.numpy())
+                msg += FUSE
+            e1.record()
+        f.sync()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        clocks = sampler.stop() if (mode == "resident" and rank == 0) else None
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        st = f.get_state(want_P=False, want_assoc=False)
+        assert np.all(st["N"] == 35) and not np.any(st["status"]) and np.all(np.isfinite(st["X"]))
+        results[mode] = {"ms": ms, "launches": f.launch_count - l0, "clocks": clocks, "ld": f.ld}
+        f.close()
+    per_msg = rp.nbytes_per_step()
+    results["h2d_bytes_per_step"] = per_msg * FUSE
+    results["d2h_bytes_per_step"] = B * results["e2e"]["ld"] * 8
+    return results
+
+
+def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
+    """cfg4: n = 8195, 8 observed landmarks per step (q = 19). Rows of P sharded over the ranks;
+    the exchange buffer (2 q n doubles) is summed with one NCCL all-reduce per step when world > 1."""
+    import awesomeslam_b200 as A
+    K, W = args.steps, args.warmup
+    tx, ty, X0, G, d = A.large_map_state(64)
+    n = X0.size
+    P0 = A.dense_P(G, d)
+    rb = 0 if rank == 0 else max(3, (n * rank) // world)
+    re = n if rank == world - 1 else max(3, (n * (rank + 1)) // world)
+    f = A.LargeFilter("ekf", n, dev.index, row_begin=rb, row_end=re)
+    f.load_state_colmajor(X0, P0)
+    del P0
+    rng, brg, idx = A.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8)
+    stream = torch.cuda.ExternalStream(f.stream, device=dev)
+    exch = None
+
+    def step():
+        nonlocal exch
+        if world == 1:
+            f.step(0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
+        else:
+            f.step_phase1(0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg)
+            if exch is None:
+                p, c = f.exchange_buffer()
+                exch = torch.as_tensor(_DevArray(p, c), device=dev)
+            dist.all_reduce(exch)
+            f.step_phase2(want_assoc=False)
+
+    with torch.cuda.stream(stream):
+        for _ in range(max(W, 3)):
+            step()
+        f.sync()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = f.launch_count
+        e0.record()
+        for _ in range(K):
+            step()
+        e1.record()
+        f.sync()
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1) / K
+        launches = f.launch_count - l0
+        kms = []
+        for _ in range(K):
+            step()
+            kms.append(f.last_kernel_ms())
+    t = torch.tensor([ms, float(np.mean(kms))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, kernel_ms = float(t[0].item()), float(t[1].item())
+    X, _ = f.get_state(want_P=False)
+    assert np.all(np.isfinite(X))
+    f.close()
+    rows = re - rb
+    bytes_launch = 2 * 8 * rows * n  # this rank's rows of P, read + written once
+    achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
+    return {
+        "workload": "cfg4: large-map EKF n=8195 (4096 landmarks), q=19 rows of H per step, FP64 P%s"
+                    % ("" if world == 1 else ", rows sharded over %d GPUs + 1 NCCL all-reduce/step" % world),
+        "steps_per_s": 1e3 / ms, "ms_per_step": ms, "launches_per_step": launches / K,
+        "roofline": {"bound": "hbm", "kernel": "large_update_bulk_kernel<2,20,8,5>", "achieved": achieved,
+                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                     "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": kernel_ms, "peak_source": peak_src},
+    }
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    import torch
+    import torch.distributed as dist
+    import awesomeslam_b200 as A
+    A.capi.lib()  # fails loudly when the CUDA library is missing: there is no fallback path
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU path)")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    hbm_peak, peak_src = measured_peaks()
+
+    res = batched_leg(args, torch, dist, rank, world, dev)
+    B, K, W = args.batch, args.steps, args.warmup
+    updates = B * world * FUSE * K
+    value = updates / (res["resident"]["ms"] * 1e-3)
+    e2e = updates / (res["e2e"]["ms"] * 1e-3)
+
+    fp64 = None
+    if rank == 0:
+        import ctypes as C
+        tf = C.c_double()
+        A.capi.check(A.capi.lib().aslam_probe_fp64_tflops(local, C.byref(tf)))
+        fp64 = tf.value
+    large = None
+    if not args.no_large:
+        large = large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src)
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    per_gpu_ups = value / world
+    line = {
+        "metric": "ekf_slam_filter_updates_per_s", "value": value, "unit": "updates/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": res["resident"]["ms"] / K,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "cfg3: 65,536 EKF-SLAM filters x 16 landmarks per GPU (n=35), Monte Carlo seeds",
+                   "filters_per_gpu": B, "messages_per_step": FUSE, "updates_per_step": B * world * FUSE,
+                   "l2": "inputs larger than L2 (covariances %.0f MB + messages per GPU)" % (B * 36 * 36 * 8 / 1e6),
+                   "parallelism": "batch-sharded, no collective" if world > 1 else "1 GPU"},
+        "e2e": {"value": e2e, "unit": "updates/s", "h2d_bytes_per_step": res["h2d_bytes_per_step"],
+                "d2h_bytes_per_step": res["d2h_bytes_per_step"], "ms_per_step": res["e2e"]["ms"] / K,
+                "api": "aslam_filter_run_host (pinned host messages) + aslam_filter_read_state"},
+        "gpu_launches": res["resident"]["launches"],
+        "clocks": res["resident"]["clocks"],
+        "roofline_batched": {
+            "kernel": "ekf_batched_kernel<36,2>", "bound": "fp64",
+            "achieved": per_gpu_ups * FLOP_PER_UPDATE / 1e12, "peak": fp64, "unit": "TFLOP/s",
+            "frac": (per_gpu_ups * FLOP_PER_UPDATE / 1e12 / fp64) if fp64 else None,
+            "flop_convention": "6 n^3 = 257,250 per update (SURVEY 8d); the kernel executes ~n^3 fma",
+            "hbm_frac_if_streamed": per_gpu_ups * BYTES_PER_UPDATE / 1e9 / hbm_peak,
+            "peak_source": "aslam_probe_fp64_tflops (DFMA chain, this run)"},
+    }
+    if large:
+        line["roofline"] = large["roofline"]
+        line["large_map"] = {k: v for k, v in large.items() if k != "roofline"}
+    else:
+        line["roofline"] = None
+    if not args.no_cpu:
+        ups, nthr, sec = cpu_leg(256 if (os.cpu_count() or 1) < 16 else 1024, 120)
+        line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": nthr, "kind": "port",
+                                "sample": "cfg3 filters x 120 messages from reset, OpenMP over filters, %.1f s" % sec}
+        line["speedup_e2e_vs_cpu"] = e2e / ups
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

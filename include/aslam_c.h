@@ -100,6 +100,10 @@ const char* aslam_last_error(void);
 const char* aslam_version(void);
 int32_t aslam_device_count(void);
 
+/* Measured throughput of the FP64 FMA pipe of `device` in TFLOP/s (roofline denominator of the
+ * batched kernels; not part of the filter path). */
+aslam_status aslam_probe_fp64_tflops(int32_t device, double* tflops);
+
 /* tools.h:62-66 quat2euler: arguments rounded to float, atan2f. Host-side helper. */
 float aslam_quat2euler(double w, double x, double y, double z);
 
@@ -150,6 +154,8 @@ aslam_status aslam_filter_get_llt_fail(aslam_filter* h, int32_t* fail_k);
  *   ekf.cpp:160-173) the observation was written to, or -1 when it went to the wait-list. */
 aslam_status aslam_filter_get_state(aslam_filter* h, double* X, double* P, uint32_t* N, int32_t* assoc,
                                     uint32_t* status);
+/* param.X only, into a caller buffer [batch][ld] (pinned memory for the end-to-end path). */
+aslam_status aslam_filter_read_state(aslam_filter* h, double* X);
 /* Z [batch][ld]; EKF only: a00/a10 [batch] = A(0,0), A(1,0) (ekf.cpp:210-211) */
 aslam_status aslam_filter_get_aux(aslam_filter* h, double* Z, double* a00, double* a10);
 /* wait-list export: count [batch]; range/bearing/hits [batch][ASLAM_MAX_WAIT] */
