@@ -25,7 +25,7 @@ ST_NONFINITE = 1 << 2
 ST_WAIT_OVERFLOW = 1 << 3
 ST_OBS_OVERFLOW = 1 << 4
 
-MAX_WAIT = 48
+MAX_WAIT = 256
 MAX_OBS = 64
 KIND_EKF = 0
 KIND_UKF = 1

@@ -26,8 +26,7 @@ uint32_t batched_padded_dim(int32_t max_state_dim, int kind) {
     const int nmax = max_state_dim - 1;
     if (nmax < 3) return 0;
     if (kind == ASLAM_KIND_UKF) {
-        if (nmax <= 29) return 30;
-        if (nmax <= 63) return 64;
+        if (nmax <= 29) return 30;  // the reference's cap; larger UKF maps: aslam_large_ukf_*
         return 0;
     }
     if (nmax <= 29) return 30;

@@ -270,6 +270,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
 #pragma unroll
                 for (int c = 0; c < CPT; ++c)
                     p[c][i] = fma(-v01.x, g[c][0], fma(-v01.y, g[c][1], fma(-v2, g[c][2], p[c][i])));
+                if ((i & 7) == 7) asm volatile("" ::: "memory");
             }
         } else {
 #pragma unroll
@@ -333,6 +334,8 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                     const double2 vi = *reinterpret_cast<const double2*>(&s.V[buf][i * 2]);
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) p[c][i] = fma(-vi.x, g[c][0], fma(-vi.y, g[c][1], p[c][i]));
+                    // keep the scheduler from hoisting all NP broadcast loads ahead of the FMAs (spills)
+                    if ((i & 7) == 7) asm volatile("" ::: "memory");
                 }
             }
         }

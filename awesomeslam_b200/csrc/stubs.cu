@@ -1,10 +1,6 @@
 // Temporary stubs (replaced as the kernels land).
 #include "large.hpp"
 namespace aslam {
-aslam_status launch_ukf_batched(const aslam_config&, const BatchState&, const BatchInput&, cudaStream_t) {
-    set_error("ukf batched: not built yet");
-    return ASLAM_ERR_UNSUPPORTED;
-}
 aslam_status large_ukf_create(aslam_large*) { set_error("ukf large: not built yet"); return ASLAM_ERR_UNSUPPORTED; }
 void large_ukf_destroy(aslam_large*) {}
 aslam_status large_ukf_step(aslam_large*, double, double, float, double, double, float, uint32_t) { return ASLAM_ERR_UNSUPPORTED; }

@@ -1,0 +1,440 @@
+// K2: batched UKF-SLAM step. Replaces, for every filter of a batch, updateZ +
+// slam of the reference (src/ukf/ukf.cpp:113-180, 260-392), the weights of src/ukf/ukf.h:73-81 and the
+// models of include/awesome_slam/common.h:46-90.
+//
+// Mapping: one CTA (128 threads) per filter; the whole working set of a step -- Paug/L, the
+// 2N+5 propagated sigma points, their measurement images, P, S, Tc, K -- lives in shared memory
+// (about 75 KB, three filters per SM) and P stays there across the `steps` messages of a launch.
+//
+// Numerics: the reference UKF is numerically fragile (w0 = (1-N)/3 < 0: P - K S K' goes indefinite
+// and Eigen's LLT silently returns a half-factored L), so every reduction here
+// keeps the reference's order -- each output element is one thread's sequential sum over the
+// sigma points / inner index, multiply and add rounded separately (the library is built with
+// -fmad=false) -- and the LLT, LU and triangular solves follow Eigen's unblocked algorithms step
+// for step. Parallelism is across output elements only. What can still differ from the CPU are
+// the last bits of sin/cos/atan2.
+#include <cuda_runtime.h>
+
+#include "frontend.cuh"
+#include "internal.hpp"
+
+namespace aslam {
+
+namespace {
+
+constexpr int UNP = 30;          // padded state dim (N <= 29: the reference's cap, config.h:45)
+constexpr int UNA = UNP + 2;     // augmented
+constexpr int UNS = 2 * UNP + 5; // sigma points (<= 63 used)
+constexpr int USP = 65;          // row pitch of the sigma-point matrices (odd: conflict-free row walks)
+constexpr int UTHREADS = 128;
+
+struct __align__(16) UkfSlot {
+    double XS[UNP][USP];   // XsigPred, later Xdiff       (row = state index, col = sigma point)
+    double ZS[UNP][USP];   // Zsig, later Zdiff
+    double L[UNA][UNA];    // Paug -> L (ukf.cpp:263-280); later K S
+    double P[UNP][UNP];
+    double S[UNP][UNP];
+    double Tc[UNP][UNP];
+    double K[UNP][UNP];
+    double LU[UNP][UNP];   // PartialPivLU of S, then S^-1 in Si
+    double Si[UNP][UNP];
+    double X[UNP], Z[UNP], Zp[UNP], Zd[UNP], W[UNS];
+    int piv[UNP];
+    int fail_k;
+    FrontSlot fr;
+};
+
+struct UkfParams {
+    BatchState st;
+    BatchInput in;
+    FrontParams fp;
+    double kq, kr, kp_lm;
+    float std_a, std_yaw;
+};
+
+// common.h:46-75 for one (augmented) sigma point: rows 0..2 of the column; `na` = point(N).
+__device__ __forceinline__ void motion_model_aug(double& x, double& y, double& th, double na, float vx, float az,
+                                                 float dt) {
+    const double th0 = th;
+    double s0, c0;
+    sincos(th0, &s0, &c0);
+    const float azdt = __fmul_rn(az, dt);
+    if (fabs((double)az) > 0.001) {
+        const float r = __fdiv_rn(vx, az);
+        double s1, c1;
+        sincos(__dadd_rn(th0, (double)azdt), &s1, &c1);
+        x = __dadd_rn(x, __dmul_rn((double)r, __dadd_rn(-s0, s1)));
+        y = __dadd_rn(y, __dmul_rn((double)r, __dsub_rn(c0, c1)));
+    } else {
+        const float vxdt = __fmul_rn(vx, dt);
+        x = __dadd_rn(x, __dmul_rn((double)vxdt, c0));
+        y = __dadd_rn(y, __dmul_rn((double)vxdt, s0));
+    }
+    th = __dadd_rn(th0, (double)azdt);
+    // common.h:69-71: 0.5 * dt * dt * point(N) * cos(point(2)), all double, left to right
+    const double h = __dmul_rn(__dmul_rn(0.5, (double)dt), (double)dt);
+    x = __dadd_rn(x, __dmul_rn(__dmul_rn(h, na), c0));
+    y = __dadd_rn(y, __dmul_rn(__dmul_rn(h, na), s0));
+    th = __dadd_rn(th, __dmul_rn(h, (double)az));  // `az`, not point(N+1), as written
+}
+
+__global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams kp) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    UkfSlot& s = *reinterpret_cast<UkfSlot*>(smem_raw);
+    const int tid = threadIdx.x;
+    const uint32_t f = blockIdx.x;
+    const float pi = kp.fp.pi;
+
+    // ---- load state
+    for (int k = tid; k < UNP * UNP; k += UTHREADS) (&s.P[0][0])[k] = kp.st.P[(size_t)f * UNP * UNP + k];
+    for (int k = tid; k < UNP; k += UTHREADS) {
+        s.X[k] = kp.st.X[(size_t)f * UNP + k];
+        s.Z[k] = kp.st.Z[(size_t)f * UNP + k];
+    }
+    if (tid == 0) {
+        s.fr.N = kp.st.N[f];
+        s.fr.status = kp.st.status[f];
+        s.fr.flags = kp.st.flags[f];
+        s.fr.wcount = kp.st.wcount[f];
+        s.fr.promote = 0;
+        s.fail_k = kp.st.llt_fail[f];
+    }
+    __syncthreads();
+
+    for (uint32_t step = 0; step < kp.in.steps; ++step) {
+        const size_t si = (size_t)step * kp.st.batch + f;
+        if (s.fr.flags & FLAG_INIT_Z) break;  // cbOdom gate (ukf.cpp:72); uniform for the CTA
+        // ---- updateZ, ukf.cpp:115-118
+        if (tid == 0) {
+            s.fr.ox = kp.in.ox[si];
+            s.fr.oy = kp.in.oy[si];
+            s.fr.yaw = kp.in.yaw[si];
+            s.fr.vx = kp.in.vx[si];
+            s.fr.az = kp.in.az[si];
+            s.fr.dt = kp.in.dt[si];
+            s.Z[0] = s.fr.ox;
+            s.Z[1] = s.fr.oy;
+            s.Z[2] = (double)s.fr.yaw;
+            uint32_t base, cnt;
+            if (kp.in.offsets) {
+                base = kp.in.offsets[f];
+                cnt = kp.in.offsets[f + 1] - base;
+            } else {
+                base = (uint32_t)(si * kp.in.obs_per_filter);
+                cnt = kp.in.obs_per_filter;
+            }
+            if (cnt > ASLAM_MAX_OBS) {
+                cnt = ASLAM_MAX_OBS;
+                s.fr.status |= ASLAM_ST_OBS_OVERFLOW;
+            }
+            s.fr.obs_base = base;
+            s.fr.nobs = cnt;
+        }
+        __syncthreads();
+        front_phase_a(s.fr, kp.fp, s.X, s.Z, kp.in.range, kp.in.bearing, f, tid, UTHREADS);
+        __syncthreads();
+        if (tid == 0) {
+            int32_t* assoc = nullptr;
+            if (kp.in.assoc && step + 1 == kp.in.steps)
+                assoc = kp.in.assoc + (kp.in.offsets ? s.fr.obs_base : f * kp.in.obs_per_filter);
+            front_phase_b(s.fr, kp.fp, s.X, s.Z, f, assoc);
+            if (s.fr.flags & FLAG_INIT_X) {  // ukf.cpp:83-87
+                s.fr.flags &= ~FLAG_INIT_X;
+                for (uint32_t j = 0; j < s.fr.N; ++j) s.X[j] = s.Z[j];
+            }
+        }
+        __syncthreads();
+        const int N = (int)s.fr.N, NA = N + 2, NS = 2 * N + 5;
+        // ---- growth of P (ukf.cpp:241) and the weights (ukf.h:73-81, recomputed: they depend on N only)
+        if (s.fr.grew_from) {
+            const int g0 = (int)s.fr.grew_from;
+            for (int k = tid; k < N * N; k += UTHREADS) {
+                const int i = k / N, j = k % N;
+                if (i >= g0 || j >= g0) s.P[i][j] = (i == j) ? kp.kp_lm : 0.0;
+            }
+        }
+        const float lambda = (float)(3.0 - (double)(N + 2));
+        const float denom = __fadd_rn(__fadd_rn(lambda, (float)N), 2.0f);  // lambda + N + 2 in float
+        for (int i = tid; i < NS; i += UTHREADS)
+            s.W[i] = i == 0 ? (double)__fdiv_rn(lambda, denom) : (double)(float)(0.5 / (double)denom);
+        // ---- Paug (ukf.cpp:262-277) into L
+        for (int k = tid; k < NA * NA; k += UTHREADS) {
+            const int i = k / NA, j = k % NA;
+            double v = 0.0;
+            if (i < N && j < N) v = s.P[i][j];
+            else if (i == j) v = (double)(i == N ? __fmul_rn(kp.std_a, kp.std_a) : __fmul_rn(kp.std_yaw, kp.std_yaw));
+            s.L[i][j] = v;
+        }
+        if (tid == 0) s.fail_k = -1;
+        __syncthreads();
+        // ---- L = Paug.llt().matrixL(): Eigen's unblocked left-looking LLT with its failure rule
+        for (int k = 0; k < NA; ++k) {
+            if (s.fail_k >= 0) break;
+            double x = s.L[k][k];
+            {
+                double sum = 0.0;
+                for (int j = 0; j < k; ++j) sum += s.L[k][j] * s.L[k][j];
+                if (k > 0) x -= sum;
+            }
+            if (x <= 0.0) {  // every thread computes the same x: uniform decision
+                __syncthreads();
+                if (tid == 0) s.fail_k = k;
+                __syncthreads();
+                break;
+            }
+            x = sqrt(x);
+            for (int i = k + 1 + tid; i < NA; i += UTHREADS) {
+                double sum = 0.0;
+                for (int j = 0; j < k; ++j) sum += s.L[i][j] * s.L[k][j];
+                s.L[i][k] = (s.L[i][k] - sum) / x;
+            }
+            __syncthreads();
+            if (tid == 0) s.L[k][k] = x;
+            __syncthreads();
+        }
+        for (int k = tid; k < NA * NA; k += UTHREADS) {
+            const int i = k / NA, j = k % NA;
+            if (j > i) s.L[i][j] = 0.0;
+        }
+        __syncthreads();
+        // ---- sigma points (ukf.cpp:283-289) propagated through f (ukf.cpp:292-297)
+        {
+            const float w = __fsqrt_rn(__fadd_rn(__fadd_rn(lambda, (float)N), 2.0f));
+            const float vx = (float)s.fr.vx, az = (float)s.fr.az, dt = s.fr.dt;
+            for (int c = tid; c < NS; c += UTHREADS) {
+                // column c: 0 -> Xaug; 1..NA -> + w L.col(c-1); NA+1..2NA -> - w L.col(c-1-NA)
+                const int lc = c == 0 ? -1 : (c <= NA ? c - 1 : c - 1 - NA);
+                const double sg = c <= NA ? (double)w : -(double)w;
+                auto aug = [&](int k) -> double {
+                    const double xa = k < N ? s.X[k] : 0.0;
+                    if (lc < 0) return xa;
+                    // Xaug + w*L  and  Xaug - w*L (the product is rounded first in both)
+                    return c <= NA ? xa + (double)w * s.L[k][lc] : xa - (double)w * s.L[k][lc];
+                };
+                (void)sg;
+                double x = aug(0), y = aug(1), th = aug(2);
+                const double na = aug(N);
+                motion_model_aug(x, y, th, na, vx, az, dt);
+                s.XS[0][c] = x;
+                s.XS[1][c] = y;
+                s.XS[2][c] = (double)normalize_angle((float)th, pi);
+                for (int k = 3; k < N; ++k) s.XS[k][c] = aug(k);
+            }
+        }
+        __syncthreads();
+        // ---- predicted mean (ukf.cpp:300-304) and Zsig (ukf.cpp:322-326)
+        for (int k = tid; k < N; k += UTHREADS) {
+            double acc = 0.0;
+            for (int i = 0; i < NS; ++i) acc += s.W[i] * s.XS[k][i];
+            s.X[k] = acc;
+        }
+        {
+            const int nl = (N - 3) / 2;
+            for (int e = tid; e < NS * (nl + 1); e += UTHREADS) {
+                const int c = e % NS, l = e / NS;
+                if (l == nl) {
+                    s.ZS[0][c] = s.XS[0][c];
+                    s.ZS[1][c] = s.XS[1][c];
+                    s.ZS[2][c] = s.XS[2][c];
+                } else {
+                    double rg, br;
+                    measure_landmark(s.XS[0][c], s.XS[1][c], s.XS[2][c], s.XS[3 + 2 * l][c], s.XS[4 + 2 * l][c], rg, br);
+                    s.ZS[3 + 2 * l][c] = rg;
+                    s.ZS[4 + 2 * l][c] = br;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- Zpred (ukf.cpp:329-339); Xdiff in place (ukf.cpp:312-313)
+        for (int k = tid; k < N; k += UTHREADS) {
+            double acc = 0.0;
+            for (int i = 0; i < NS; ++i) acc += s.W[i] * s.ZS[k][i];
+            if (k >= 2 && (k & 1) == 0) acc = (double)normalize_angle((float)acc, pi);
+            s.Zp[k] = acc;
+        }
+        for (int e = tid; e < N * NS; e += UTHREADS) {
+            const int k = e / NS, c = e % NS;
+            double d = s.XS[k][c] - s.X[k];
+            if (k == 2) d = (double)normalize_angle((float)d, pi);
+            s.XS[k][c] = d;
+        }
+        __syncthreads();
+        // ---- Zdiff in place (ukf.cpp:347-351)
+        for (int e = tid; e < N * NS; e += UTHREADS) {
+            const int k = e / NS, c = e % NS;
+            double d = s.ZS[k][c] - s.Zp[k];
+            if (k >= 2 && (k & 1) == 0) d = (double)normalize_angle((float)d, pi);
+            s.ZS[k][c] = d;
+        }
+        __syncthreads();
+        // ---- P (ukf.cpp:307-319), S (ukf.cpp:342-357), Tc (ukf.cpp:360-375): one thread per entry
+        for (int e = tid; e < 3 * N * N; e += UTHREADS) {
+            const int which = e / (N * N), r = e % (N * N), a = r / N, b = r % N;
+            const double* da = which == 1 ? s.ZS[a] : s.XS[a];
+            const double* db = which == 0 ? s.XS[b] : s.ZS[b];
+            double acc = 0.0;
+            for (int i = 0; i < NS; ++i) acc = acc + (s.W[i] * da[i]) * db[i];
+            if (which == 0) s.P[a][b] = acc + ((a == b && a < 3) ? kp.kq : 0.0);
+            else if (which == 1) {
+                const double v = acc + (a == b ? kp.kr : 0.0);
+                s.S[a][b] = v;
+                s.LU[a][b] = v;
+            } else s.Tc[a][b] = acc;
+        }
+        __syncthreads();
+        // ---- S.inverse(): PartialPivLU (unblocked, first largest pivot) ...
+        for (int k = 0; k < N; ++k) {
+            if (tid == 0) {
+                int p = k;
+                double best = fabs(s.LU[k][k]);
+                for (int i = k + 1; i < N; ++i) {
+                    const double v = fabs(s.LU[i][k]);
+                    if (v > best) {
+                        best = v;
+                        p = i;
+                    }
+                }
+                s.piv[k] = best != 0.0 ? p : -1 - p;  // zero pivot: recorded, no swap/scale
+            }
+            __syncthreads();
+            const int pr = s.piv[k];
+            const bool nz = pr >= 0;
+            const int p = nz ? pr : -1 - pr;
+            if (nz && p != k)
+                for (int j = tid; j < N; j += UTHREADS) {
+                    const double t = s.LU[k][j];
+                    s.LU[k][j] = s.LU[p][j];
+                    s.LU[p][j] = t;
+                }
+            __syncthreads();
+            if (nz) {
+                const double pv = s.LU[k][k];
+                for (int i = k + 1 + tid; i < N; i += UTHREADS) s.LU[i][k] /= pv;
+            }
+            __syncthreads();
+            for (int e = tid; e < (N - k - 1) * (N - k - 1); e += UTHREADS) {
+                const int i = k + 1 + e / (N - k - 1), j = k + 1 + e % (N - k - 1);
+                s.LU[i][j] -= s.LU[i][k] * s.LU[k][j];
+            }
+            __syncthreads();
+        }
+        // ... then solve against the permuted identity, one column per thread
+        for (int e = tid; e < N * N; e += UTHREADS) s.Si[e / N][e % N] = (e / N == e % N) ? 1.0 : 0.0;
+        __syncthreads();
+        for (int j = tid; j < N; j += UTHREADS) {
+            for (int k = 0; k < N; ++k) {
+                const int pr = s.piv[k];
+                const int p = pr >= 0 ? pr : -1 - pr;
+                if (p != k) {
+                    const double t = s.Si[k][j];
+                    s.Si[k][j] = s.Si[p][j];
+                    s.Si[p][j] = t;
+                }
+            }
+            for (int i = 0; i < N; ++i) {
+                double v = s.Si[i][j];
+                for (int k = 0; k < i; ++k) v -= s.LU[i][k] * s.Si[k][j];
+                s.Si[i][j] = v;
+            }
+            for (int i = N - 1; i >= 0; --i) {
+                double v = s.Si[i][j];
+                for (int k = i + 1; k < N; ++k) v -= s.LU[i][k] * s.Si[k][j];
+                s.Si[i][j] = v / s.LU[i][i];
+            }
+        }
+        __syncthreads();
+        // ---- K = Tc S^-1 (ukf.cpp:378); residual (ukf.cpp:381-386)
+        for (int e = tid; e < N * N; e += UTHREADS) {
+            const int i = e / N, j = e % N;
+            double acc = 0.0;
+            for (int k = 0; k < N; ++k) acc += s.Tc[i][k] * s.Si[k][j];
+            s.K[i][j] = acc;
+        }
+        for (int k = tid; k < N; k += UTHREADS) {
+            double d = s.Z[k] - s.Zp[k];
+            if (k >= 2 && (k & 1) == 0) d = (double)normalize_angle((float)d, pi);
+            s.Zd[k] = d;
+        }
+        __syncthreads();
+        // ---- X += K Zdiff (ukf.cpp:389); K S into L's storage
+        for (int i = tid; i < N; i += UTHREADS) {
+            double acc = 0.0;
+            for (int k = 0; k < N; ++k) acc += s.K[i][k] * s.Zd[k];
+            s.X[i] = s.X[i] + acc;
+        }
+        double* KS = &s.L[0][0];  // N x N, pitch UNP
+        for (int e = tid; e < N * N; e += UTHREADS) {
+            const int i = e / N, j = e % N;
+            double acc = 0.0;
+            for (int k = 0; k < N; ++k) acc += s.K[i][k] * s.S[k][j];
+            KS[i * UNP + j] = acc;
+        }
+        __syncthreads();
+        // ---- P -= (K S) K' (ukf.cpp:391)
+        for (int e = tid; e < N * N; e += UTHREADS) {
+            const int i = e / N, j = e % N;
+            double acc = 0.0;
+            for (int k = 0; k < N; ++k) acc += KS[i * UNP + k] * s.K[j][k];
+            s.P[i][j] = s.P[i][j] - acc;
+        }
+        if (tid == 0 && s.fail_k >= 0) s.fr.status |= ASLAM_ST_LLT_FAILED;
+        __syncthreads();
+    }
+
+    // ---- write back
+    bool bad = false;
+    for (int k = tid; k < UNP * UNP; k += UTHREADS) {
+        const double v = (&s.P[0][0])[k];
+        kp.st.P[(size_t)f * UNP * UNP + k] = v;
+        bad |= !isfinite(v);
+    }
+    for (int k = tid; k < UNP; k += UTHREADS) {
+        kp.st.X[(size_t)f * UNP + k] = s.X[k];
+        kp.st.Z[(size_t)f * UNP + k] = s.Z[k];
+        bad |= !isfinite(s.X[k]);
+    }
+    if (bad) atomicOr(&kp.st.status[f], (uint32_t)ASLAM_ST_NONFINITE);
+    if (tid == 0) {
+        kp.st.N[f] = s.fr.N;
+        if (s.fr.status) atomicOr(&kp.st.status[f], s.fr.status);
+        kp.st.flags[f] = s.fr.flags;
+        kp.st.wcount[f] = s.fr.wcount;
+        kp.st.llt_fail[f] = s.fail_k;
+    }
+}
+
+}  // namespace
+
+aslam_status launch_ukf_batched(const aslam_config& cfg, const BatchState& st, const BatchInput& in,
+                                cudaStream_t stream) {
+    if (st.ld != UNP) {
+        set_error("ukf_batched: only the reference's cap (max_state_dim <= 30) is built; use aslam_large_ukf_*");
+        return ASLAM_ERR_UNSUPPORTED;
+    }
+    UkfParams kp;
+    kp.st = st;
+    kp.in = in;
+    kp.fp.pi = cfg.pi;
+    kp.fp.thresh = cfg.min_dist_thresh;
+    kp.fp.occ = cfg.min_landmark_occ;
+    kp.fp.cap = cfg.max_state_dim;
+    kp.fp.wrange = st.wrange;
+    kp.fp.wbearing = st.wbearing;
+    kp.fp.whits = st.whits;
+    kp.kq = (double)cfg.ukf_kq;
+    kp.kr = (double)cfg.ukf_kr;
+    kp.kp_lm = (double)cfg.ukf_kp_landmark_pose;
+    kp.std_a = cfg.ukf_std_a;
+    kp.std_yaw = cfg.ukf_std_yaw;
+    const size_t smem = sizeof(UkfSlot);
+    static bool attr_set = false;
+    if (!attr_set) {
+        ASLAM_CUDA(cudaFuncSetAttribute(ukf_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    ukf_batched_kernel<<<st.batch, UTHREADS, smem, stream>>>(kp);
+    ASLAM_CUDA(cudaGetLastError());
+    return ASLAM_OK;
+}
+
+}  // namespace aslam

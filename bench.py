@@ -129,7 +129,7 @@ def cpu_leg(sample_filters, msgs, threads=0):
     O.build()
     lmx, lmy = A.map_cfg3()
     rp = A.Replay(lmx, lmy, sample_filters, msgs, seed0=A.replay.SEED_CFG3)
-    cfg = O.default_config(max_state_dim=64)
+    cfg = O.default_config(max_state_dim=36)
     nthr = threads or (os.cpu_count() or 1)
     sec, X, P, N = O.run_batch("ekf", cfg, sample_filters, msgs, L_CFG3, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt,
                                rp.range, rp.bearing, nthr, 36, want_P=False)
@@ -151,7 +151,7 @@ def reference_arm(args):
     lmx, lmy = A.map_cfg3()
     total_msgs = WARM_MSGS + (args.warmup + args.steps) * FUSE
     rp = A.Replay(lmx, lmy, sample, total_msgs, seed0=A.replay.SEED_CFG3)
-    cfg = O.default_config(max_state_dim=64)
+    cfg = O.default_config(max_state_dim=36)
     nthr = os.cpu_count() or 1
     # the oracle's batch runner starts every filter from reset: time the whole replay, subtract nothing,
     # and attribute the time to the timed steps in proportion to their messages (the warm-up messages
@@ -218,7 +218,7 @@ def batched_leg(args, torch, dist, rank, world, dev):
 
     results = {}
     for mode in ("resident", "e2e"):
-        f = A.BatchedFilter("ekf", B, dev.index, max_state_dim=64)
+        f = A.BatchedFilter("ekf", B, dev.index, max_state_dim=36)
         stream = torch.cuda.ExternalStream(f.stream, device=dev)
         xout = torch.empty((B, f.ld), dtype=torch.float64).pin_memory()
         run_resident(f, 0, WARM_MSGS)  # bring every filter to N = 35 (not timed)

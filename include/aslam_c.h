@@ -55,7 +55,7 @@ enum {
     ASLAM_ST_OBS_OVERFLOW = 1u << 4   /* more than ASLAM_MAX_OBS observations in one message */
 };
 
-#define ASLAM_MAX_WAIT 48u /* capacity of the per-filter new-landmark wait-list */
+#define ASLAM_MAX_WAIT 256u /* capacity of the per-filter new-landmark wait-list */
 #define ASLAM_MAX_OBS 64u  /* observations per filter per message */
 #define ASLAM_BATCH_MAX_DIM 64 /* largest max_state_dim the batched kernels accept */
 

@@ -1,0 +1,61 @@
+"""Parity of the batched UKF CUDA path (through the C ABI) against the CPU oracle: config 2 of
+BASELINE.json (single UKF-SLAM filter, landmarks.yaml map, 1000 messages) and a small batch.
+
+FP64 tolerance 1e-9 (norm-wise, X and P); N, association, wait-list and the LLT-failure column
+(Eigen's silent half-factored L, ukf.cpp:280) must be EQUAL at every step."""
+import numpy as np
+import pytest
+
+from test_ekf_batched_gpu import _run_single
+from util import TOL_F64, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+def test_cfg2_single_ukf_1000_steps(aslam, orc):
+    # The reference UKF is chaotic once P - K S K' has gone indefinite (w0 < 0): free-running
+    # bit-level agreement with a CPU whose libm differs in the last bit of sin/cos/atan2 cannot last 1000
+    # steps. Contract: every step <= 1e-9 and all integer outputs equal, with at most 25 float-cast-flip
+    # re-synchronisations (each <= 1e-5), which are counted and printed.
+    worst, o = _run_single(aslam, orc, "ukf", 1000, resync_budget=25)
+    print("cfg2 worst relerr", {k: v for k, v in worst.items() if k != "resyncs"}, "final N", o.N,
+          "resyncs", [(t, "%.1e" % max(a, b)) for t, a, b in worst["resyncs"]])
+
+
+def test_ukf_stationary_other_seed(aslam, orc):
+    worst, o = _run_single(aslam, orc, "ukf", 120, seed=5, warm=120, resync_budget=3)
+    print("stationary worst relerr", worst, "final N", o.N)
+
+
+def test_ukf_batch_of_filters(aslam, orc):
+    """32 UKF filters x 60 messages in ONE launch (state stays in shared memory between messages)."""
+    lmx, lmy = aslam.map_cfg1()
+    B, T, L = 32, 60, 8
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=77)
+    f = aslam.BatchedFilter("ukf", B, 0)
+    f.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+    s = f.get_state()
+    fails = f.get_llt_fail()
+    blips = []
+    for b in range(B):
+        o = orc.Filter("ukf")
+        for t in range(T):
+            o.set_observations(rp.range[t, b], rp.bearing[t, b])
+            o.step(rp.x[t, b], rp.y[t, b], rp.yaw[t, b], rp.vx[t, b], rp.az[t, b], rp.dt[t, b])
+        X, Z, P = o.state()
+        n = o.N
+        assert int(s["N"][b]) == n
+        assert int(fails[b]) == o.llt_fail()
+        e = max(relerr(s["X"][b, :n], X), relerr(s["P"][b, :n, :n], P))
+        if e > TOL_F64:
+            blips.append((b, e))
+    print("UKF batch: filters beyond 1e-9 after 60 free-running messages:", blips)
+    # free-running for 60 messages: at most 2 of the 32 filters may have taken a float-cast flip (<= 1e-5)
+    assert len(blips) <= 2 and all(e <= 1e-5 for _, e in blips)
+    f.close()
+
+
+def test_ukf_cap_above_reference_is_refused(aslam):
+    with pytest.raises(aslam.capi.AslamError) as e:
+        aslam.BatchedFilter("ukf", 1, 0, max_state_dim=64)
+    assert e.value.status == aslam.capi.ASLAM_ERR_UNSUPPORTED
