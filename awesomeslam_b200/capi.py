@@ -108,6 +108,10 @@ SIGNATURES = {
     "aslam_large_launch_count": (C.c_uint64, [_vp]),
     "aslam_large_last_kernel_ms": (_i32, [_vp, C.POINTER(_f32)]),
     "aslam_large_status": (_i32, [_vp, C.POINTER(_u32), C.POINTER(_i32)]),
+    "aslam_dense_gemm_nt": (_i32, [_vp, _i32, _i32, _i32, _vp, _sz, _vp, _sz, _vp, _sz, _f64, _f64, _i32]),
+    "aslam_dense_cholesky": (_i32, [_vp, _vp, _sz, _i32, _vp, _vp]),
+    "aslam_dense_trsm": (_i32, [_vp, _vp, _sz, _i32, _vp, _sz, _i32, _vp]),
+    "aslam_probe_dmma_tflops": (_i32, [_i32, C.POINTER(_f64)]),
     "aslam_replay_generate": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, _f64, _f64, C.c_uint64, _u32,
                                      _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }

@@ -7,6 +7,7 @@
 #include <new>
 #include <vector>
 
+#include "dense_fp64.hpp"
 #include "large.hpp"
 
 namespace aslam {
@@ -242,6 +243,35 @@ aslam_status aslam_large_status(aslam_large* h, uint32_t* status, int32_t* llt_f
     }
     if (llt_fail) *llt_fail = -1;
     return ASLAM_OK;
+}
+
+aslam_status aslam_dense_gemm_nt(void* stream, int32_t M, int32_t N, int32_t K, const double* d_A, size_t lda,
+                                 const double* d_B, size_t ldb, double* d_C, size_t ldc, double alpha, double beta,
+                                 int32_t lower_only) {
+    if (!d_A || !d_B || !d_C) return ASLAM_ERR_ARG;
+    dense::Epilogue e;
+    e.alpha = alpha;
+    e.beta = beta;
+    e.lower_only = lower_only != 0;
+    return dense::dgemm_nt((cudaStream_t)stream, M, N, K, d_A, lda, d_B, ldb, d_C, ldc, e, nullptr);
+}
+
+aslam_status aslam_dense_cholesky(void* stream, double* d_A, size_t ld, int32_t n, double* d_inv_blocks,
+                                  int32_t* d_fail) {
+    if (!d_A || !d_inv_blocks || !d_fail || n <= 0) return ASLAM_ERR_ARG;
+    return dense::cholesky_lower((cudaStream_t)stream, d_A, ld, n, d_inv_blocks, d_fail, nullptr);
+}
+
+aslam_status aslam_dense_trsm(void* stream, double* d_B, size_t ldb, int32_t m, const double* d_L, size_t ldl,
+                              int32_t n, const double* d_inv_blocks) {
+    if (!d_B || !d_L || !d_inv_blocks) return ASLAM_ERR_ARG;
+    return dense::trsm_right_lower_t((cudaStream_t)stream, d_B, ldb, m, d_L, ldl, n, d_inv_blocks, nullptr);
+}
+
+aslam_status aslam_probe_dmma_tflops(int32_t device, double* tflops) {
+    if (!tflops) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(device));
+    return dense::probe_dmma_tflops(tflops);
 }
 
 }  // extern "C"

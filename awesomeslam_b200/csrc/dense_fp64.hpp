@@ -1,0 +1,56 @@
+// FP64 dense building blocks of the large-map UKF (kernels K6, K8, K9): the contractions
+// the reference runs as Eigen products / rank-1 loops / LLT / inverse (src/ukf/ukf.cpp:280, 307-391).
+// All matrices are ROW-major with the contraction index contiguous ("NT" form): every product is
+//     C[i][j] = alpha * sum_k A[i][k] * B[j][k]  (+ beta * C[i][j])  (+ r1 * u[i] * v[j])  (+ diag[i] if i == j)
+// Tiles are moved by TMA (cp.async.bulk.tensor.2d, SASS UTMALDG) into a 4-stage shared-memory ring by a dedicated
+// producer warp and contracted on the FP64 tensor pipe (mma.sync m8n8k4 f64, SASS DMMA.8x8x4) -- tcgen05 has no
+// FP64 kind, DMMA is the FP64 tensor path of sm_100a.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "internal.hpp"
+
+namespace aslam {
+namespace dense {
+
+constexpr int CHOL_BS = 64;  // block size of the blocked Cholesky / triangular solves
+
+struct Epilogue {
+    double alpha = 1.0, beta = 0.0;
+    const double* u = nullptr;     // rank-1 term r1 * u[i] * v[j] (u indexed by the row of C, v by its column)
+    const double* v = nullptr;
+    double r1 = 0.0;
+    const double* diag = nullptr;  // added to C[i][i]
+    bool lower_only = false;       // skip tiles that lie entirely above the diagonal
+};
+
+// C (M x N, ldc) = alpha * A (M x K, lda) * B (N x K, ldb)' + ...   Base pointers 16-byte aligned, ld even.
+// Returns the number of kernels launched through *launches (may be null).
+aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, size_t lda, const double* B, size_t ldb,
+                      double* C, size_t ldc, const Epilogue& e, uint64_t* launches);
+
+// In-place blocked Cholesky of the lower triangle of A (n x n, row-major, ld): A <- L with L L' = A. The strict
+// upper triangle is left with unspecified values. inv_blocks [ceil(n/64)][64*64] receives the inverse of every
+// 64 x 64 diagonal block of L (row-major, pitch 64). *d_fail (device int, must hold -1 on entry) receives the
+// index of the first non-positive pivot (Eigen's LLT would stop there, ukf.cpp:280); the factorisation carries on
+// with unspecified values after it.
+aslam_status cholesky_lower(cudaStream_t st, double* A, size_t ld, int n, double* inv_blocks, int* d_fail,
+                            uint64_t* launches);
+
+// B (m x n, ldb) <- B * L^-T for the lower-triangular L (n x n, ldl) whose diagonal-block inverses are inv_blocks.
+aslam_status trsm_right_lower_t(cudaStream_t st, double* B, size_t ldb, int m, const double* L, size_t ldl, int n,
+                                const double* inv_blocks, uint64_t* launches);
+
+// v (n) <- L^-1 v (forward substitution with the same blocked data), one CTA.
+aslam_status trsv_lower(cudaStream_t st, double* v, const double* L, size_t ldl, int n, const double* inv_blocks,
+                        uint64_t* launches);
+
+// A[j][i] <- A[i][j] for i > j.
+aslam_status symmetrize_from_lower(cudaStream_t st, double* A, size_t ld, int n, uint64_t* launches);
+
+// Measured throughput of the DMMA pipe of the current device, TFLOP/s (roofline denominator for the GEMMs).
+aslam_status probe_dmma_tflops(double* tflops);
+
+}  // namespace dense
+}  // namespace aslam

@@ -1,0 +1,307 @@
+// FP64 "NT" GEMM for the large-map UKF (dense_fp64.hpp): TMA tile loads + DMMA.
+//
+// CTA tile BM x BN, K walked in slabs of BK = 16 doubles (128 bytes per row: one TMA box per operand per slab).
+// Warp NW (the last one) is the producer: one lane waits for a free stage (empty mbarrier), arms the full
+// mbarrier with the slab's byte count and issues the two cp.async.bulk.tensor.2d loads; out-of-range rows and the K
+// tail are zero-filled by the TMA unit, so the main loop has no edge cases. Warps 0..NW-1 own 32 x WN sub-tiles:
+// per slab each lane fetches its A and B fragments with 16-byte shared loads (two consecutive k per load: the
+// contraction index is permuted identically for A and B, which a dot product does not care about) and issues
+// mma.sync.m8n8k4.f64; when a warp is done with a stage it arrives on the empty mbarrier. No CTA-wide barrier in
+// the loop. The accumulators (WM/8 x WN/8 x 2 doubles per lane) are written once, with the fused epilogue
+//     C = alpha * acc + beta * C + r1 * u[i] v[j] + (i == j) diag[i].
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <mutex>
+
+#include "bulk_copy.cuh"
+#include "dense_fp64.hpp"
+
+namespace aslam {
+namespace dense {
+
+namespace {
+
+constexpr int BK = 16;
+constexpr int NST = 4;
+
+struct GemmParams {
+    double* C;
+    size_t ldc;
+    int M, N, K;
+    double alpha, beta, r1;
+    const double* u;
+    const double* v;
+    const double* diag;
+    int lower_only;
+};
+
+__device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* map, int c_inner, int c_outer,
+                                            uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+            bulk::smem_u32(dst_smem)),
+        "l"(map), "r"(c_inner), "r"(c_outer), "r"(bulk::smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bulk::smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+struct Geo {
+    static constexpr int NW = WARPS_M * WARPS_N;
+    static constexpr int THREADS = (NW + 1) * 32;
+    static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
+    static constexpr int MI = WM / 8, NI = WN / 8;
+    static constexpr size_t A_BYTES = (size_t)BM * BK * sizeof(double);
+    static constexpr size_t B_BYTES = (size_t)BN * BK * sizeof(double);
+    static constexpr size_t STAGE = A_BYTES + B_BYTES;
+    static constexpr size_t SMEM = NST * STAGE + 2 * NST * sizeof(uint64_t) + 128;
+    static_assert(WM % 8 == 0 && WN % 8 == 0, "warp tile must be a multiple of the 8 x 8 mma tile");
+};
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(Geo<BM, BN, WARPS_M, WARPS_N>::THREADS, 1)
+dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+    using G = Geo<BM, BN, WARPS_M, WARPS_N>;
+    extern __shared__ unsigned char smem_dyn[];
+    // 128-byte aligned base for the TMA destinations
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 127) & ~(uintptr_t)127);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + NST * G::STAGE);
+    uint64_t* empty = full + NST;
+    const int bm = blockIdx.y, bn = blockIdx.x;
+    const int row0 = bm * BM, col0 = bn * BN;
+    if (p.lower_only && row0 + BM - 1 < col0) return;  // tile entirely above the diagonal
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int KT = (p.K + BK - 1) / BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NST; ++s) {
+            bulk::mbar_init(&full[s], 1);
+            bulk::mbar_init(&empty[s], G::NW);
+        }
+        bulk::fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == G::NW) {  // ---------------- producer
+        if (lane == 0) {
+            for (int kt = 0; kt < KT; ++kt) {
+                const int st = kt % NST;
+                if (kt >= NST) bulk::mbar_wait(&empty[st], ((kt / NST) - 1) & 1);
+                bulk::mbar_expect_tx(&full[st], (uint32_t)G::STAGE);
+                unsigned char* sa = smem + st * G::STAGE;
+                tma_load_2d(sa, &tmA, kt * BK, row0, &full[st]);
+                tma_load_2d(sa + G::A_BYTES, &tmB, kt * BK, col0, &full[st]);
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumers
+    const int wm = (warp / WARPS_N) * G::WM, wn = (warp % WARPS_N) * G::WN;
+    const int g = lane >> 2, t = lane & 3;
+    double acc[G::MI][G::NI][2];
+#pragma unroll
+    for (int mi = 0; mi < G::MI; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < G::NI; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+
+    for (int kt = 0; kt < KT; ++kt) {
+        const int st = kt % NST;
+        bulk::mbar_wait(&full[st], (kt / NST) & 1);
+        const double* As = reinterpret_cast<const double*>(smem + st * G::STAGE);
+        const double* Bs = reinterpret_cast<const double*>(smem + st * G::STAGE + G::A_BYTES);
+#pragma unroll
+        for (int kg = 0; kg < BK / 8; ++kg) {
+            double2 a[G::MI], b[G::NI];
+#pragma unroll
+            for (int mi = 0; mi < G::MI; ++mi)
+                a[mi] = *reinterpret_cast<const double2*>(As + (wm + mi * 8 + g) * BK + kg * 8 + 2 * t);
+#pragma unroll
+            for (int ni = 0; ni < G::NI; ++ni)
+                b[ni] = *reinterpret_cast<const double2*>(Bs + (wn + ni * 8 + g) * BK + kg * 8 + 2 * t);
+#pragma unroll
+            for (int mi = 0; mi < G::MI; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < G::NI; ++ni) {
+                    dmma(acc[mi][ni][0], acc[mi][ni][1], a[mi].x, b[ni].x);
+                    dmma(acc[mi][ni][0], acc[mi][ni][1], a[mi].y, b[ni].y);
+                }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[st]);
+    }
+
+    // ---------------- epilogue
+    const bool has_beta = p.beta != 0.0;
+#pragma unroll
+    for (int mi = 0; mi < G::MI; ++mi) {
+        const int r = row0 + wm + mi * 8 + g;
+        if (r >= p.M) continue;
+        const double ur = p.u ? p.r1 * p.u[r] : 0.0;
+        double* crow = p.C + (size_t)r * p.ldc;
+#pragma unroll
+        for (int ni = 0; ni < G::NI; ++ni) {
+            const int c = col0 + wn + ni * 8 + 2 * t;
+            if (c >= p.N) continue;
+            const bool two = c + 1 < p.N;
+            double o0 = p.alpha * acc[mi][ni][0], o1 = p.alpha * acc[mi][ni][1];
+            if (has_beta) {
+                if (two) {
+                    const double2 old = *reinterpret_cast<const double2*>(crow + c);
+                    o0 = fma(p.beta, old.x, o0);
+                    o1 = fma(p.beta, old.y, o1);
+                } else {
+                    o0 = fma(p.beta, crow[c], o0);
+                }
+            }
+            if (p.u) {
+                o0 = fma(ur, p.v[c], o0);
+                if (two) o1 = fma(ur, p.v[c + 1], o1);
+            }
+            if (p.diag) {
+                if (c == r) o0 += p.diag[r];
+                if (c + 1 == r) o1 += p.diag[r];
+            }
+            if (two)
+                *reinterpret_cast<double2*>(crow + c) = make_double2(o0, o1);
+            else
+                crow[c] = o0;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------- tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+// rows x K matrix, row pitch ld doubles, box = box_rows x BK
+bool make_map(CUtensorMap* m, const double* base, int rows, int K, size_t ld, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled is not available from the driver");
+        return false;
+    }
+    const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)ld * sizeof(double)};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(base), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + "): rows " + std::to_string(rows) + " K " +
+                  std::to_string(K) + " ld " + std::to_string(ld));
+        return false;
+    }
+    return true;
+}
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+aslam_status launch(cudaStream_t st, const double* A, size_t lda, const double* B, size_t ldb, const GemmParams& p) {
+    using G = Geo<BM, BN, WARPS_M, WARPS_N>;
+    static bool attr = false;
+    if (!attr) {
+        ASLAM_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
+        attr = true;
+    }
+    CUtensorMap ta, tb;
+    if (!make_map(&ta, A, p.M, p.K, lda, BM) || !make_map(&tb, B, p.N, p.K, ldb, BN)) return ASLAM_ERR_CUDA;
+    dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
+    dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N><<<grid, G::THREADS, G::SMEM, st>>>(ta, tb, p);
+    ASLAM_CUDA(cudaGetLastError());
+    return ASLAM_OK;
+}
+
+}  // namespace
+
+aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, size_t lda, const double* B, size_t ldb,
+                      double* C, size_t ldc, const Epilogue& e, uint64_t* launches) {
+    if (M <= 0 || N <= 0 || K <= 0) return ASLAM_OK;
+    if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(C)) & 15u ||
+        (lda & 1u) || (ldb & 1u) || (ldc & 1u)) {
+        set_error("dgemm_nt: operands must be 16-byte aligned with even leading dimensions");
+        return ASLAM_ERR_ARG;
+    }
+    GemmParams p;
+    p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K;
+    p.alpha = e.alpha; p.beta = e.beta; p.r1 = e.r1; p.u = e.u; p.v = e.v; p.diag = e.diag;
+    p.lower_only = e.lower_only ? 1 : 0;
+    if (launches) ++*launches;
+    // tile shape: 128 x 128 when that still fills the 148 SMs about twice, else 128 x 64; narrow N -> 128 x 64
+    const long tiles128 = (long)((M + 127) / 128) * ((N + 127) / 128) / (e.lower_only ? 2 : 1);
+    if (N > 64 && tiles128 >= 280) return launch<128, 128, 4, 2>(st, A, lda, B, ldb, p);
+    return launch<128, 64, 4, 2>(st, A, lda, B, ldb, p);
+}
+
+// ---------------------------------------------------------------------------------- DMMA pipe probe
+namespace {
+__global__ void dmma_probe_kernel(double* out, int iters) {
+    double c[8][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = 0.0;
+    const double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dmma(c[i][0], c[i][1], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += c[i][0] + c[i][1];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+}  // namespace
+
+aslam_status probe_dmma_tflops(double* tflops) {
+    int dev = 0, sms = 0;
+    ASLAM_CUDA(cudaGetDevice(&dev));
+    ASLAM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int threads = 256, blocks = sms * 4, iters = 4096;
+    double* d = nullptr;
+    ASLAM_CUDA(cudaMalloc(&d, (size_t)threads * blocks * sizeof(double)));
+    cudaEvent_t e0, e1;
+    ASLAM_CUDA(cudaEventCreate(&e0));
+    ASLAM_CUDA(cudaEventCreate(&e1));
+    dmma_probe_kernel<<<blocks, threads>>>(d, 64);
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        ASLAM_CUDA(cudaEventRecord(e0));
+        dmma_probe_kernel<<<blocks, threads>>>(d, iters);
+        ASLAM_CUDA(cudaEventRecord(e1));
+        ASLAM_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ASLAM_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (ms < best) best = ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    const double flops = (double)blocks * (threads / 32) * (double)iters * 8.0 * 512.0;  // 8x8x4 mma = 512 flop
+    *tflops = flops / (best * 1e-3) / 1e12;
+    return ASLAM_OK;
+}
+
+}  // namespace dense
+}  // namespace aslam

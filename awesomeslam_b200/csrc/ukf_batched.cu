@@ -52,32 +52,6 @@ struct UkfParams {
     float std_a, std_yaw;
 };
 
-// common.h:46-75 for one (augmented) sigma point: rows 0..2 of the column; `na` = point(N).
-__device__ __forceinline__ void motion_model_aug(double& x, double& y, double& th, double na, float vx, float az,
-                                                 float dt) {
-    const double th0 = th;
-    double s0, c0;
-    sincos(th0, &s0, &c0);
-    const float azdt = __fmul_rn(az, dt);
-    if (fabs((double)az) > 0.001) {
-        const float r = __fdiv_rn(vx, az);
-        double s1, c1;
-        sincos(__dadd_rn(th0, (double)azdt), &s1, &c1);
-        x = __dadd_rn(x, __dmul_rn((double)r, __dadd_rn(-s0, s1)));
-        y = __dadd_rn(y, __dmul_rn((double)r, __dsub_rn(c0, c1)));
-    } else {
-        const float vxdt = __fmul_rn(vx, dt);
-        x = __dadd_rn(x, __dmul_rn((double)vxdt, c0));
-        y = __dadd_rn(y, __dmul_rn((double)vxdt, s0));
-    }
-    th = __dadd_rn(th0, (double)azdt);
-    // common.h:69-71: 0.5 * dt * dt * point(N) * cos(point(2)), all double, left to right
-    const double h = __dmul_rn(__dmul_rn(0.5, (double)dt), (double)dt);
-    x = __dadd_rn(x, __dmul_rn(__dmul_rn(h, na), c0));
-    y = __dadd_rn(y, __dmul_rn(__dmul_rn(h, na), s0));
-    th = __dadd_rn(th, __dmul_rn(h, (double)az));  // `az`, not point(N+1), as written
-}
-
 __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams kp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     UkfSlot& s = *reinterpret_cast<UkfSlot*>(smem_raw);

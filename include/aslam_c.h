@@ -211,6 +211,25 @@ aslam_status aslam_large_last_kernel_ms(aslam_large* h, float* ms);
 /* status bits of the filter (ASLAM_ST_*), and for the UKF the first failing LLT pivot or -1. */
 aslam_status aslam_large_status(aslam_large* h, uint32_t* status, int32_t* llt_fail);
 
+/* ---------------------------------------------------------------- FP64 dense blocks ------- */
+/* The contractions of the large-map UKF (ukf.cpp:280, 307-391: Eigen LLT, rank-1 sums, inverse) as stand-alone
+ * calls on DEVICE pointers, enqueued on `stream` (a cudaStream_t, NULL = default stream). Row-major, contraction
+ * index contiguous; pointers 16-byte aligned, leading dimensions even.
+ *   gemm_nt : C[i][j] = alpha sum_k A[i][k] B[j][k] + beta C[i][j]   (lower_only: skip tiles above the diagonal)
+ *   cholesky: A <- L (lower, in place; strict upper triangle unspecified); inv_blocks [ceil(n/64)][4096] doubles;
+ *             d_fail: device int, first non-positive pivot or -1
+ *   trsm    : B <- B L^-T with the inv_blocks of cholesky
+ * Exported for the parity tests and the tensor-pipe roofline; the filters call the same code internally. */
+aslam_status aslam_dense_gemm_nt(void* stream, int32_t M, int32_t N, int32_t K, const double* d_A, size_t lda,
+                                 const double* d_B, size_t ldb, double* d_C, size_t ldc, double alpha, double beta,
+                                 int32_t lower_only);
+aslam_status aslam_dense_cholesky(void* stream, double* d_A, size_t ld, int32_t n, double* d_inv_blocks,
+                                  int32_t* d_fail);
+aslam_status aslam_dense_trsm(void* stream, double* d_B, size_t ldb, int32_t m, const double* d_L, size_t ldl,
+                              int32_t n, const double* d_inv_blocks);
+/* Measured throughput of the FP64 tensor pipe (DMMA) of `device`, TFLOP/s. */
+aslam_status aslam_probe_dmma_tflops(int32_t device, double* tflops);
+
 /* ---------------------------------------------------------------- synthetic replay ------- */
 /* Deterministic replay generator of SURVEY.md sec. 8d (host code, no GPU needed):
  * map (lm_x, lm_y)[L]; `warm` stationary steps then vx, az constant, dt = 1.0f;

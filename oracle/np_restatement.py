@@ -386,3 +386,89 @@ class UkfNp(_Front):
         dz = self._wrap(self.Z - Zp)
         self.X = X + K @ dz
         self.P = P - K @ S @ K.T
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Vectorised form of one UKF message for LARGE maps (cfg5: n = 2051 finishes in seconds instead of minutes). Same
+# formulas as UkfNp (ukf.cpp:113-180, 260-392) with the per-sigma-point loops written as matrix operations; the
+# map does not grow (unmatched observations are reported as -1 and dropped). tests/test_oracle.py checks it against
+# the loop form above at a size both can run.
+def normalize_angle_vec(theta):
+    t = np.asarray(theta, np.float64).astype(np.float32)
+    two_pi = f32(2) * PI
+    r = np.fmod(t, two_pi).astype(np.float32)
+    r = np.where(r > PI, (r - two_pi).astype(np.float32), r)
+    r = np.where(r < -PI, (r + two_pi).astype(np.float32), r)
+    return r.astype(np.float64)
+
+
+def ukf_large_step(X, Z, P, ox, oy, yaw, vx, az, dt, rng, brg):
+    """Returns (X', Z', P', assoc, llt_fail). P indexed [i, j]."""
+    X = np.array(X, np.float64)
+    Z = np.array(Z, np.float64)
+    N = X.size
+    Z[0], Z[1], Z[2] = ox, oy, float(f32(yaw))
+    lmx32 = X[3::2].astype(np.float32).astype(np.float64)
+    lmy32 = X[4::2].astype(np.float32).astype(np.float64)
+    assoc = []
+    for r, b in zip(rng, brg):
+        r, b = f32(r), normalize_angle(b)
+        px, py = to_point(r, b, Z)
+        dx = (px - lmx32).astype(np.float32)
+        dy = (py - lmy32).astype(np.float32)
+        d = np.sqrt((dx * dx).astype(np.float32) + (dy * dy).astype(np.float32)).astype(np.float32)
+        c = int(np.argmin(d))  # first minimum, as the strict `<` of ukf.cpp:144
+        if d[c] < MIN_DIST_THRESH:
+            Z[3 + 2 * c], Z[4 + 2 * c] = float(r), float(b)
+            assoc.append(2 * c)
+        else:
+            assoc.append(-1)
+    vx, az, dt = f32(vx), f32(az), f32(dt)
+    lam = f32(3.0 - (N + 2))
+    denom = f32(f32(lam + f32(N)) + f32(2))
+    wts = np.full(2 * N + 5, float(f32(0.5 / float(denom))))
+    wts[0] = float(f32(lam / denom))
+    NA, NS = N + 2, 2 * N + 5
+    Paug = np.zeros((NA, NA))
+    Paug[:N, :N] = P
+    Paug[N, N] = float(f32(UKF_STD_A * UKF_STD_A))
+    Paug[N + 1, N + 1] = float(f32(UKF_STD_YAW * UKF_STD_YAW))
+    try:
+        L = np.linalg.cholesky(Paug)
+        fail = -1
+    except np.linalg.LinAlgError:
+        L, fail = eigen_llt_lower(Paug)
+    w = float(f32(np.sqrt(denom)))
+    Xaug = np.concatenate([X, [0.0, 0.0]])
+    Xs = np.empty((NA, NS))
+    Xs[:, 0] = Xaug
+    Xs[:, 1:NA + 1] = Xaug[:, None] + w * L
+    Xs[:, NA + 1:] = Xaug[:, None] - w * L
+    Xp = Xs[:N].copy()
+    for i in range(NS):
+        col = np.concatenate([Xs[:3, i], np.zeros(N - 3), Xs[N:, i]])  # f only reads rows 0..2 and N
+        Xp[:3, i] = state_transition(N, col, vx, az, dt)[:3]
+    Xp[2] = normalize_angle_vec(Xp[2])
+    mean = Xp @ wts
+    D = Xp - mean[:, None]
+    D[2] = normalize_angle_vec(D[2])
+    Q = np.zeros(N)
+    Q[:3] = float(UKF_KQ)
+    Pp = (D * wts) @ D.T + np.diag(Q)
+    Zs = Xp.copy()
+    dx = Xp[3::2] - Xp[0]
+    dy = Xp[4::2] - Xp[1]
+    Zs[3::2] = np.sqrt(dx * dx + dy * dy)
+    Zs[4::2] = np.arctan2(dy, dx) - Xp[2]
+    Zp = Zs @ wts
+    Zp[2::2] = normalize_angle_vec(Zp[2::2])
+    DZ = Zs - Zp[:, None]
+    DZ[2::2] = normalize_angle_vec(DZ[2::2])
+    S = (DZ * wts) @ DZ.T + np.eye(N) * float(UKF_KR)
+    Tc = (D * wts) @ DZ.T
+    K = np.linalg.solve(S.T, Tc.T).T
+    dz = Z - Zp
+    dz[2::2] = normalize_angle_vec(dz[2::2])
+    Xn = mean + K @ dz
+    Pn = Pp - K @ S @ K.T
+    return Xn, Z, Pn, np.array(assoc, np.int32), fail

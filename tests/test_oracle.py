@@ -214,3 +214,27 @@ def test_ukf_weights_are_float_values(orc):
     assert u.w[0] == -6.0 and u.w[1] == float(np.float32(0.5 / 3.0))  # lambda = 3 - 21 = -18
     u._weights(17)
     assert u.w[0] == float(np.float32(-16.0) / np.float32(3.0)) and math.isclose(u.w[0], -5.3333335, rel_tol=1e-7)
+
+
+def test_vectorised_large_ukf_step_matches_oracle(orc):
+    """oracle/np_restatement.ukf_large_step (the full-size cfg5 checker of the GPU tests) against the C++ oracle's
+    verbatim UKFSlam::slam at n = 35 (unblocked LLT regime) and n = 131 (blocked)."""
+    import awesomeslam_b200 as A
+    from oracle import np_restatement as R
+    for side, pitch in ((4, 3.0), (8, 2.0)):
+        tx, ty, X0, G, d = A.large_map_state(side, pitch=pitch)
+        P0 = A.dense_P(G, d)
+        n = X0.size
+        rng, brg, idx = A.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8)
+        Z0 = R.measurement(n, X0)
+        odom = (0.01, -0.01, 0.002, 0.05, 0.1, 1.0)
+        o = orc.Filter("ukf", max_state_dim=100000)
+        o.load_state(X0, Z0, P0)
+        X, Z, P = X0, Z0, P0
+        for step in range(2):
+            X, Z, P, assoc, fail = R.ukf_large_step(X, Z, P, *odom, rng, brg)
+            o.set_observations(rng, brg)
+            o.step(*odom)
+            Xo, Zo, Po = o.state()
+            assert np.array_equal(assoc, o.assoc()) and fail == o.llt_fail() == -1
+            assert relerr(X, Xo) < 1e-11 and relerr(P, Po) < 1e-11 and relerr(Z, Zo) < 1e-15, (n, step)
