@@ -53,24 +53,19 @@ __global__ void __launch_bounds__(256) chol_panel_kernel(double* A, size_t ld, i
         if (j <= i) A[(size_t)i * ld + j] = s[i][j];
     }
     // inverse: column c of inv(L) by forward substitution, 4 lanes per column splitting the inner sum
+    // (every lane runs the same trip count: the shuffles are full-warp)
     const int c = tid >> 2, part = tid & 3;
-    if (c < bs) {
-        if (part == 0) si[c][c] = 1.0 / s[c][c];
-        __syncwarp();
-        for (int i = c + 1; i < bs; ++i) {
-            double sum = 0.0;
+    if (c < bs && part == 0) si[c][c] = 1.0 / s[c][c];
+    __syncwarp();
+    for (int i = 1; i < bs; ++i) {
+        const bool act = c < bs && i > c;
+        double sum = 0.0;
+        if (act)
             for (int j = c + part; j < i; j += 4) sum = fma(s[i][j], si[j][c], sum);
-            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-            if (part == 0) si[i][c] = -sum / s[i][i];
-            __syncwarp();
-        }
-    } else {
-        for (int i = 0; i < bs; ++i) {  // keep the warp's shuffles convergent for bs < 64
-            __shfl_xor_sync(0xffffffffu, 0.0, 1);
-            __shfl_xor_sync(0xffffffffu, 0.0, 2);
-            __syncwarp();
-        }
+        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+        if (act && part == 0) si[i][c] = -sum / s[i][i];
+        __syncwarp();
     }
     __syncthreads();
     for (int idx = tid; idx < BS * BS; idx += 256) {

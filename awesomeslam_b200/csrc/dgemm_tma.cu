@@ -6,7 +6,7 @@
 // tail are zero-filled by the TMA unit, so the main loop has no edge cases. Warps 0..NW-1 own 32 x WN sub-tiles:
 // per slab each lane fetches its A and B fragments with 16-byte shared loads (two consecutive k per load: the
 // contraction index is permuted identically for A and B, which a dot product does not care about) and issues
-// mma.sync.m8n8k4.f64; when a warp is done with a stage it arrives on the empty mbarrier. No CTA-wide barrier in
+// mma.sync.m8n8k4.f64; a warp releases a stage (arrives on its empty mbarrier) once it has moved on to the next slab. No CTA-wide barrier in
 // the loop. The accumulators (WM/8 x WN/8 x 2 doubles per lane) are written once, with the fused epilogue
 //     C = alpha * acc + beta * C + r1 * u[i] v[j] + (i == j) diag[i].
 #include <cuda.h>
@@ -70,9 +70,10 @@ template <int BM, int BN, int WARPS_M, int WARPS_N>
 __global__ void __launch_bounds__(Geo<BM, BN, WARPS_M, WARPS_N>::THREADS, 1)
 dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
     using G = Geo<BM, BN, WARPS_M, WARPS_N>;
-    extern __shared__ unsigned char smem_dyn[];
-    // 128-byte aligned base for the TMA destinations
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 127) & ~(uintptr_t)127);
+    // TMA destinations need 128-byte alignment; the kernel has no static shared memory, so the dynamic window starts
+    // at the (1024-byte aligned) base of the CTA's shared memory. No pointer arithmetic through integers here: the
+    // fragment loads must stay in the shared address space (LDS), not become generic loads.
+    extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + NST * G::STAGE);
     uint64_t* empty = full + NST;
     const int bm = blockIdx.y, bn = blockIdx.x;
@@ -116,6 +117,11 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     for (int kt = 0; kt < KT; ++kt) {
         const int st = kt % NST;
         bulk::mbar_wait(&full[st], (kt / NST) & 1);
+        // Release the PREVIOUS stage here, behind the spin loop: every mma of slab kt-1 was issued before the loop, and an
+        // mma cannot issue until the shared loads feeding it have returned, so the stage is no longer being read.
+        // (Arriving at the end of the slab's own iteration is wrong: ptxas hoists the arrive above the DMMAs -- there is
+        // no register dependence -- and the TMA refill then races the loads still in flight.)
+        if (kt > 0 && lane == 0) mbar_arrive(&empty[(kt - 1) % NST]);
         const double* As = reinterpret_cast<const double*>(smem + st * G::STAGE);
         const double* Bs = reinterpret_cast<const double*>(smem + st * G::STAGE + G::A_BYTES);
 #pragma unroll
@@ -135,8 +141,6 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     dmma(acc[mi][ni][0], acc[mi][ni][1], a[mi].y, b[ni].y);
                 }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[st]);
     }
 
     // ---------------- epilogue
