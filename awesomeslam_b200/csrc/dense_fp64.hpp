@@ -21,6 +21,7 @@ struct Epilogue {
     const double* u = nullptr;     // rank-1 term r1 * u[i] * v[j] (u indexed by the row of C, v by its column)
     const double* v = nullptr;
     double r1 = 0.0;
+    const double* r1_dev = nullptr;  // when set, the coefficient is read from device memory instead of r1
     const double* diag = nullptr;  // added to C[i][i]
     bool lower_only = false;       // skip tiles that lie entirely above the diagonal
 };

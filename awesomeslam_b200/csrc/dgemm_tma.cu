@@ -33,6 +33,7 @@ struct GemmParams {
     const double* u;
     const double* v;
     const double* diag;
+    const double* r1_dev;
     int lower_only;
 };
 
@@ -145,11 +146,12 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
     // ---------------- epilogue
     const bool has_beta = p.beta != 0.0;
+    const double r1 = p.r1_dev ? *p.r1_dev : p.r1;
 #pragma unroll
     for (int mi = 0; mi < G::MI; ++mi) {
         const int r = row0 + wm + mi * 8 + g;
         if (r >= p.M) continue;
-        const double ur = p.u ? p.r1 * p.u[r] : 0.0;
+        const double ur = p.u ? r1 * p.u[r] : 0.0;
         double* crow = p.C + (size_t)r * p.ldc;
 #pragma unroll
         for (int ni = 0; ni < G::NI; ++ni) {
@@ -251,7 +253,7 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     }
     GemmParams p;
     p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K;
-    p.alpha = e.alpha; p.beta = e.beta; p.r1 = e.r1; p.u = e.u; p.v = e.v; p.diag = e.diag;
+    p.alpha = e.alpha; p.beta = e.beta; p.r1 = e.r1; p.u = e.u; p.v = e.v; p.diag = e.diag; p.r1_dev = e.r1_dev;
     p.lower_only = e.lower_only ? 1 : 0;
     if (launches) ++*launches;
     // tile shape: 128 x 128 when that still fills the 148 SMs about twice, else 128 x 64; narrow N -> 128 x 64

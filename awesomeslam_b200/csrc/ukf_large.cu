@@ -13,9 +13,13 @@
 //                                               one TMA + DMMA GEMM with the rank-1 term and Q fused into its epilogue
 //   Zsig = h(XsigPred_i), Zpred        :322-339 zsig_kernel, zdiff_kernel (wraps as written, float)
 //   S, Tc                              :342-375 two more GEMMs of the same kind (S lower tiles only)
-//   K = Tc S^-1; X += K dz; P -= K S K':378-391 S = Ls Ls' (Cholesky), W = Tc Ls^-T:  K S K' = W W',  K dz = W (Ls^-1 dz).
-//                                               Mathematically identical; avoids forming S^-1 and K. S must be positive
-//                                               definite (status bit ASLAM_ST_LLT_FAILED otherwise).
+//   K = Tc S^-1; X += K dz; P -= K S K':378-391 w_0 = (1-N)/3 << 0 makes S INDEFINITE for large maps (the reference does not
+//                                               care: S.inverse() is an LU). S = M + c u u' with M = wc DZ DZ' + R positive
+//                                               definite, c = w0 - wc, u = dz_0, so with M = Lm Lm' (Cholesky), W = Tc Lm^-T,
+//                                               a = Lm^-1 u, b = Lm^-1 dz, g = W a, den = 1 + c a.a (Sherman-Morrison):
+//                                                 K S K' = Tc S^-1 Tc' = W W' - (c/den) g g'
+//                                                 K dz   = Tc S^-1 dz  = W b  - (c/den) (a.b) g
+//                                               Identical in exact arithmetic; no S^-1, no K, no pivoting.
 // All matrices are row-major with the contraction index contiguous. P is kept exactly symmetric (lower triangle
 // computed, then mirrored); the reference's P is symmetric to rounding.
 #include <cuda_runtime.h>
@@ -46,7 +50,9 @@ struct UkfLarge {
     double* zpred = nullptr;   // [n]
     double* d0 = nullptr;      // [n] column 0 of D
     double* dz0 = nullptr;     // [n] column 0 of DZ
-    double* dzv = nullptr;     // [n] wrap(Z - Zpred), then Ls^-1 of it
+    double* dzv = nullptr;     // [n] wrap(Z - Zpred), then Lm^-1 of it
+    double* gvec = nullptr;    // [n] g = W Lm^-1 dz_0
+    double* coef = nullptr;    // [2] Sherman-Morrison scalars
     double* qdiag = nullptr;   // [n] diagonal of Q
     double* rdiag = nullptr;   // [n] diagonal of R
     double* invP = nullptr;    // [nb][64*64]
@@ -288,17 +294,46 @@ __global__ void __launch_bounds__(256) zdiff_kernel(SigmaArgs a, double* ZS, con
     }
 }
 
-// X = mean + W v (ukf.cpp:389 with K dz = W (Ls^-1 dz)); one warp per row. Flags non-finite results.
-__global__ void __launch_bounds__(256) state_update_kernel(int n, size_t ld, const double* W, const double* v,
-                                                          const double* mean, double* X, uint32_t* status) {
+// coef[0] = c / den, coef[1] = -(c / den) (a . b), den = 1 + c (a . a)  (Sherman-Morrison scalars). One CTA.
+__global__ void __launch_bounds__(256) sm_scalars_kernel(int n, const double* a, const double* b, double c, double* coef,
+                                                        uint32_t* status) {
+    __shared__ double sh[8];
+    double saa = 0.0, sab = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) {
+        saa = fma(a[i], a[i], saa);
+        sab = fma(a[i], b[i], sab);
+    }
+    const double taa = block_sum(saa, sh);
+    const double tab = block_sum(sab, sh);
+    if (threadIdx.x == 0) {
+        const double den = 1.0 + c * taa;
+        const double k = c / den;
+        coef[0] = k;
+        coef[1] = -k * tab;
+        if (!isfinite(k)) atomicOr(status, (uint32_t)ASLAM_ST_NONFINITE);
+    }
+}
+
+// g = W a;  X = mean + W b + coef[1] g  (ukf.cpp:389). One warp per row. Flags non-finite results.
+__global__ void __launch_bounds__(256) state_update_kernel(int n, size_t ld, const double* W, const double* a,
+                                                          const double* b, const double* coef, const double* mean,
+                                                          double* g, double* X, uint32_t* status) {
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= n) return;
     const double* wr = W + (size_t)row * ld;
-    double acc = 0.0;
-    for (int j = lane; j < n; j += 32) acc = fma(wr[j], v[j], acc);
-    for (int off = 16; off; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    double ga = 0.0, gb = 0.0;
+    for (int j = lane; j < n; j += 32) {
+        const double w = wr[j];
+        ga = fma(w, a[j], ga);
+        gb = fma(w, b[j], gb);
+    }
+    for (int off = 16; off; off >>= 1) {
+        ga += __shfl_xor_sync(0xffffffffu, ga, off);
+        gb += __shfl_xor_sync(0xffffffffu, gb, off);
+    }
     if (lane == 0) {
-        const double x = mean[row] + acc;
+        const double x = mean[row] + gb + coef[1] * ga;
+        g[row] = ga;
         X[row] = x;
         if (!isfinite(x)) atomicOr(status, (uint32_t)ASLAM_ST_NONFINITE);
     }
@@ -353,6 +388,8 @@ aslam_status large_ukf_create(aslam_large* h) {
     A((void**)&u->d0, n * sizeof(double));
     A((void**)&u->dz0, n * sizeof(double));
     A((void**)&u->dzv, n * sizeof(double));
+    A((void**)&u->gvec, n * sizeof(double));
+    A((void**)&u->coef, 2 * sizeof(double));
     A((void**)&u->qdiag, n * sizeof(double));
     A((void**)&u->rdiag, n * sizeof(double));
     A((void**)&u->invP, (size_t)nb * 64 * 64 * sizeof(double));
@@ -373,7 +410,7 @@ aslam_status large_ukf_create(aslam_large* h) {
 void large_ukf_destroy(aslam_large* h) {
     UkfLarge* u = static_cast<UkfLarge*>(h->ukf);
     if (!u) return;
-    void* ptrs[] = {u->Z, u->Lb, u->S, u->Tc, u->D, u->DZ, u->pose, u->mean, u->zpred, u->d0, u->dz0, u->dzv,
+    void* ptrs[] = {u->Z, u->Lb, u->S, u->Tc, u->D, u->DZ, u->pose, u->mean, u->zpred, u->d0, u->dz0, u->dzv, u->gvec, u->coef,
                     u->qdiag, u->rdiag, u->invP, u->invS, u->fail, u->status};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -468,32 +505,42 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     e.u = u->d0; e.v = u->d0; e.diag = u->qdiag;
     rc = dense::dgemm_nt(st, n, n, u->ns, u->D, u->nsld, u->D, u->nsld, h->P, u->ld, e, &nl);
     if (rc != ASLAM_OK) return rc;
-    e.u = u->dz0; e.v = u->dz0; e.diag = u->rdiag;
+    // M = wc DZ DZ' + R: the positive definite part of S (its rank-1 term c dz_0 dz_0' is applied analytically below)
+    e.u = nullptr; e.v = nullptr; e.r1 = 0.0; e.diag = u->rdiag;
     rc = dense::dgemm_nt(st, n, n, u->ns, u->DZ, u->nsld, u->DZ, u->nsld, u->S, u->ld, e, &nl);
     if (rc != ASLAM_OK) return rc;
     e.lower_only = false;
+    e.r1 = u->w0 - u->wc;
     e.u = u->d0; e.v = u->dz0; e.diag = nullptr;
     rc = dense::dgemm_nt(st, n, n, u->ns, u->D, u->nsld, u->DZ, u->nsld, u->Tc, u->ld, e, &nl);
     if (rc != ASLAM_OK) return rc;
-    // ---- S = Ls Ls';  W = Tc Ls^-T;  P -= W W';  X = mean + W (Ls^-1 dz)
+    // ---- M = Lm Lm';  W = Tc Lm^-T;  a = Lm^-1 dz_0;  b = Lm^-1 dz
     rc = dense::cholesky_lower(st, u->S, u->ld, n, u->invS, u->fail + 1, &nl);
     if (rc != ASLAM_OK) return rc;
     rc = dense::trsm_right_lower_t(st, u->Tc, u->ld, n, u->S, u->ld, n, u->invS, &nl);
     if (rc != ASLAM_OK) return rc;
+    rc = dense::trsv_lower(st, u->dz0, u->S, u->ld, n, u->invS, &nl);
+    if (rc != ASLAM_OK) return rc;
+    rc = dense::trsv_lower(st, u->dzv, u->S, u->ld, n, u->invS, &nl);
+    if (rc != ASLAM_OK) return rc;
+    sm_scalars_kernel<<<1, 256, 0, st>>>(n, u->dz0, u->dzv, u->w0 - u->wc, u->coef, u->status);
+    state_update_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, u->ld, u->Tc, u->dz0, u->dzv, u->coef, u->mean, u->gvec, h->X,
+                                                   u->status);
+    ASLAM_CUDA(cudaGetLastError());
+    nl += 2;
+    // ---- P = P_pred - W W' + (c/den) g g'
     dense::Epilogue d;
     d.alpha = -1.0;
     d.beta = 1.0;
     d.lower_only = true;
+    d.u = u->gvec; d.v = u->gvec; d.r1_dev = u->coef;
     rc = dense::dgemm_nt(st, n, n, n, u->Tc, u->ld, u->Tc, u->ld, h->P, u->ld, d, &nl);
     if (rc != ASLAM_OK) return rc;
     rc = dense::symmetrize_from_lower(st, h->P, u->ld, n, &nl);
     if (rc != ASLAM_OK) return rc;
-    rc = dense::trsv_lower(st, u->dzv, u->S, u->ld, n, u->invS, &nl);
-    if (rc != ASLAM_OK) return rc;
-    state_update_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, u->ld, u->Tc, u->dzv, u->mean, h->X, u->status);
     fail_to_status_kernel<<<1, 1, 0, st>>>(u->fail, u->status);
     ASLAM_CUDA(cudaGetLastError());
-    nl += 2;
+    ++nl;
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, st));
     return ASLAM_OK;
 }
