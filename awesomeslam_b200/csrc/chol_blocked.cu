@@ -13,65 +13,84 @@ namespace dense {
 namespace {
 
 constexpr int BS = CHOL_BS;
-constexpr int PITCH = BS + 1;
 
-// One CTA, 256 threads. A: bs x bs diagonal block (row-major, ld). Factor in place (lower), write inv(L) (pitch 64,
-// zero above the diagonal and beyond bs). k0: global index of the block's first row (for the failure report).
+// One CTA, 256 threads as a 16 x 16 grid; thread (ti, tj) keeps the 4 x 4 sub-blocks A[4ti.., 4tj..] and X[4ti.., 4tj..]
+// in registers. A: bs x bs diagonal block (row-major, ld), padded to 64 with the identity. Right-looking Cholesky fused
+// with the elimination of [L | I], so that X ends as inv(L): per column k the owners publish column k of A and row k
+// of X through (double-buffered) shared memory, one __syncthreads, then every thread applies both rank-1 updates to
+// its registers. Writes L over the lower triangle of A and inv(L) (pitch 64, zero above the diagonal and beyond bs) to
+// `inv`. k0: global index of the block's first row (for the failure report: Eigen's LLT stops at the first x <= 0).
 __global__ void __launch_bounds__(256) chol_panel_kernel(double* A, size_t ld, int bs, double* inv, int* fail, int k0) {
-    extern __shared__ __align__(16) unsigned char panel_smem[];
-    double(*s)[PITCH] = reinterpret_cast<double(*)[PITCH]>(panel_smem);
-    double(*si)[PITCH] = s + BS;
-    const int tid = threadIdx.x;
-    for (int idx = tid; idx < BS * BS; idx += 256) {
-        const int i = idx / BS, j = idx % BS;
-        s[i][j] = (i < bs && j <= i) ? A[(size_t)i * ld + j] : (i == j ? 1.0 : 0.0);
-        si[i][j] = 0.0;
-    }
-    __syncthreads();
-    for (int k = 0; k < bs; ++k) {
-        if (tid == 0) {
-            double x = s[k][k];
-            if (!(x > 0.0)) {  // Eigen: `if (x <= 0) return k;` -- recorded, then carried on with |x| so nothing traps
-                atomicCAS(fail, -1, k0 + k);
-                x = x == 0.0 ? 1.0 : fabs(x);
+    __shared__ double col[2][BS];
+    __shared__ double xrow[2][BS];
+    const int tid = threadIdx.x, ti = tid >> 4, tj = tid & 15;
+    double a[4][4], x[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int i = 4 * ti + r, j = 4 * tj + c;
+            a[r][c] = (i < bs && j <= i) ? A[(size_t)i * ld + j] : (i == j ? 1.0 : 0.0);
+            x[r][c] = i == j ? 1.0 : 0.0;
+        }
+    for (int kb = 0; kb < BS / 4; ++kb) {
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const int k = 4 * kb + kk, buf = kk & 1;
+            if (tj == kb) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) col[buf][4 * ti + r] = a[r][kk];
             }
-            s[k][k] = sqrt(x);
+            if (ti == kb) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) xrow[buf][4 * tj + c] = x[kk][c];
+            }
+            __syncthreads();
+            double akk = col[buf][k];
+            if (!(akk > 0.0)) {
+                if (tid == 0 && k < bs) atomicCAS(fail, -1, k0 + k);
+                akk = akk == 0.0 ? 1.0 : fabs(akk);
+            }
+            const double d = sqrt(akk), rd = 1.0 / d;
+            double li[4], lj[4], xk[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                li[r] = col[buf][4 * ti + r] * rd;
+                lj[r] = col[buf][4 * tj + r] * rd;
+                xk[r] = xrow[buf][4 * tj + r] * rd;
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int i = 4 * ti + r;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int j = 4 * tj + c;
+                    if (i > k && j > k) a[r][c] = fma(-li[r], lj[c], a[r][c]);
+                    if (i > k) x[r][c] = fma(-li[r], xk[c], x[r][c]);
+                }
+            }
+            if (tj == kb) {  // column k of L
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const int i = 4 * ti + r;
+                    if (i > k) a[r][kk] = li[r];
+                    if (i == k) a[r][kk] = d;
+                }
+            }
+            if (ti == kb) {  // row k of inv(L)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) x[kk][c] = xk[c];
+            }
         }
-        __syncthreads();
-        const double d = s[k][k];
-        for (int i = k + 1 + tid; i < bs; i += 256) s[i][k] = s[i][k] / d;
-        __syncthreads();
-        const int rem = bs - k - 1;
-        for (int idx = tid; idx < rem * rem; idx += 256) {
-            const int i = k + 1 + idx / rem, j = k + 1 + idx % rem;
-            if (j <= i) s[i][j] = fma(-s[i][k], s[j][k], s[i][j]);
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int i = 4 * ti + r, j = 4 * tj + c;
+            if (i < bs && j <= i) A[(size_t)i * ld + j] = a[r][c];
+            inv[i * BS + j] = (i < bs && j <= i) ? x[r][c] : 0.0;
         }
-        __syncthreads();
-    }
-    for (int idx = tid; idx < bs * bs; idx += 256) {
-        const int i = idx / bs, j = idx % bs;
-        if (j <= i) A[(size_t)i * ld + j] = s[i][j];
-    }
-    // inverse: column c of inv(L) by forward substitution, 4 lanes per column splitting the inner sum
-    // (every lane runs the same trip count: the shuffles are full-warp)
-    const int c = tid >> 2, part = tid & 3;
-    if (c < bs && part == 0) si[c][c] = 1.0 / s[c][c];
-    __syncwarp();
-    for (int i = 1; i < bs; ++i) {
-        const bool act = c < bs && i > c;
-        double sum = 0.0;
-        if (act)
-            for (int j = c + part; j < i; j += 4) sum = fma(s[i][j], si[j][c], sum);
-        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-        if (act && part == 0) si[i][c] = -sum / s[i][i];
-        __syncwarp();
-    }
-    __syncthreads();
-    for (int idx = tid; idx < BS * BS; idx += 256) {
-        const int i = idx / BS, j = idx % BS;
-        inv[idx] = (i < bs && j <= i) ? si[i][j] : 0.0;
-    }
 }
 
 // v <- L^-1 v: one CTA of 1024 threads walks the 64-row blocks; block b: r = v_b - L[b, 0:b0] v[0:b0], v_b = inv_b r.
@@ -126,17 +145,11 @@ __global__ void symmetrize_kernel(double* A, size_t ld, int n) {
 
 aslam_status cholesky_lower(cudaStream_t st, double* A, size_t ld, int n, double* inv_blocks, int* d_fail,
                             uint64_t* launches) {
-    constexpr int PANEL_SMEM = 2 * BS * PITCH * (int)sizeof(double);
-    static bool attr = false;
-    if (!attr) {
-        ASLAM_CUDA(cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
-        attr = true;
-    }
     for (int k0 = 0; k0 < n; k0 += BS) {
         const int bs = n - k0 < BS ? n - k0 : BS;
         double* A11 = A + (size_t)k0 * ld + k0;
         double* inv = inv_blocks + (size_t)(k0 / BS) * BS * BS;
-        chol_panel_kernel<<<1, 256, PANEL_SMEM, st>>>(A11, ld, bs, inv, d_fail, k0);
+        chol_panel_kernel<<<1, 256, 0, st>>>(A11, ld, bs, inv, d_fail, k0);
         ASLAM_CUDA(cudaGetLastError());
         if (launches) ++*launches;
         const int rs = n - k0 - bs;
@@ -158,20 +171,22 @@ aslam_status cholesky_lower(cudaStream_t st, double* A, size_t ld, int n, double
 
 aslam_status trsm_right_lower_t(cudaStream_t st, double* B, size_t ldb, int m, const double* L, size_t ldl, int n,
                                 const double* inv_blocks, uint64_t* launches) {
-    // X L' = B, column block j: X_j = (B_j - X_{<j} L[j, <j]') inv(L_jj)'
+    // X L' = B, right-looking by 64-column blocks: X_j = B_j inv(L_jj)' (in place), then the columns to the right lose
+    // X_j L[>j, j]'. Every update is a wide GEMM (all SMs busy); the left-looking form leaves 17 CTAs walking a long K.
     for (int j0 = 0; j0 < n; j0 += BS) {
         const int bs = n - j0 < BS ? n - j0 : BS;
-        if (j0 > 0) {
-            Epilogue e;
-            e.alpha = -1.0;
-            e.beta = 1.0;
-            aslam_status rc = dgemm_nt(st, m, bs, j0, B, ldb, L + (size_t)j0 * ldl, ldl, B + j0, ldb, e, launches);
-            if (rc != ASLAM_OK) return rc;
-        }
         Epilogue f;
         aslam_status rc = dgemm_nt(st, m, bs, bs, B + j0, ldb, inv_blocks + (size_t)(j0 / BS) * BS * BS, BS, B + j0, ldb, f,
                                    launches);
         if (rc != ASLAM_OK) return rc;
+        const int rest = n - j0 - bs;
+        if (rest > 0) {
+            Epilogue e;
+            e.alpha = -1.0;
+            e.beta = 1.0;
+            rc = dgemm_nt(st, m, rest, bs, B + j0, ldb, L + (size_t)(j0 + bs) * ldl + j0, ldl, B + j0 + bs, ldb, e, launches);
+            if (rc != ASLAM_OK) return rc;
+        }
     }
     return ASLAM_OK;
 }

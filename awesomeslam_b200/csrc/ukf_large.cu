@@ -42,7 +42,7 @@ struct UkfLarge {
     double* Z = nullptr;       // [n] persistent measurement vector (ukf.cpp:154-155)
     double* Lb = nullptr;      // [n][ld] Cholesky factor of P (lower)
     double* S = nullptr;       // [n][ld]
-    double* Tc = nullptr;      // [n][ld], later W
+    double* Tc = nullptr;      // [n + 2][ld], later W; rows n, n+1 carry dz_0' and dz' through the triangular solve
     double* D = nullptr;       // [n][nsld]
     double* DZ = nullptr;      // [n][nsld] Zsig, then Zdiff
     double* pose = nullptr;    // [3][nsld] rows 0..2 of XsigPred
@@ -379,7 +379,7 @@ aslam_status large_ukf_create(aslam_large* h) {
     A((void**)&u->Z, n * sizeof(double));
     A((void**)&u->Lb, mat);
     A((void**)&u->S, mat);
-    A((void**)&u->Tc, mat);
+    A((void**)&u->Tc, (size_t)(n + 2) * u->ld * sizeof(double));
     A((void**)&u->D, sig);
     A((void**)&u->DZ, sig);
     A((void**)&u->pose, 3 * u->nsld * sizeof(double));
@@ -514,17 +514,17 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     e.u = u->d0; e.v = u->dz0; e.diag = nullptr;
     rc = dense::dgemm_nt(st, n, n, u->ns, u->D, u->nsld, u->DZ, u->nsld, u->Tc, u->ld, e, &nl);
     if (rc != ASLAM_OK) return rc;
-    // ---- M = Lm Lm';  W = Tc Lm^-T;  a = Lm^-1 dz_0;  b = Lm^-1 dz
+    // ---- M = Lm Lm';  [W; a'; b'] = [Tc; dz_0'; dz'] Lm^-T  (a = Lm^-1 dz_0, b = Lm^-1 dz ride along as two extra rows)
     rc = dense::cholesky_lower(st, u->S, u->ld, n, u->invS, u->fail + 1, &nl);
     if (rc != ASLAM_OK) return rc;
-    rc = dense::trsm_right_lower_t(st, u->Tc, u->ld, n, u->S, u->ld, n, u->invS, &nl);
+    double* arow = u->Tc + (size_t)n * u->ld;
+    double* brow = arow + u->ld;
+    ASLAM_CUDA(cudaMemcpyAsync(arow, u->dz0, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    ASLAM_CUDA(cudaMemcpyAsync(brow, u->dzv, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    rc = dense::trsm_right_lower_t(st, u->Tc, u->ld, n + 2, u->S, u->ld, n, u->invS, &nl);
     if (rc != ASLAM_OK) return rc;
-    rc = dense::trsv_lower(st, u->dz0, u->S, u->ld, n, u->invS, &nl);
-    if (rc != ASLAM_OK) return rc;
-    rc = dense::trsv_lower(st, u->dzv, u->S, u->ld, n, u->invS, &nl);
-    if (rc != ASLAM_OK) return rc;
-    sm_scalars_kernel<<<1, 256, 0, st>>>(n, u->dz0, u->dzv, u->w0 - u->wc, u->coef, u->status);
-    state_update_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, u->ld, u->Tc, u->dz0, u->dzv, u->coef, u->mean, u->gvec, h->X,
+    sm_scalars_kernel<<<1, 256, 0, st>>>(n, arow, brow, u->w0 - u->wc, u->coef, u->status);
+    state_update_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, u->ld, u->Tc, arow, brow, u->coef, u->mean, u->gvec, h->X,
                                                    u->status);
     ASLAM_CUDA(cudaGetLastError());
     nl += 2;

@@ -334,6 +334,47 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
     }
 
 
+def ukf_large_leg(args, torch, dev):
+    """cfg5: large-map UKF, n = 2051 (1024 landmarks, 4107 sigma points), one message from the supplied positive
+    definite state per step (a second consecutive message of the reference UKF already finds P indefinite, SURVEY 3.2:
+    the state is re-loaded before every step, outside the timed region). Timed: the whole device chain of the step
+    (Cholesky, sigma points, the three weighted-product GEMMs, solves, update) with CUDA events on the handle's stream."""
+    import ctypes as C
+    import awesomeslam_b200 as A
+    side = 32
+    tx, ty, X0, G, d = A.large_map_state(side, pitch=100.0 / side)
+    P0 = A.dense_P(G, d)
+    n = X0.size
+    rng, brg, idx = A.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8)
+    f = A.LargeFilter("ukf", n, dev.index)
+    ms = []
+    for it in range(max(args.warmup, 3) + min(args.steps, 10)):
+        f.load_state(X0, P0)
+        l0 = f.launch_count
+        f.step(0.01, -0.01, 0.002, 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
+        t = f.last_kernel_ms()
+        launches = f.launch_count - l0
+        if it >= max(args.warmup, 3):
+            ms.append(t)
+    X, _ = f.get_state(want_P=False)
+    status, fail = f.status()
+    assert np.all(np.isfinite(X)) and status == 0 and fail == -1
+    f.close()
+    tf = C.c_double()
+    A.capi.check(A.capi.lib().aslam_probe_dmma_tflops(dev.index, C.byref(tf)))
+    step_ms = float(np.mean(ms))
+    N, NS = n, 2 * n + 5
+    executed = ((N ** 3) / 3 * 2 + 2 * N * N * NS + N * N * NS * 2 + N ** 3 * 2)  # 2 chol, P+M lower, Tc full, trsm+syrk
+    reference_form = (N + 2) ** 3 / 3 + 3 * 2 * N * N * NS + 2 * N ** 3 * 4       # SURVEY 8d: ~176 GF
+    return {"workload": "cfg5: large-map UKF n=2051 (1024 landmarks), 4107 sigma points, FP64",
+            "steps_per_s": 1e3 / step_ms, "ms_per_step": step_ms, "launches_per_step": launches,
+            "roofline": {"bound": "tensor", "kernel": "dgemm_nt_kernel (TMA + DMMA.8x8x4) chain", "unit": "TFLOP/s",
+                         "achieved": executed / (step_ms * 1e-3) / 1e12, "peak": tf.value,
+                         "frac": executed / (step_ms * 1e-3) / 1e12 / tf.value if tf.value else None,
+                         "executed_flop_per_step": executed, "reference_form_flop_per_step": reference_form,
+                         "peak_source": "aslam_probe_dmma_tflops (DMMA chain, this run)"}}
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -370,6 +411,9 @@ def main():
     large = None
     if not args.no_large:
         large = large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src)
+    ukf_large = None
+    if rank == 0 and not args.no_large:
+        ukf_large = ukf_large_leg(args, torch, dev)
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -404,6 +448,8 @@ def main():
         line["large_map"] = {k: v for k, v in large.items() if k != "roofline"}
     else:
         line["roofline"] = None
+    if ukf_large:
+        line["large_map_ukf"] = ukf_large
     if not args.no_cpu:
         ups, nthr, sec = cpu_leg(256 if (os.cpu_count() or 1) < 16 else 1024, 120)
         line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": nthr, "kind": "port",
