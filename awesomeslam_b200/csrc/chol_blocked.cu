@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(256) chol_panel_kernel(double* A, size_t ld, i
                 if (tid == 0 && k < bs) atomicCAS(fail, -1, k0 + k);
                 akk = akk == 0.0 ? 1.0 : fabs(akk);
             }
-            const double d = sqrt(akk), rd = 1.0 / d;
+            const double rd = rsqrt(akk), d = akk * rd;  // a few ulp from sqrt/divide: far inside the FP64 tolerance
             double li[4], lj[4], xk[4];
 #pragma unroll
             for (int r = 0; r < 4; ++r) {

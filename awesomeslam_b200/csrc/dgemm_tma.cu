@@ -12,6 +12,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <mutex>
 
 #include "bulk_copy.cuh"
@@ -241,6 +242,63 @@ aslam_status launch(cudaStream_t st, const double* A, size_t lda, const double* 
     return ASLAM_OK;
 }
 
+// Ragged edge. A last tile row (or column) holding only a few rows would still cost a full pass over K for every
+// tile in it -- at cfg5 (2051 = 16 * 128 + 3) that is a whole extra wave. Those few rows / columns are computed here
+// instead: one warp per index of the long side, the <= 16 short-side vectors (L2-resident) against it.
+constexpr int SKINNY_MAX = 16;
+__global__ void __launch_bounds__(256) dgemm_skinny_kernel(GemmParams p, const double* __restrict__ A, size_t lda,
+                                                          const double* __restrict__ B, size_t ldb, int i0, int i1, int j0,
+                                                          int j1, int long_is_col) {
+    const int warp = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int nlong = long_is_col ? j1 - j0 : i1 - i0;
+    const int nshort = long_is_col ? i1 - i0 : j1 - j0;
+    if (warp >= nlong) return;
+    const double* lv = long_is_col ? B + (size_t)(j0 + warp) * ldb : A + (size_t)(i0 + warp) * lda;
+    const double* sv = long_is_col ? A + (size_t)i0 * lda : B + (size_t)j0 * ldb;
+    const size_t sld = long_is_col ? lda : ldb;
+    double acc[SKINNY_MAX];
+#pragma unroll
+    for (int s = 0; s < SKINNY_MAX; ++s) acc[s] = 0.0;
+    // 4 k per lane and trip: independent loads in flight (the short vectors come from L2)
+    for (int k0 = 0; k0 < p.K; k0 += 128) {
+        double x[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int k = k0 + q * 32 + lane;
+            x[q] = k < p.K ? lv[k] : 0.0;
+        }
+#pragma unroll
+        for (int s = 0; s < SKINNY_MAX; ++s) {
+            if (s < nshort) {
+                const double* sp = sv + (size_t)s * sld;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int k = k0 + q * 32 + lane;
+                    acc[s] = fma(x[q], k < p.K ? sp[k] : 0.0, acc[s]);
+                }
+            }
+        }
+    }
+    const double r1 = p.r1_dev ? *p.r1_dev : p.r1;
+#pragma unroll
+    for (int s = 0; s < SKINNY_MAX; ++s) {
+        if (s >= nshort) break;
+        double v = acc[s];
+        for (int off = 16; off; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+        if (lane == 0) {
+            const int i = long_is_col ? i0 + s : i0 + warp;
+            const int j = long_is_col ? j0 + warp : j0 + s;
+            if (p.lower_only && j > i) continue;
+            double* c = p.C + (size_t)i * p.ldc + j;
+            double o = p.alpha * v;
+            if (p.beta != 0.0) o = fma(p.beta, *c, o);
+            if (p.u) o = fma(r1 * p.u[i], p.v[j], o);
+            if (p.diag && i == j) o += p.diag[i];
+            *c = o;
+        }
+    }
+}
+
 }  // namespace
 
 aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, size_t lda, const double* B, size_t ldb,
@@ -255,10 +313,37 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K;
     p.alpha = e.alpha; p.beta = e.beta; p.r1 = e.r1; p.u = e.u; p.v = e.v; p.diag = e.diag; p.r1_dev = e.r1_dev;
     p.lower_only = e.lower_only ? 1 : 0;
+    // ragged edge (see dgemm_skinny_kernel); not when C aliases an operand (the in-place panel products)
+    const bool alias = C == A || C == B || K < 512;  // short K: the ragged tile is cheap, an extra launch is not
+    int Mm = M, Nm = N;
+    if (!alias && M > 128 && M % 128 != 0 && M % 128 <= SKINNY_MAX) Mm = M - M % 128;
+    if (!alias && N > 128 && N % 128 != 0 && N % 128 <= SKINNY_MAX) Nm = N - N % 128;
+    if (e.lower_only && Nm > Mm) Nm = Mm;  // columns beyond the main rows only matter for the tail rows
+    if (Mm < M) {  // tail rows, all columns
+        dgemm_skinny_kernel<<<(N + 7) / 8, 256, 0, st>>>(p, A, lda, B, ldb, Mm, M, 0, N, 1);
+        ASLAM_CUDA(cudaGetLastError());
+        if (launches) ++*launches;
+    }
+    if (Nm < N && !e.lower_only) {  // tail columns, main rows
+        dgemm_skinny_kernel<<<(Mm + 7) / 8, 256, 0, st>>>(p, A, lda, B, ldb, 0, Mm, Nm, N, 0);
+        ASLAM_CUDA(cudaGetLastError());
+        if (launches) ++*launches;
+    }
+    p.M = Mm;
+    p.N = Nm;
     if (launches) ++*launches;
-    // tile shape: 128 x 128 when that still fills the 148 SMs about twice, else 128 x 64; narrow N -> 128 x 64
-    const long tiles128 = (long)((M + 127) / 128) * ((N + 127) / 128) / (e.lower_only ? 2 : 1);
-    if (N > 64 && tiles128 >= 280) return launch<128, 128, 4, 2>(st, A, lda, B, ldb, p);
+    // tile shape: 128 x 128 when that fills the 148 SMs in whole waves about as well as 128 x 64 would, narrow N -> 128 x 64
+    const long tr = (Mm + 127) / 128, tc128 = (Nm + 127) / 128, tc64 = (Nm + 63) / 64;
+    long t128 = 0, t64 = 0;
+    for (long i = 0; i < tr; ++i) {
+        const long lim128 = e.lower_only ? std::min(tc128, i + 1) : tc128;            // tiles with col0 <= last row
+        const long lim64 = e.lower_only ? std::min(tc64, 2 * (i + 1)) : tc64;
+        t128 += lim128;
+        t64 += lim64;
+    }
+    const long sms = 148;
+    const double cost128 = 2.0 * (double)((t128 + sms - 1) / sms), cost64 = 1.08 * (double)((t64 + sms - 1) / sms);
+    if (Nm > 64 && cost128 <= cost64) return launch<128, 128, 4, 2>(st, A, lda, B, ldb, p);
     return launch<128, 64, 4, 2>(st, A, lda, B, ldb, p);
 }
 

@@ -42,7 +42,7 @@ def _padded(torch, rows, cols, rng):
     return buf[:, :cols]
 
 
-@pytest.mark.parametrize("M,N,K", [(128, 64, 16), (131, 70, 37), (300, 300, 64), (515, 259, 1030), (2051, 2051, 263)])
+@pytest.mark.parametrize("M,N,K", [(128, 64, 16), (131, 70, 37), (300, 300, 64), (515, 259, 1030), (2051, 2051, 600)])
 def test_dense_gemm_nt(aslam, M, N, K):
     torch = _torch()
     rng = np.random.default_rng(M + N + K)
@@ -53,10 +53,10 @@ def test_dense_gemm_nt(aslam, M, N, K):
     assert relerr(Cm.cpu().numpy(), ref.cpu().numpy()) < 1e-13
 
 
-def test_dense_gemm_lower_only_and_inplace_panel(aslam):
+@pytest.mark.parametrize("n,K", [(700, 150), (2051, 520), (1283, 70)])
+def test_dense_gemm_lower_only(aslam, n, K):
     torch = _torch()
     rng = np.random.default_rng(3)
-    n, K = 700, 150
     A = _padded(torch, n, K, rng)
     Cm = _padded(torch, n, n, rng)
     C0 = Cm.clone()
@@ -65,7 +65,7 @@ def test_dense_gemm_lower_only_and_inplace_panel(aslam):
     got = Cm.cpu().numpy()
     il = np.tril_indices(n)
     assert relerr(got[il], ref[il]) < 1e-13
-    # tiles entirely above the diagonal are untouched (128 x 64 tiles)
+    # tiles entirely above the diagonal are untouched (128 x 128 or 128 x 64 tiles)
     assert np.array_equal(got[:128, 640:], C0.cpu().numpy()[:128, 640:])
 
 
