@@ -2,6 +2,7 @@
 
 Everything is compiled with explicit nvcc / g++ command lines; the products are
   awesomeslam_b200/lib/libaslam_b200.so   the C-ABI library (include/aslam_c.h)
+  awesomeslam_b200/lib/aslam_replay       the ROS-free C++ replay harness (include/aslam_filters.hpp)
   oracle/liboracle.so                     TEST INFRASTRUCTURE: CPU restatement of the reference
 """
 import os
@@ -73,6 +74,19 @@ def build_library(force=False, verbose=False):
     return LIB
 
 
+HARNESS = os.path.join(LIBDIR, "aslam_replay")
+
+
+def build_harness(force=False):
+    """The ROS-free C++ replay harness (awesomeslam_b200/harness/replay_main.cpp) over include/aslam_filters.hpp."""
+    src = os.path.join(ROOT, "awesomeslam_b200", "harness", "replay_main.cpp")
+    deps = [src, os.path.join(ROOT, "include", "aslam_filters.hpp"), os.path.join(ROOT, "include", "aslam_c.h"), LIB]
+    if force or _stale(HARNESS, deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++14", "-I", os.path.join(ROOT, "include"), src, "-L", LIBDIR,
+                               "-laslam_b200", "-Wl,-rpath,$ORIGIN", "-pthread", "-ldl", "-lrt", "-o", HARNESS])
+    return HARNESS
+
+
 def build_oracle(force=False):
     odir = os.path.join(ROOT, "oracle")
     srcs = [os.path.join(odir, "oracle_c.cpp")]
@@ -86,4 +100,5 @@ def build_oracle(force=False):
 if __name__ == "__main__":
     v = "-v" in sys.argv
     print(build_library(force="-f" in sys.argv, verbose=v))
+    print(build_harness(force="-f" in sys.argv))
     print(build_oracle(force="-f" in sys.argv))
