@@ -540,6 +540,131 @@ __global__ void __launch_bounds__(256, 1) large_update_bulk_kernel(uint32_t n, u
     if (tid == 0) bulk::wait_group<0>();
 }
 
+// K5, warp-specialised form (default). Same tiles and shared-memory ring as the kernel above, but the copy engine is
+// driven by a dedicated ninth warp, so the 8 consumer warps never meet in a CTA-wide barrier:
+//   producer lane : wait done[st] -> bulk-store the stage -> (one chunk later, once that store has been read out of
+//                   shared memory) re-arm full[st] and bulk-load the chunk NST ahead
+//   consumer warp : wait full[st] -> update its 64 rows of the stage in place, 4 columns interleaved (8 independent
+//                   DFMA chains per thread instead of 2) -> fence.proxy.async -> arrive on done[st]
+// ncu on the kernel above (profiles/r01_summary.md): 26 % of the samples sat in __syncthreads behind thread 0's 17 bulk
+// instructions per chunk and 37 % in the 20-deep dependent DFMA chains; both are structural and are what this removes.
+__device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bulk::smem_u32(bar)) : "memory");
+}
+
+template <int R, int Q, int CS, int NST>
+__global__ void __launch_bounds__(288, 1) large_update_ws_kernel(uint32_t n, uint32_t rb, uint32_t nrows, size_t ldp,
+                                                                double* __restrict__ P, const double* __restrict__ K,
+                                                                const double* __restrict__ hp, uint32_t cols_per_cta) {
+    using G = BulkGeo<R, Q, CS, NST>;
+    static_assert(R == 2 && CS % 4 == 0, "the interleaved inner loop is written for 2 rows x 4 columns");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + NST * G::STAGE);
+    uint64_t* done = full + NST;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t r0 = blockIdx.y * G::ROWS;
+    const uint32_t rows_here = min((uint32_t)G::ROWS, (uint32_t)ldp - r0);
+    const uint32_t seg_bytes = rows_here * sizeof(double);
+    const uint32_t c_begin = blockIdx.x * cols_per_cta;
+    const uint32_t c_end = min(n, c_begin + cols_per_cta);
+    if (c_begin >= c_end) return;
+    const uint32_t nchunks = (c_end - c_begin + CS - 1) / CS;
+    auto stage_p = [&](int st) { return reinterpret_cast<double*>(smem_raw + st * G::STAGE); };
+    auto stage_h = [&](int st) { return reinterpret_cast<double*>(smem_raw + st * G::STAGE + G::P_BYTES); };
+
+    if (tid == 0) {
+        for (int s = 0; s < NST; ++s) {
+            bulk::mbar_init(&full[s], 1);
+            bulk::mbar_init(&done[s], 8);
+        }
+        bulk::fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == 8) {  // ---------------- producer
+        if (lane != 0) return;
+        auto issue_load = [&](uint32_t chunk) {
+            const int st = chunk % NST;
+            const uint32_t c0 = c_begin + chunk * CS;
+            const uint32_t cw = min((uint32_t)CS, c_end - c0);
+            bulk::mbar_expect_tx(&full[st], cw * seg_bytes + cw * Q * (uint32_t)sizeof(double));
+            double* dp = stage_p(st);
+            for (uint32_t c = 0; c < cw; ++c)
+                bulk::g2s(dp + c * G::ROWS, P + (size_t)(c0 + c) * ldp + r0, seg_bytes, &full[st]);
+            bulk::g2s(stage_h(st), hp + (size_t)c0 * Q, cw * Q * (uint32_t)sizeof(double), &full[st]);
+        };
+        for (uint32_t c = 0; c < (uint32_t)(NST - 1) && c < nchunks; ++c) issue_load(c);
+        for (uint32_t chunk = 0; chunk < nchunks; ++chunk) {
+            const int st = chunk % NST;
+            const uint32_t c0 = c_begin + chunk * CS;
+            const uint32_t cw = min((uint32_t)CS, c_end - c0);
+            bulk::mbar_wait(&done[st], (chunk / NST) & 1u);
+            const double* sp = stage_p(st);
+            for (uint32_t c = 0; c < cw; ++c) bulk::s2g(P + (size_t)(c0 + c) * ldp + r0, sp + c * G::ROWS, seg_bytes);
+            bulk::commit_group();
+            const uint32_t nxt = chunk + NST - 1;  // goes into the stage drained one chunk ago
+            if (nxt < nchunks) {
+                bulk::wait_group_read<1>();
+                issue_load(nxt);
+            }
+        }
+        bulk::wait_group<0>();
+        return;
+    }
+
+    // ---------------- consumers
+    const uint32_t i0 = r0 + tid * R;
+    double nk[Q][R];
+#pragma unroll
+    for (int k = 0; k < Q; ++k)
+#pragma unroll
+        for (int r = 0; r < R; ++r) nk[k][r] = (i0 + r < nrows) ? -K[(size_t)k * n + rb + i0 + r] : 0.0;
+    const bool active = (uint32_t)(tid * R) < rows_here;
+
+    for (uint32_t chunk = 0; chunk < nchunks; ++chunk) {
+        const int st = chunk % NST;
+        const uint32_t cw = min((uint32_t)CS, c_end - (c_begin + chunk * CS));
+        bulk::mbar_wait(&full[st], (chunk / NST) & 1u);
+        if (active) {
+            double* sp = stage_p(st) + tid * R;
+            const double* sh = stage_h(st);
+            if (cw == CS) {
+#pragma unroll
+                for (int cg = 0; cg < CS; cg += 4) {
+                    double2 v[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) v[c] = *reinterpret_cast<const double2*>(sp + (cg + c) * G::ROWS);
+#pragma unroll
+                    for (int k = 0; k < Q; k += 2) {
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const double2 h = *reinterpret_cast<const double2*>(sh + (cg + c) * Q + k);
+                            v[c].x = fma(nk[k][0], h.x, v[c].x);
+                            v[c].y = fma(nk[k][1], h.x, v[c].y);
+                            v[c].x = fma(nk[k + 1][0], h.y, v[c].x);
+                            v[c].y = fma(nk[k + 1][1], h.y, v[c].y);
+                        }
+                    }
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) *reinterpret_cast<double2*>(sp + (cg + c) * G::ROWS) = v[c];
+                }
+            } else {
+                for (uint32_t c = 0; c < cw; ++c)
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        double v = sp[c * G::ROWS + r];
+#pragma unroll
+                        for (int k = 0; k < Q; ++k) v = fma(nk[k][r], sh[c * Q + k], v);
+                        sp[c * G::ROWS + r] = v;
+                    }
+            }
+            bulk::fence_proxy_async();
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cta(&done[st]);
+    }
+}
+
 // Any q (up to LARGE_QMAX): K read from global (L2-resident), FP64-bound for large q anyway.
 __global__ void __launch_bounds__(256) large_update_generic_kernel(uint32_t n, uint32_t rb, uint32_t nrows,
                                                                   size_t ldp, double* __restrict__ P,
@@ -621,6 +746,17 @@ aslam_status large_ekf_phase2(aslam_large* h) {
             else
                 large_update_kernel<1, 40, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K,
                                                                           h->hp, cols_per_cta);
+        } else if (QT == 20 && !(variant && variant[0] == 'b')) {  // default; ASLAM_LARGE_UPDATE=bulk: the one-barrier kernel
+            using G = BulkGeo<2, 20, 8, 5>;
+            constexpr size_t WS_SMEM = G::SMEM + 5 * sizeof(uint64_t);
+            static bool set = false;
+            if (!set) {
+                ASLAM_CUDA(cudaFuncSetAttribute(large_update_ws_kernel<2, 20, 8, 5>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WS_SMEM));
+                set = true;
+            }
+            large_update_ws_kernel<2, 20, 8, 5><<<grid, 288, WS_SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
+                                                                                  h->K, h->hp, cols_per_cta);
         } else if (QT == 20) {
             using G = BulkGeo<2, 20, 8, 5>;
             static bool set = false;
