@@ -45,98 +45,125 @@ struct FrontArgs {
 
 __global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t n, double* X, double* A,
                                                           const float* obs, LargeCtx* ctx) {
-    __shared__ unsigned long long red[32];
     __shared__ float s_nb[ASLAM_MAX_OBS];
     __shared__ int s_corr[ASLAM_MAX_OBS];
     __shared__ float s_mind[ASLAM_MAX_OBS];
-    const int tid = threadIdx.x;
+    __shared__ int s_lm[ASLAM_MAX_OBS], s_ob[ASLAM_MAX_OBS];
+    __shared__ int s_cnt;
+    __shared__ double s_pose[3];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t L = (n - 3) / 2;
     const double z0 = a.ox, z1 = a.oy, z2 = (double)a.yaw;
-    for (uint32_t o = 0; o < a.m; ++o) {
-        const float r = obs[o];
-        const float b = normalize_angle(obs[ASLAM_MAX_OBS + o], a.pi);  // ekf.cpp:150
-        const float2 pt = to_point(r, b, z0, z1, z2);                   // structures.h:104-111
-        unsigned long long best = ~0ull;
-        for (uint32_t l = tid; l < L; l += blockDim.x) {
-            const float d = euler_distance(pt.x, pt.y, (float)X[3 + 2 * l], (float)X[4 + 2 * l]);
-            // d >= 0: its bit pattern orders like the value; the low word breaks ties toward the
-            // lowest landmark, which is what the strict `<` of ekf.cpp:168 keeps
-            const unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | l;
-            best = umin64(best, key);
+    // ---- nearest landmark of every observation. Thread o < m projects observation o (structures.h:104-111); then
+    // every thread keeps a few landmarks in registers and scans all observations against them: one pass over X,
+    // one round of warp reductions, one CTA barrier, one final reduction per observation.
+    __shared__ float2 s_pt[ASLAM_MAX_OBS];
+    __shared__ unsigned long long s_red[ASLAM_MAX_OBS][32];
+    if (tid < (int)a.m) {
+        const float b = normalize_angle(obs[ASLAM_MAX_OBS + tid], a.pi);  // ekf.cpp:150
+        s_nb[tid] = b;
+        s_pt[tid] = to_point(obs[tid], b, z0, z1, z2);
+    }
+    __syncthreads();
+    constexpr int LPT = 4;  // landmarks per thread and pass
+    for (uint32_t o = 0; o < a.m; ++o) s_red[o][warp] = ~0ull;
+    for (uint32_t l0 = 0; l0 < L; l0 += 1024 * LPT) {
+        float lx[LPT], ly[LPT];
+#pragma unroll
+        for (int u = 0; u < LPT; ++u) {
+            const uint32_t l = l0 + u * 1024 + tid;
+            lx[u] = l < L ? (float)X[3 + 2 * l] : 0.0f;
+            ly[u] = l < L ? (float)X[4 + 2 * l] : 0.0f;
         }
+        for (uint32_t o = 0; o < a.m; ++o) {
+            const float2 pt = s_pt[o];
+            unsigned long long best = ~0ull;
+#pragma unroll
+            for (int u = 0; u < LPT; ++u) {
+                const uint32_t l = l0 + u * 1024 + tid;
+                if (l < L) {
+                    const float d = euler_distance(pt.x, pt.y, lx[u], ly[u]);
+                    // d >= 0: its bit pattern orders like the value; the low word breaks ties toward the
+                    // lowest landmark, which is what the strict `<` of ekf.cpp:168 keeps
+                    best = umin64(best, ((unsigned long long)__float_as_uint(d) << 32) | l);
+                }
+            }
+            for (int off = 16; off; off >>= 1) best = umin64(best, __shfl_xor_sync(0xffffffffu, best, off));
+            if (lane == 0) s_red[o][warp] = umin64(s_red[o][warp], best);
+        }
+    }
+    __syncthreads();
+    for (uint32_t o = warp; o < a.m; o += 32) {
+        unsigned long long best = s_red[o][lane];
         for (int off = 16; off; off >>= 1) best = umin64(best, __shfl_xor_sync(0xffffffffu, best, off));
-        if ((tid & 31) == 0) red[tid >> 5] = best;
-        __syncthreads();
-        if (tid < 32) {
-            unsigned long long v = tid < (int)(blockDim.x >> 5) ? red[tid] : ~0ull;
-            for (int off = 16; off; off >>= 1) v = umin64(v, __shfl_xor_sync(0xffffffffu, v, off));
-            if (tid == 0) {
-                s_nb[o] = b;
-                s_corr[o] = (int)(v & 0xffffffffu) * 2;  // corr_id counts state entries (ekf.cpp:170)
-                s_mind[o] = __uint_as_float((unsigned)(v >> 32));
-            }
+        if (lane == 0) {
+            s_corr[o] = (int)(best & 0xffffffffu) * 2;  // corr_id counts state entries (ekf.cpp:170)
+            s_mind[o] = __uint_as_float((unsigned)(best >> 32));
         }
-        __syncthreads();
     }
-    if (tid != 0) return;
-
-    // ---- sequential part: which landmark keeps which observation (later messages overwrite Z)
-    int lm[ASLAM_MAX_OBS], ob[ASLAM_MAX_OBS];
-    int cnt = 0;
-    for (uint32_t o = 0; o < a.m; ++o) {
-        if (L > 0 && s_mind[o] < a.thresh) {  // ekf.cpp:175
-            ctx->assoc[o] = s_corr[o];
-            int k = 0;
-            while (k < cnt && lm[k] != s_corr[o]) ++k;
-            if (k == cnt) {
-                lm[cnt] = s_corr[o];
-                ob[cnt] = (int)o;
-                ++cnt;
+    __syncthreads();
+    if (tid == 0) {
+        // ---- sequential part: which landmark keeps which observation (later messages overwrite Z)
+        int cnt = 0;
+        for (uint32_t o = 0; o < a.m; ++o) {
+            if (L > 0 && s_mind[o] < a.thresh) {  // ekf.cpp:175
+                ctx->assoc[o] = s_corr[o];
+                int k = 0;
+                while (k < cnt && s_lm[k] != s_corr[o]) ++k;
+                if (k == cnt) {
+                    s_lm[cnt] = s_corr[o];
+                    s_ob[cnt] = (int)o;
+                    ++cnt;
+                } else {
+                    s_ob[k] = (int)o;
+                }
             } else {
-                ob[k] = (int)o;
+                ctx->assoc[o] = -1;
             }
-        } else {
-            ctx->assoc[o] = -1;
         }
-    }
-    for (int i = 1; i < cnt; ++i) {  // ascending landmark order, as the oracle walks the map
-        const int l = lm[i], o = ob[i];
-        int k = i - 1;
-        while (k >= 0 && lm[k] > l) {
-            lm[k + 1] = lm[k];
-            ob[k + 1] = ob[k];
-            --k;
+        for (int i = 1; i < cnt; ++i) {  // ascending landmark order, as the oracle walks the map
+            const int l = s_lm[i], o = s_ob[i];
+            int k = i - 1;
+            while (k >= 0 && s_lm[k] > l) {
+                s_lm[k + 1] = s_lm[k];
+                s_ob[k + 1] = s_ob[k];
+                --k;
+            }
+            s_lm[k + 1] = l;
+            s_ob[k + 1] = o;
         }
-        lm[k + 1] = l;
-        ob[k + 1] = o;
+        s_cnt = cnt;
+        ctx->q = 3 + 2 * cnt;
+    } else if (tid == 32) {
+        // ---- A (ekf.cpp:206-212) and the pose predict (ekf.cpp:295-296)
+        double a00 = A[0], a10 = A[1];
+        motion_jacobian(a.vx, a.az, a.dt, z2, a00, a10);
+        A[0] = a00;
+        A[1] = a10;
+        double x = X[0], y = X[1], th = X[2];
+        motion_model(x, y, th, (float)a.vx, (float)a.az, a.dt);
+        th = (double)normalize_angle((float)th, a.pi);
+        s_pose[0] = x;
+        s_pose[1] = y;
+        s_pose[2] = th;
     }
-    // ---- A (ekf.cpp:206-212) and the pose predict (ekf.cpp:295-296)
-    double a00 = A[0], a10 = A[1];
-    motion_jacobian(a.vx, a.az, a.dt, z2, a00, a10);
-    A[0] = a00;
-    A[1] = a10;
-    double x = X[0], y = X[1], th = X[2];
-    motion_model(x, y, th, (float)a.vx, (float)a.az, a.dt);
-    th = (double)normalize_angle((float)th, a.pi);
-    X[0] = x;
-    X[1] = y;
-    X[2] = th;
-    // ---- rows of H in use
-    const int q = 3 + 2 * cnt;
-    ctx->q = q;
-    for (int k = 0; k < 3; ++k) {
+    __syncthreads();
+    const int cnt = s_cnt, q = 3 + 2 * cnt;
+    const double x = s_pose[0], y = s_pose[1], th = s_pose[2];
+    // ---- rows of H in use: thread k < 3 the pose rows, thread 3 + c landmark c, the rest the padding rows
+    if (tid < 3) {
+        const int k = tid;
+        X[k] = s_pose[k];
         ctx->rows[k] = k;
         ctx->hnnz[k] = 1;
         ctx->hcol[k][0] = k;
         ctx->hk[k][0] = k;
         ctx->hval[k][0] = 1.0;
         ctx->rdiag[k] = a.kr_pose;
-    }
-    ctx->y[0] = a.ox - x;
-    ctx->y[1] = a.oy - y;
-    ctx->y[2] = (double)normalize_angle((float)(z2 - th), a.pi);
-    for (int c = 0; c < cnt; ++c) {
-        const int i = lm[c];
+        ctx->y[k] = k == 0 ? a.ox - x : (k == 1 ? a.oy - y : (double)normalize_angle((float)(z2 - th), a.pi));
+    } else if (tid < 3 + cnt) {
+        const int c = tid - 3;
+        const int i = s_lm[c];
         const double lx = X[3 + i], ly = X[4 + i];
         const HEntries h = jacobian_entries(x, y, lx, ly);
         const int kr = 3 + 2 * c, kb = kr + 1;
@@ -157,14 +184,16 @@ __global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t
         ctx->rdiag[kb] = a.kr_lm;
         double rg, br;
         measure_landmark(x, y, th, lx, ly, rg, br);
-        ctx->y[kr] = (double)obs[ob[c]] - rg;                                          // Z - h(X)
-        ctx->y[kb] = (double)normalize_angle((float)((double)s_nb[ob[c]] - br), a.pi);  // ekf.cpp:306
-    }
-    for (int k = q; k < (int)a.q_ub; ++k) {  // unused rows: harmless identity padding
-        ctx->rows[k] = -1;
-        ctx->hnnz[k] = 0;
-        ctx->y[k] = 0.0;
-        ctx->rdiag[k] = 1.0;
+        ctx->y[kr] = (double)obs[s_ob[c]] - rg;                                          // Z - h(X)
+        ctx->y[kb] = (double)normalize_angle((float)((double)s_nb[s_ob[c]] - br), a.pi);  // ekf.cpp:306
+    } else if (tid < (int)a.q_ub + cnt) {  // unused rows q .. q_ub-1: harmless identity padding
+        const int k = q + (tid - 3 - cnt);
+        if (k < (int)a.q_ub) {
+            ctx->rows[k] = -1;
+            ctx->hnnz[k] = 0;
+            ctx->y[k] = 0.0;
+            ctx->rdiag[k] = 1.0;
+        }
     }
 }
 
@@ -234,6 +263,67 @@ __global__ void large_gather_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t
     }
 }
 
+// Exchange buffer for q <= QT (QT = 20 or 40): same values as large_gather_kernel, arranged for latency (context in
+// shared memory, 2 q independent loads per thread, H_o's fixed row structure with static register indices).
+template <int QT>
+__global__ void __launch_bounds__(256) large_gather_fast_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp,
+                                                               const double* __restrict__ P,
+                                                               const LargeCtx* __restrict__ ctx, uint32_t q_ub,
+                                                               double* __restrict__ E) {
+    __shared__ double s_hval[QT][5];
+    __shared__ int s_rows[QT];
+    const int q = ctx->q;
+    const int tid = threadIdx.x;
+    if (tid < QT) {
+        const bool in = tid < q;
+        s_rows[tid] = in ? ctx->rows[tid] : 0;
+#pragma unroll
+        for (int e = 0; e < 5; ++e) s_hval[tid][e] = in ? ctx->hval[tid][e] : 0.0;
+    }
+    __syncthreads();
+    const uint32_t t = blockIdx.x * 256 + tid;
+    if (t >= n) return;
+    const bool mine = t >= rb && t < re;
+    double raw[QT], colv[QT];
+#pragma unroll
+    for (int k = 0; k < QT; ++k) {
+        const uint32_t r = (uint32_t)s_rows[k];
+        raw[k] = (k < q && r >= rb && r < re) ? P[(size_t)t * ldp + (r - rb)] : 0.0;   // P(rows[k], t)
+        colv[k] = (k < q && mine) ? P[(size_t)r * ldp + (t - rb)] : 0.0;               // P(t, rows[k])
+    }
+    double pht[QT];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        double sum = 0.0;
+        sum += colv[k] * s_hval[k][0];
+        pht[k] = sum;
+    }
+#pragma unroll
+    for (int c = 0; c < (QT - 3) / 2; ++c) {
+        const int kr = 3 + 2 * c, kb = kr + 1;
+        double sr = 0.0, sb = 0.0;  // entries of the row left to right, as the generic kernel sums them
+        sr += colv[0] * s_hval[kr][0];
+        sr += colv[1] * s_hval[kr][1];
+        sr += colv[kr] * s_hval[kr][2];
+        sr += colv[kb] * s_hval[kr][3];
+        sb += colv[0] * s_hval[kb][0];
+        sb += colv[1] * s_hval[kb][1];
+        sb += colv[2] * s_hval[kb][2];
+        sb += colv[kr] * s_hval[kb][3];
+        sb += colv[kb] * s_hval[kb][4];
+        pht[kr] = sr;
+        pht[kb] = sb;
+    }
+    if ((QT - 3) % 2) pht[QT - 1] = 0.0;
+#pragma unroll
+    for (int k = 0; k < QT; ++k) {
+        if (k < (int)q_ub) {
+            E[(size_t)k * n + t] = raw[k];
+            E[(size_t)(q_ub + k) * n + t] = pht[k];
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // Gain. Every CTA rebuilds S = H_o P H_o' + R_o and inverts it in shared memory (Gauss-Jordan with
 // partial pivoting, in place; q <= 131), then produces its slice of H_o P (layout [j][QT], rows
@@ -246,7 +336,6 @@ __global__ void __launch_bounds__(256) large_gain_kernel(uint32_t n, const Large
     const int q = ctx->q;
     double* S = sm;  // q x q, row-major
     __shared__ int piv[LARGE_QMAX];
-    __shared__ int s_p;
     const int tid = threadIdx.x, nt = blockDim.x;
     // S(a,b) = sum_e (H_o P)[a][col_b[e]] * v_b[e] + R;  (H_o P)[a][j] = sum_e' v_a[e'] * row_{hk[a][e']}[j]
     for (int idx = tid; idx < q * q; idx += nt) {
@@ -261,55 +350,62 @@ __global__ void __launch_bounds__(256) large_gain_kernel(uint32_t n, const Large
         S[idx] = s + (a == b ? ctx->rdiag[a] : 0.0);
     }
     __syncthreads();
-    for (int k = 0; k < q; ++k) {
-        if (tid == 0) {
+    // in-place Gauss-Jordan inverse with partial pivoting by ONE warp (q <= 131: a handful of rows per lane);
+    // __syncwarp instead of CTA barriers: the 19 x 19 case takes a few microseconds instead of ~50
+    if (tid < 32) {
+        const int lane = tid;
+        for (int k = 0; k < q; ++k) {
+            // pivot: largest |S(i,k)|, i >= k; ties to the lowest row (first maximum, as Eigen's PartialPivLU scans)
+            double best = -1.0;
             int p = k;
-            double best = fabs(S[k * q + k]);
-            for (int i = k + 1; i < q; ++i) {
+            for (int i = k + lane; i < q; i += 32) {
                 const double v = fabs(S[i * q + k]);
                 if (v > best) {
                     best = v;
                     p = i;
                 }
             }
-            s_p = p;
-            piv[k] = p;
-        }
-        __syncthreads();
-        const int p = s_p;
-        if (p != k)
-            for (int j = tid; j < q; j += nt) {
-                const double t = S[k * q + j];
-                S[k * q + j] = S[p * q + j];
-                S[p * q + j] = t;
+            for (int off = 16; off; off >>= 1) {
+                const double ob = __shfl_xor_sync(0xffffffffu, best, off);
+                const int op = __shfl_xor_sync(0xffffffffu, p, off);
+                if (ob > best || (ob == best && op < p)) {
+                    best = ob;
+                    p = op;
+                }
             }
-        __syncthreads();
-        const double d = 1.0 / S[k * q + k];
-        __syncthreads();
-        for (int j = tid; j < q; j += nt) S[k * q + j] = (j == k ? 1.0 : S[k * q + j]) * d;
-        __syncthreads();
-        for (int idx = tid; idx < q * q; idx += nt) {
-            const int i = idx / q, j = idx % q;
-            if (i == k) continue;
-            const double f = S[i * q + k];
-            if (j == k) continue;
-            S[idx] = fma(-f, S[k * q + j], S[idx]);
-        }
-        __syncthreads();
-        for (int i = tid; i < q; i += nt)
-            if (i != k) S[i * q + k] = -S[i * q + k] * S[k * q + k];
-        __syncthreads();
-    }
-    for (int k = q - 1; k >= 0; --k) {  // undo the row swaps as column swaps
-        const int p = piv[k];
-        if (p != k)
-            for (int i = tid; i < q; i += nt) {
-                const double t = S[i * q + k];
-                S[i * q + k] = S[i * q + p];
-                S[i * q + p] = t;
+            if (lane == 0) piv[k] = p;
+            if (p != k)
+                for (int j = lane; j < q; j += 32) {
+                    const double t = S[k * q + j];
+                    S[k * q + j] = S[p * q + j];
+                    S[p * q + j] = t;
+                }
+            __syncwarp();
+            const double d = 1.0 / S[k * q + k];
+            __syncwarp();
+            for (int j = lane; j < q; j += 32) S[k * q + j] = (j == k ? 1.0 : S[k * q + j]) * d;
+            __syncwarp();
+            for (int i = lane; i < q; i += 32) {  // lane owns whole rows: no conflicts
+                if (i == k) continue;
+                const double f = S[i * q + k];
+                for (int j = 0; j < q; ++j)
+                    if (j != k) S[i * q + j] = fma(-f, S[k * q + j], S[i * q + j]);
+                S[i * q + k] = -f * S[k * q + k];
             }
-        __syncthreads();
+            __syncwarp();
+        }
+        for (int k = q - 1; k >= 0; --k) {  // undo the row swaps as column swaps
+            const int p = piv[k];
+            if (p != k)
+                for (int i = lane; i < q; i += 32) {
+                    const double t = S[i * q + k];
+                    S[i * q + k] = S[i * q + p];
+                    S[i * q + p] = t;
+                }
+            __syncwarp();
+        }
     }
+    __syncthreads();
     // ---- slices
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
@@ -327,6 +423,161 @@ __global__ void __launch_bounds__(256) large_gain_kernel(uint32_t n, const Large
             dx += s * ctx->y[k];
         }
         K[(size_t)k * n + t] = s;
+    }
+    X[t] += dx;  // ekf.cpp:309
+}
+
+// Gain for q <= QT (QT = 20 or 40), the path cfg4 takes. Same result as large_gain_kernel, arranged for latency: the
+// per-step context is copied to shared memory once, S^-1 is done by one warp, and every thread first pulls its 2 q
+// values of the exchange buffer with independent (unrolled) loads, then does all arithmetic from registers and shared
+// memory. H_o has the fixed structure pose rows = identity, then (range, bearing) pairs -- ekf.cpp:124-132 -- so
+// H_o P for landmark pair c needs only raw rows 0, 1, 2, 3+2c, 4+2c: static register indices.
+template <int QT>
+__global__ void __launch_bounds__(256) large_gain_fast_kernel(uint32_t n, const LargeCtx* __restrict__ ctx, uint32_t q_ub,
+                                                             const double* __restrict__ E, double* __restrict__ hp,
+                                                             double* __restrict__ K, double* __restrict__ X) {
+    __shared__ double S[QT * QT];
+    __shared__ double s_hval[QT][5];
+    __shared__ int s_hk[QT][5], s_hcol[QT][5], s_hnnz[QT], piv[QT];
+    __shared__ double s_y[QT], s_rdiag[QT];
+    const int q = ctx->q;
+    const int tid = threadIdx.x;
+    if (tid < QT) {
+        const bool in = tid < q;
+        s_hnnz[tid] = in ? ctx->hnnz[tid] : 0;
+        s_y[tid] = in ? ctx->y[tid] : 0.0;
+        s_rdiag[tid] = in ? ctx->rdiag[tid] : 1.0;
+#pragma unroll
+        for (int e = 0; e < 5; ++e) {
+            s_hval[tid][e] = in ? ctx->hval[tid][e] : 0.0;
+            s_hk[tid][e] = in ? ctx->hk[tid][e] : 0;
+            s_hcol[tid][e] = in ? ctx->hcol[tid][e] : 0;
+        }
+    }
+    __syncthreads();
+    // S = H_s Psub H_s' + R with Psub(k1,k2) = P(rows[k1], rows[k2]) (every column H_o touches is one of its own rows'
+    // state indices) and H_s the q x q sparse form of H_o: one round of independent loads, then shared memory only.
+    // Zero-padded to QT x QT with the identity on the padding diagonal.
+    __shared__ double T[QT * QT];  // Psub, then H_s Psub
+    __shared__ int s_rows[QT];
+    if (tid < QT) s_rows[tid] = tid < q ? ctx->rows[tid] : 0;
+    __syncthreads();
+    for (int idx = tid; idx < QT * QT; idx += 256) {
+        const int k1 = idx / QT, k2 = idx % QT;
+        S[idx] = (k1 < q && k2 < q) ? E[(size_t)k1 * n + s_rows[k2]] : 0.0;  // Psub, staged in S
+    }
+    __syncthreads();
+    for (int idx = tid; idx < QT * QT; idx += 256) {
+        const int a = idx / QT, j = idx % QT;
+        double hpaj = 0.0;
+        for (int f = 0; f < s_hnnz[a]; ++f) hpaj += s_hval[a][f] * S[s_hk[a][f] * QT + j];
+        T[idx] = hpaj;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < QT * QT; idx += 256) {
+        const int a = idx / QT, b = idx % QT;
+        double sum = 0.0;
+        for (int e = 0; e < s_hnnz[b]; ++e) sum += T[a * QT + s_hk[b][e]] * s_hval[b][e];
+        S[idx] = sum + (a == b ? s_rdiag[a] : 0.0);
+    }
+    __syncthreads();
+    if (tid < 32) {  // in-place Gauss-Jordan with partial pivoting, one warp, lane = row (+32)
+        const int lane = tid;
+        for (int k = 0; k < q; ++k) {
+            double best = -1.0;
+            int p = k;
+            for (int i = k + lane; i < q; i += 32) {
+                const double v = fabs(S[i * QT + k]);
+                if (v > best) {
+                    best = v;
+                    p = i;
+                }
+            }
+            for (int off = 16; off; off >>= 1) {
+                const double ob = __shfl_xor_sync(0xffffffffu, best, off);
+                const int op = __shfl_xor_sync(0xffffffffu, p, off);
+                if (ob > best || (ob == best && op < p)) {
+                    best = ob;
+                    p = op;
+                }
+            }
+            if (lane == 0) piv[k] = p;
+            if (p != k)
+                for (int j = lane; j < q; j += 32) {
+                    const double t = S[k * QT + j];
+                    S[k * QT + j] = S[p * QT + j];
+                    S[p * QT + j] = t;
+                }
+            __syncwarp();
+            const double d = 1.0 / S[k * QT + k];
+            __syncwarp();
+            for (int j = lane; j < q; j += 32) S[k * QT + j] = (j == k ? 1.0 : S[k * QT + j]) * d;
+            __syncwarp();
+            for (int i = lane; i < q; i += 32) {
+                if (i == k) continue;
+                const double f = S[i * QT + k];
+                for (int j = 0; j < q; ++j)
+                    if (j != k) S[i * QT + j] = fma(-f, S[k * QT + j], S[i * QT + j]);
+                S[i * QT + k] = -f * S[k * QT + k];
+            }
+            __syncwarp();
+        }
+        for (int k = q - 1; k >= 0; --k) {
+            const int p = piv[k];
+            if (p != k)
+                for (int i = lane; i < q; i += 32) {
+                    const double t = S[i * QT + k];
+                    S[i * QT + k] = S[i * QT + p];
+                    S[i * QT + p] = t;
+                }
+            __syncwarp();
+        }
+        // padding rows / columns of S^-1 must not contribute
+        for (int idx = lane; idx < QT * QT; idx += 32)
+            if (idx / QT >= q || idx % QT >= q) S[idx] = 0.0;
+    }
+    __syncthreads();
+    const uint32_t t = blockIdx.x * 256 + tid;
+    if (t >= n) return;
+    double raw[QT], pht[QT];
+#pragma unroll
+    for (int k = 0; k < QT; ++k) {
+        raw[k] = k < q ? E[(size_t)k * n + t] : 0.0;
+        pht[k] = k < q ? E[(size_t)(q_ub + k) * n + t] : 0.0;
+    }
+    // H_o P column t
+    double hpv[QT];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) hpv[k] = s_hval[k][0] * raw[k];
+#pragma unroll
+    for (int c = 0; c < (QT - 3) / 2; ++c) {
+        const int kr = 3 + 2 * c, kb = kr + 1;
+        // same summation order as the generic kernel: entries e = 0.. of the row, left to right
+        double sr = 0.0, sb = 0.0;
+        sr += s_hval[kr][0] * raw[0];
+        sr += s_hval[kr][1] * raw[1];
+        sr += s_hval[kr][2] * raw[kr];
+        sr += s_hval[kr][3] * raw[kb];
+        sb += s_hval[kb][0] * raw[0];
+        sb += s_hval[kb][1] * raw[1];
+        sb += s_hval[kb][2] * raw[2];
+        sb += s_hval[kb][3] * raw[kr];
+        sb += s_hval[kb][4] * raw[kb];
+        hpv[kr] = sr;
+        hpv[kb] = sb;
+    }
+    if ((QT - 3) % 2) hpv[QT - 1] = 0.0;
+    double* hpo = hp + (size_t)t * QT;
+#pragma unroll
+    for (int k = 0; k < QT; k += 2) *reinterpret_cast<double2*>(hpo + k) = make_double2(hpv[k], hpv[k + 1]);
+    double dx = 0.0;
+#pragma unroll
+    for (int k = 0; k < QT; ++k) {  // K row t
+        double sum = 0.0;
+#pragma unroll
+        for (int e = 0; e < QT; ++e) sum += pht[e] * S[e * QT + k];
+        dx += sum * s_y[k];
+        K[(size_t)k * n + t] = sum;
     }
     X[t] += dx;  // ekf.cpp:309
 }
@@ -701,7 +952,14 @@ aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, dou
     large_front_kernel<<<1, 1024, 0, h->stream>>>(a, n, h->X, h->A, h->d_obs, h->ctx);
     large_predict_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A,
                                                     (double)h->cfg.ekf_kq);
-    large_gather_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub, h->exch);
+    if (a.q_ub <= 20)
+        large_gather_fast_kernel<20><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub,
+                                                                h->exch);
+    else if (a.q_ub <= 40)
+        large_gather_fast_kernel<40><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub,
+                                                                h->exch);
+    else
+        large_gather_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub, h->exch);
     ASLAM_CUDA(cudaGetLastError());
     h->launches += 3;
     h->q_host = a.q_ub;
@@ -717,7 +975,12 @@ aslam_status large_ekf_phase2(aslam_large* h) {
         ASLAM_CUDA(cudaFuncSetAttribute(large_gain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set = smem;
     }
-    large_gain_kernel<<<nb, 256, smem, h->stream>>>(n, h->ctx, q_ub, h->exch, QT, h->hp, h->K, h->X);
+    if (QT == 20)
+        large_gain_fast_kernel<20><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X);
+    else if (QT == 40)
+        large_gain_fast_kernel<40><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X);
+    else
+        large_gain_kernel<<<nb, 256, smem, h->stream>>>(n, h->ctx, q_ub, h->exch, QT, h->hp, h->K, h->X);
     const uint32_t nrows = h->row_end - h->row_begin;
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
     if (QT == 20 || QT == 40) {
