@@ -328,10 +328,23 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
         "workload": "cfg4: large-map EKF n=8195 (4096 landmarks), q=19 rows of H per step, FP64 P%s"
                     % ("" if world == 1 else ", rows sharded over %d GPUs + 1 NCCL all-reduce/step" % world),
         "steps_per_s": 1e3 / ms, "ms_per_step": ms, "launches_per_step": launches / K,
-        "roofline": {"bound": "hbm", "kernel": "large_update_bulk_kernel<2,20,8,5>", "achieved": achieved,
-                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+        "roofline": {"bound": "hbm", "kernel": "large_update_ws_kernel<2,20,8,5>", "achieved": achieved,
+                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                     "traffic": _ncu_traffic() if world == 1 else None,
                      "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": kernel_ms, "peak_source": peak_src},
     }
+
+
+def _ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the cfg4 streaming update, from the committed
+    `ncu --set full` capture (profiles/r01_traffic.json names the capture); None when the file is absent."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    try:
+        with open(p) as fh:
+            t = json.load(fh)
+        return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 def ukf_large_leg(args, torch, dev):
