@@ -72,6 +72,8 @@ SIGNATURES = {
     "aslam_quat2euler": (_f32, [_f64, _f64, _f64, _f64]),
     "aslam_probe_fp64_tflops": (_i32, [_i32, C.POINTER(_f64)]),
     "aslam_filter_read_state": (_i32, [_vp, _vp]),
+    "aslam_filter_read_state_async": (_i32, [_vp, _vp, C.POINTER(C.c_uint64)]),
+    "aslam_filter_read_wait": (_i32, [_vp, C.c_uint64]),
     "aslam_ekf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
     "aslam_ukf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
     "aslam_filter_destroy": (_i32, [_vp]),

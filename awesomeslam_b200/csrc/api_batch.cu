@@ -132,8 +132,20 @@ struct aslam_filter {
     size_t assoc_capacity = 0;
     double* d_scratch = nullptr;  // export scratch, lazily sized
     size_t scratch_bytes = 0;
-    unsigned char* d_replay = nullptr;  // run_host staging: [steps] messages
-    size_t replay_bytes = 0;
+    // run_host staging: two message blocks filled on `copy_stream` so that the host->device copy of
+    // call k+1 overlaps the kernel of call k (ev_copied / ev_consumed order the two streams)
+    unsigned char* d_replay[2] = {nullptr, nullptr};
+    size_t replay_bytes[2] = {0, 0};
+    int replay_next = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr};
+    cudaEvent_t ev_consumed[2] = {nullptr, nullptr};
+    // read_state_async: X is snapshotted device-side on `stream`, then copied out on `out_stream`
+    double* d_xsnap[2] = {nullptr, nullptr};
+    cudaStream_t out_stream = nullptr;
+    cudaEvent_t ev_snap[2] = {nullptr, nullptr};
+    cudaEvent_t ev_read[2] = {nullptr, nullptr};
+    uint64_t read_seq = 0;
     uint64_t launches = 0;  // filter-step kernels launched so far
 };
 
@@ -203,6 +215,13 @@ aslam_status create_filter(int kind, const aslam_config* cfg, uint32_t batch, in
         if (rc == ASLAM_OK) rc = s;
     };
     if (!cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+    if (!cuda_ok(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+    if (!cuda_ok(cudaStreamCreateWithFlags(&h->out_stream, cudaStreamNonBlocking), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+    for (int i = 0; i < 2; ++i) {
+        cudaEvent_t* evs[] = {&h->ev_copied[i], &h->ev_consumed[i], &h->ev_snap[i], &h->ev_read[i]};
+        for (cudaEvent_t* e : evs)
+            if (!cuda_ok(cudaEventCreateWithFlags(e, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
+    }
     chk(dev_alloc(&h->st.X, (size_t)batch * ld));
     chk(dev_alloc(&h->st.Z, (size_t)batch * ld));
     chk(dev_alloc(&h->st.P, (size_t)batch * ld * ld));
@@ -304,6 +323,34 @@ aslam_status aslam_filter_read_state(aslam_filter* h, double* X) {
     return ASLAM_OK;
 }
 
+/* Pipelined variant: X is snapshotted on the handle's stream (device to device, behind everything
+ * enqueued so far) and copied to the caller's buffer on a second stream, so the next run_* call does
+ * not wait for the PCIe transfer. *ticket identifies the read for aslam_filter_read_wait. */
+aslam_status aslam_filter_read_state_async(aslam_filter* h, double* X, uint64_t* ticket) {
+    if (!h || !X) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)h->st.batch * h->st.ld * sizeof(double);
+    const int s = (int)(h->read_seq & 1);
+    if (!h->d_xsnap[s]) ASLAM_CUDA(cudaMalloc((void**)&h->d_xsnap[s], bytes));
+    ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_read[s], 0));  // snapshot s was last drained two reads ago
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_xsnap[s], h->st.X, bytes, cudaMemcpyDeviceToDevice, h->stream));
+    ASLAM_CUDA(cudaEventRecord(h->ev_snap[s], h->stream));
+    ASLAM_CUDA(cudaStreamWaitEvent(h->out_stream, h->ev_snap[s], 0));
+    ASLAM_CUDA(cudaMemcpyAsync(X, h->d_xsnap[s], bytes, cudaMemcpyDeviceToHost, h->out_stream));
+    ASLAM_CUDA(cudaEventRecord(h->ev_read[s], h->out_stream));
+    if (ticket) *ticket = h->read_seq;
+    h->read_seq += 1;
+    return ASLAM_OK;
+}
+
+/* Blocks until the read with this ticket (and every earlier one) has landed in its host buffer. */
+aslam_status aslam_filter_read_wait(aslam_filter* h, uint64_t ticket) {
+    if (!h || ticket >= h->read_seq) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    ASLAM_CUDA(cudaEventSynchronize(h->ev_read[ticket & 1]));
+    return ASLAM_OK;
+}
+
 float aslam_quat2euler(double w, double x, double y, double z) {
     const float fw = (float)w, fx = (float)x, fy = (float)y, fz = (float)z;
     // tools.h:64: float arithmetic throughout, atan2f
@@ -322,21 +369,31 @@ aslam_status aslam_ukf_create(const aslam_config* cfg, uint32_t batch, int32_t d
 aslam_status aslam_filter_destroy(aslam_filter* h) {
     if (!h) return ASLAM_OK;
     cudaSetDevice(h->device);
-    if (h->stream) cudaStreamSynchronize(h->stream);
-    void* ptrs[] = {h->st.X,      h->st.Z,       h->st.P,     h->st.A,        h->st.N,    h->st.status,
-                    h->st.flags,  h->st.wcount,  h->st.wrange, h->st.wbearing, h->st.whits, h->st.llt_fail,
-                    h->d_odom64,  h->d_odom32,   h->d_range,  h->d_bearing,   h->d_offsets, h->d_assoc,
-                    h->d_scratch, h->d_replay};
+    cudaStream_t streams[] = {h->stream, h->copy_stream, h->out_stream};
+    for (cudaStream_t st : streams)
+        if (st) cudaStreamSynchronize(st);
+    void* ptrs[] = {h->st.X,      h->st.Z,        h->st.P,        h->st.A,        h->st.N,     h->st.status,
+                    h->st.flags,  h->st.wcount,   h->st.wrange,   h->st.wbearing, h->st.whits, h->st.llt_fail,
+                    h->d_odom64,  h->d_odom32,    h->d_range,     h->d_bearing,   h->d_offsets, h->d_assoc,
+                    h->d_scratch, h->d_replay[0], h->d_replay[1], h->d_xsnap[0],  h->d_xsnap[1]};
     for (void* p : ptrs)
         if (p) cudaFree(p);
-    if (h->stream) cudaStreamDestroy(h->stream);
+    for (int i = 0; i < 2; ++i) {
+        cudaEvent_t evs[] = {h->ev_copied[i], h->ev_consumed[i], h->ev_snap[i], h->ev_read[i]};
+        for (cudaEvent_t e : evs)
+            if (e) cudaEventDestroy(e);
+    }
+    for (cudaStream_t st : streams)
+        if (st) cudaStreamDestroy(st);
     delete h;
     return ASLAM_OK;
 }
 
 aslam_status aslam_filter_sync(aslam_filter* h) {
     if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaStreamSynchronize(h->copy_stream));
     ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->out_stream));
     return ASLAM_OK;
 }
 void* aslam_filter_stream(aslam_filter* h) { return h ? (void*)h->stream : nullptr; }
@@ -481,29 +538,37 @@ aslam_status aslam_filter_run_host(aslam_filter* h, uint32_t steps, const aslam_
     const size_t n = (size_t)steps * h->st.batch, no = n * obs_per_filter;
     // one staging block: 4 double arrays, then 2 + 2*obs float arrays (all 8-byte aligned starts)
     const size_t bytes = n * 4 * sizeof(double) + (n * 2 + no * 2) * sizeof(float) + 64;
-    if (bytes > h->replay_bytes) {
+    const int b = h->replay_next;
+    h->replay_next ^= 1;
+    if (bytes > h->replay_bytes[b]) {
         ASLAM_CUDA(cudaStreamSynchronize(h->stream));
-        if (h->d_replay) cudaFree(h->d_replay);
-        h->d_replay = nullptr;
-        h->replay_bytes = 0;
-        ASLAM_CUDA(cudaMalloc((void**)&h->d_replay, bytes));
-        h->replay_bytes = bytes;
+        ASLAM_CUDA(cudaStreamSynchronize(h->copy_stream));
+        if (h->d_replay[b]) cudaFree(h->d_replay[b]);
+        h->d_replay[b] = nullptr;
+        h->replay_bytes[b] = 0;
+        ASLAM_CUDA(cudaMalloc((void**)&h->d_replay[b], bytes));
+        h->replay_bytes[b] = bytes;
     }
-    double* d64 = reinterpret_cast<double*>(h->d_replay);
+    // block b was last read by the kernel of the call before the previous one
+    cudaStream_t cs = h->copy_stream;
+    ASLAM_CUDA(cudaStreamWaitEvent(cs, h->ev_consumed[b], 0));
+    double* d64 = reinterpret_cast<double*>(h->d_replay[b]);
     float* d32 = reinterpret_cast<float*>(d64 + 4 * n);
     const cudaMemcpyKind k = cudaMemcpyHostToDevice;
-    ASLAM_CUDA(cudaMemcpyAsync(d64 + 0 * n, o->x, n * sizeof(double), k, h->stream));
-    ASLAM_CUDA(cudaMemcpyAsync(d64 + 1 * n, o->y, n * sizeof(double), k, h->stream));
-    ASLAM_CUDA(cudaMemcpyAsync(d64 + 2 * n, o->vx, n * sizeof(double), k, h->stream));
-    ASLAM_CUDA(cudaMemcpyAsync(d64 + 3 * n, o->az, n * sizeof(double), k, h->stream));
-    ASLAM_CUDA(cudaMemcpyAsync(d32 + 0 * n, o->yaw, n * sizeof(float), k, h->stream));
-    ASLAM_CUDA(cudaMemcpyAsync(d32 + 1 * n, o->dt, n * sizeof(float), k, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 0 * n, o->x, n * sizeof(double), k, cs));
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 1 * n, o->y, n * sizeof(double), k, cs));
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 2 * n, o->vx, n * sizeof(double), k, cs));
+    ASLAM_CUDA(cudaMemcpyAsync(d64 + 3 * n, o->az, n * sizeof(double), k, cs));
+    ASLAM_CUDA(cudaMemcpyAsync(d32 + 0 * n, o->yaw, n * sizeof(float), k, cs));
+    ASLAM_CUDA(cudaMemcpyAsync(d32 + 1 * n, o->dt, n * sizeof(float), k, cs));
     float* dr = d32 + 2 * n;
     float* db = dr + no;
     if (no) {
-        ASLAM_CUDA(cudaMemcpyAsync(dr, range, no * sizeof(float), k, h->stream));
-        ASLAM_CUDA(cudaMemcpyAsync(db, bearing, no * sizeof(float), k, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(dr, range, no * sizeof(float), k, cs));
+        ASLAM_CUDA(cudaMemcpyAsync(db, bearing, no * sizeof(float), k, cs));
     }
+    ASLAM_CUDA(cudaEventRecord(h->ev_copied[b], cs));
+    ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copied[b], 0));
     aslam_odom d;
     d.x = d64;
     d.y = d64 + n;
@@ -511,7 +576,9 @@ aslam_status aslam_filter_run_host(aslam_filter* h, uint32_t steps, const aslam_
     d.az = d64 + 3 * n;
     d.yaw = d32;
     d.dt = d32 + n;
-    return aslam_filter_run_device(h, steps, &d, dr, db, obs_per_filter);
+    const aslam_status rc = aslam_filter_run_device(h, steps, &d, dr, db, obs_per_filter);
+    ASLAM_CUDA(cudaEventRecord(h->ev_consumed[b], h->stream));
+    return rc;
 }
 
 uint64_t aslam_filter_launch_count(aslam_filter* h) { return h ? h->launches : 0; }

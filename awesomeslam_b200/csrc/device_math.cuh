@@ -15,7 +15,17 @@ namespace aslam {
 // float product.
 __device__ __forceinline__ float normalize_angle(float theta, float pi) {
     const float two_pi = __fmul_rn(2.0f, pi);
-    float ret = fmodf(theta, two_pi);
+    // fmodf is exact, so its two common cases are written out: |theta| < 2pi returns theta itself and
+    // 2pi <= |theta| < 4pi returns |theta| - 2pi, a float subtraction that is exact (Sterbenz), with
+    // theta's sign. Everything else (and NaN/Inf) takes the library routine.
+    const float a = fabsf(theta);
+    float ret;
+    if (a < two_pi)
+        ret = theta;
+    else if (a < __fmul_rn(2.0f, two_pi))
+        ret = copysignf(__fsub_rn(a, two_pi), theta);
+    else
+        ret = fmodf(theta, two_pi);
     ret = ret > pi ? __fsub_rn(ret, two_pi) : ret;
     ret = ret < -pi ? __fadd_rn(ret, two_pi) : ret;
     return ret;
@@ -23,9 +33,12 @@ __device__ __forceinline__ float normalize_angle(float theta, float pi) {
 
 // tools.h:53-59 eulerDistance on two Points whose coordinates are float-exact doubles
 // (structures.h:52): dx, dy rounded to float; sqrtf(dx*dx + dy*dy) with separate roundings.
+// The reference subtracts the float-exact doubles and rounds the difference to float; that is the
+// float subtraction: the double difference is exact whenever the exponents are within 29 bits, and
+// beyond that both roundings return the larger operand.
 __device__ __forceinline__ float euler_distance(float ax, float ay, float bx, float by) {
-    const float dx = (float)((double)ax - (double)bx);
-    const float dy = (float)((double)ay - (double)by);
+    const float dx = __fsub_rn(ax, bx);
+    const float dy = __fsub_rn(ay, by);
     return __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
 }
 

@@ -38,6 +38,25 @@ struct Geo {
     static_assert(NP % CPT == 0, "NP must be a multiple of CPT");
 };
 
+// One message of one filter, staged in shared memory by cp.async one step ahead of its use.
+struct __align__(16) MsgBuf {
+    double ox, oy, vx, az;
+    float yaw, dt;
+    uint32_t base, cnt;
+    float rng[ASLAM_MAX_OBS];
+    float brg[ASLAM_MAX_OBS];
+};
+
+__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 template <int NP>
 struct __align__(16) EkfSlot {
     double V[2][NP * 4];  // block rows of H_g P: pitch 4 for the pose block, 2 for landmark blocks
@@ -47,6 +66,8 @@ struct __align__(16) EkfSlot {
     double Y0[NP];        // Z - h(x_pred), bearings wrapped (ekf.cpp:302-307)
     double H[(NP - 3) / 2 + 1][4];
     double a00, a10;
+    float Xf[NP];         // float copy of X for the association distances (ekf.cpp:161,166 round to float)
+    MsgBuf msg[2];        // this step's message and the next one (in flight)
     FrontSlot fr;
 };
 
@@ -56,6 +77,38 @@ struct EkfParams {
     FrontParams fp;
     double kq, kr_pose, kr_lm, kp_lm;
 };
+
+// Start the asynchronous copy of message `step` of filter f into m: the six odometry fields by six
+// threads, the observation list spread over the filter's threads. No register is held across the wait.
+template <int TPF>
+__device__ __forceinline__ void prefetch_message(MsgBuf& m, const BatchInput& in, uint32_t batch, uint32_t f,
+                                                 uint32_t step, int ct) {
+    const size_t si = (size_t)step * batch + f;
+    uint32_t base, cnt;
+    if (in.offsets) {
+        base = in.offsets[f];
+        cnt = in.offsets[f + 1] - base;
+    } else {
+        base = (uint32_t)(si * in.obs_per_filter);
+        cnt = in.obs_per_filter;
+    }
+    if (ct == 6) {
+        m.base = base;
+        m.cnt = cnt;
+    }
+    if (cnt > ASLAM_MAX_OBS) cnt = ASLAM_MAX_OBS;
+    if (ct < 4) {
+        const double* src = ct == 0 ? in.ox : ct == 1 ? in.oy : ct == 2 ? in.vx : in.az;
+        cp_async8(&m.ox + ct, src + si);
+    } else if (ct < 6) {
+        const float* src = ct == 4 ? in.yaw : in.dt;
+        cp_async4(&m.yaw + (ct - 4), src + si);
+    }
+    for (uint32_t o = ct; o < cnt; o += TPF) {
+        cp_async4(&m.rng[o], in.range + base + o);
+        cp_async4(&m.brg[o], in.bearing + base + o);
+    }
+}
 
 template <int NP, int CPT>
 __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(const EkfParams kp) {
@@ -88,6 +141,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
     for (int j = ct; j < NP; j += TPF) {
         s.X[j] = live ? kp.st.X[(size_t)f * NP + j] : 0.0;
         s.Z[j] = live ? kp.st.Z[(size_t)f * NP + j] : 0.0;
+        s.Xf[j] = (float)s.X[j];
     }
     if (ct == 0) {
         s.fr.N = live ? kp.st.N[f] : 3;
@@ -98,53 +152,57 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
         s.a00 = live ? kp.st.A[2 * (size_t)f] : 1.0;
         s.a10 = live ? kp.st.A[2 * (size_t)f + 1] : 0.0;
     }
+    if (live) prefetch_message<TPF>(s.msg[0], kp.in, kp.st.batch, f, 0, ct);
+    cp_async_wait_all();
     __syncthreads();
 
     for (uint32_t step = 0; step < kp.in.steps; ++step) {
-        const size_t si = (size_t)step * kp.st.batch + f;
         // ---- cbOdom gate (ekf.cpp:76): nothing happens before the first observation message
         const bool gated = !live || (s.fr.flags & FLAG_INIT_Z);
         if (threadIdx.x == 0) s_lcta = 0;
+        // this step's message has landed (waited for behind the previous step); the next one starts now and is in
+        // flight for the whole step
+        const MsgBuf& m = s.msg[step & 1];
+        if (live && step + 1 < kp.in.steps) prefetch_message<TPF>(s.msg[(step + 1) & 1], kp.in, kp.st.batch, f, step + 1, ct);
         // ---- updateZandA, ekf.cpp:139-142
-        if (ct == 0 && !gated) {
-            s.fr.ox = kp.in.ox[si];
-            s.fr.oy = kp.in.oy[si];
-            s.fr.yaw = kp.in.yaw[si];
-            s.fr.vx = kp.in.vx[si];
-            s.fr.az = kp.in.az[si];
-            s.fr.dt = kp.in.dt[si];
-            s.Z[0] = s.fr.ox;
-            s.Z[1] = s.fr.oy;
-            s.Z[2] = (double)s.fr.yaw;
-            uint32_t base, cnt;
-            if (kp.in.offsets) {
-                base = kp.in.offsets[f];
-                cnt = kp.in.offsets[f + 1] - base;
-            } else {
-                base = (uint32_t)(si * kp.in.obs_per_filter);
-                cnt = kp.in.obs_per_filter;
+        if (!gated) {
+            if (ct == 0) {
+                s.fr.ox = m.ox;
+                s.fr.oy = m.oy;
+                s.fr.yaw = m.yaw;
+                s.fr.vx = m.vx;
+                s.fr.az = m.az;
+                s.fr.dt = m.dt;
+                s.Z[0] = m.ox;
+                s.Z[1] = m.oy;
+                s.Z[2] = (double)m.yaw;
+                uint32_t cnt = m.cnt;
+                if (cnt > ASLAM_MAX_OBS) {
+                    cnt = ASLAM_MAX_OBS;
+                    s.fr.status |= ASLAM_ST_OBS_OVERFLOW;
+                }
+                s.fr.obs_base = m.base;
+                s.fr.nobs = cnt;
+                s.fr.unassoc = 0;
             }
-            if (cnt > ASLAM_MAX_OBS) {
-                cnt = ASLAM_MAX_OBS;
-                s.fr.status |= ASLAM_ST_OBS_OVERFLOW;
-            }
-            s.fr.obs_base = base;
-            s.fr.nobs = cnt;
+            for (int l = ct; l < (int)(sizeof(s.fr.owner) / sizeof(int32_t)); l += TPF) s.fr.owner[l] = 0;
         }
         __syncthreads();
-        if (!gated) front_phase_a(s.fr, kp.fp, s.X, s.Z, kp.in.range, kp.in.bearing, f, ct, TPF);
+        if (!gated) front_phase_a<true>(s.fr, kp.fp, s.Xf, s.Z, m.rng, m.brg, 0u, f, ct, TPF);
         __syncthreads();
-        if (ct == 0 && !gated) {
+        if (!gated) {
             int32_t* assoc = nullptr;
             if (kp.in.assoc && step + 1 == kp.in.steps) assoc = kp.in.assoc + (kp.in.offsets ? s.fr.obs_base : f * kp.in.obs_per_filter);
-            front_phase_b(s.fr, kp.fp, s.X, s.Z, f, assoc);
-            if (s.fr.flags & FLAG_INIT_X) {  // ekf.cpp:87-91
-                s.fr.flags &= ~FLAG_INIT_X;
-                for (uint32_t j = 0; j < s.fr.N; ++j) s.X[j] = s.Z[j];
-            }
+            front_phase_b_assoc(s.fr, s.Z, assoc, ct, TPF);
+        }
+        if (ct == 0 && !gated) {
+            front_phase_b_wait(s.fr, kp.fp, s.X, s.Z, f);
+            // ekf.cpp:87-91 X = Z on the first processed message: the pose rows here, the landmark rows
+            // (other threads may still be writing Z) behind the next barrier
+            const bool initx = s.fr.flags & FLAG_INIT_X;
             motion_jacobian(s.fr.vx, s.fr.az, s.fr.dt, s.Z[2], s.a00, s.a10);  // ekf.cpp:206-212
             // slam(): ekf.cpp:295-296
-            double x = s.X[0], y = s.X[1], th = s.X[2];
+            double x = initx ? s.Z[0] : s.X[0], y = initx ? s.Z[1] : s.X[1], th = initx ? s.Z[2] : s.X[2];
             motion_model(x, y, th, (float)s.fr.vx, (float)s.fr.az, s.fr.dt);
             s.X[0] = x;
             s.X[1] = y;
@@ -154,6 +212,9 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
         __syncthreads();
         const uint32_t N = s.fr.N;
         const int lcta = s_lcta;
+        const bool initx = !gated && (s.fr.flags & FLAG_INIT_X);
+        if (initx)
+            for (uint32_t j = 3 + ct; j < N; j += TPF) s.X[j] = s.Z[j];
         // ---- growth of P (ekf.cpp:277): new diagonal entries, the rest of the new rows/cols is 0
         if (s.fr.grew_from && !gated) {
             const uint32_t g0 = s.fr.grew_from;
@@ -213,6 +274,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                 s.Y0[4 + 2 * l] = (double)normalize_angle((float)(s.Z[4 + 2 * l] - br), kp.fp.pi);
             }
             if (ct == 0) {
+                if (initx) s.fr.flags &= ~FLAG_INIT_X;
                 s.Y0[0] = s.Z[0] - x;
                 s.Y0[1] = s.Z[1] - y;
                 s.Y0[2] = (double)normalize_angle((float)(s.Z[2] - th), kp.fp.pi);
@@ -344,8 +406,13 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
         if (!gated) {
 #pragma unroll
             for (int c = 0; c < CPT; ++c)
-                if ((uint32_t)(j0 + c) < N) s.X[j0 + c] += dl[c];
+                if ((uint32_t)(j0 + c) < N) {
+                    const double xn = s.X[j0 + c] + dl[c];
+                    s.X[j0 + c] = xn;
+                    s.Xf[j0 + c] = (float)xn;
+                }
         }
+        cp_async_wait_all();  // every thread waits for its own copies of the next message; the barrier publishes them
         __syncthreads();
     }
 

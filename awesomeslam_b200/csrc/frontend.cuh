@@ -23,6 +23,11 @@ struct FrontSlot {
     float2 wpt[ASLAM_MAX_WAIT];  // wait-list entries projected with the CURRENT pose (ekf.cpp:228-234)
     uint32_t nobs, obs_base, wcount, N, status, flags, grew_from;
     int32_t promote;
+    // TRACK mode of phase A: owner[l] = 1 + the LAST observation associated with landmark l (the one
+    // whose Z write survives in the reference's sequential loop), unassoc = some observation missed
+    int32_t owner[(64 - 3) / 2 + 2];
+    uint32_t unassoc;
+    uint8_t ohit[ASLAM_MAX_OBS];  // TRACK: the observation was associated (decided with the pre-promotion N)
     double ox, oy, vx, az;
     float yaw, dt;
 };
@@ -36,15 +41,19 @@ struct FrontParams {
 };
 
 // Phase A. X, Z: the filter's state vectors in shared memory (Z[0..2] already hold the
-// odometry pose). lane/width: this thread's index in the filter's thread group.
-__device__ __forceinline__ void front_phase_a(FrontSlot& s, const FrontParams& fp, const double* X,
+// odometry pose); X may be a float copy of the state (the reference rounds the landmark coordinates
+// to float before the distance, ekf.cpp:161,166). lane/width: this thread's index in the filter's
+// thread group; observation o is range[obs_first + o]. TRACK: also fill owner[] / unassoc (both zeroed
+// by the caller before the call).
+template <bool TRACK = false, typename XT = double>
+__device__ __forceinline__ void front_phase_a(FrontSlot& s, const FrontParams& fp, const XT* X,
                                               const double* Z, const float* range, const float* bearing,
-                                              uint32_t f, int lane, int width) {
+                                              uint32_t obs_first, uint32_t f, int lane, int width) {
     const double z0 = Z[0], z1 = Z[1], z2 = Z[2];
     const uint32_t N = s.N;
     for (uint32_t o = lane; o < s.nobs; o += width) {
-        const float r = range[s.obs_base + o];
-        const float b = normalize_angle(bearing[s.obs_base + o], fp.pi);
+        const float r = range[obs_first + o];
+        const float b = normalize_angle(bearing[obs_first + o], fp.pi);
         const float2 pt = to_point(r, b, z0, z1, z2);
         int32_t corr = 0;
         float mind = 0.0f;
@@ -63,6 +72,14 @@ __device__ __forceinline__ void front_phase_a(FrontSlot& s, const FrontParams& f
         s.opt[o] = pt;
         s.ocorr[o] = corr;
         s.omind[o] = mind;
+        if (TRACK) {
+            const bool hit = N > 3 && mind < fp.thresh;  // ekf.cpp:175
+            s.ohit[o] = hit;
+            if (hit)
+                atomicMax(&s.owner[corr >> 1], (int32_t)o + 1);
+            else
+                s.unassoc = 1u;
+        }
     }
     const float* wr = fp.wrange + (size_t)f * ASLAM_MAX_WAIT;
     const float* wb = fp.wbearing + (size_t)f * ASLAM_MAX_WAIT;
@@ -108,6 +125,42 @@ __device__ __forceinline__ void wait_list_update(FrontSlot& s, const FrontParams
     }
 }
 
+// Promotion of wait-list entries seen exactly `occ` times and growth of X/Z (ekf.cpp:190-203,
+// 255-290; the caller grows P). One thread per filter.
+__device__ __forceinline__ void front_promote(FrontSlot& s, const FrontParams& fp, double* X, double* Z, uint32_t f) {
+    if (!s.promote) return;
+    s.promote = 0;
+    float* wr = fp.wrange + (size_t)f * ASLAM_MAX_WAIT;
+    float* wb = fp.wbearing + (size_t)f * ASLAM_MAX_WAIT;
+    uint32_t* wh = fp.whits + (size_t)f * ASLAM_MAX_WAIT;
+    uint32_t fresh = 0;
+    for (uint32_t w = 0; w < s.wcount; ++w) fresh += (wh[w] == (uint32_t)fp.occ);
+    if (!fresh) return;
+    const uint32_t cacheN = s.N;
+    const uint32_t newN = cacheN + 2 * fresh;
+    const bool accept = newN < (uint32_t)fp.cap;  // ekf.cpp:263
+    uint32_t k = cacheN;
+    for (uint32_t w = 0; w < s.wcount; ++w) {
+        if (wh[w] != (uint32_t)fp.occ) continue;
+        wh[w] += 1;  // ekf.cpp:195: bumped even when the batch is then rejected
+        if (!accept) continue;
+        const double r = (double)wr[w], b = (double)wb[w];
+        Z[k] = r;
+        Z[k + 1] = b;
+        double sn, cs;
+        sincos(__dadd_rn(Z[2], b), &sn, &cs);  // ekf.cpp:287-288
+        X[k] = __dadd_rn(Z[0], __dmul_rn(r, cs));
+        X[k + 1] = __dadd_rn(Z[1], __dmul_rn(r, sn));
+        k += 2;
+    }
+    if (accept) {
+        s.grew_from = cacheN;
+        s.N = newN;
+    } else {
+        s.status |= ASLAM_ST_CAP_REJECTED;
+    }
+}
+
 // Phase B, one thread per filter. Writes Z for associated observations, maintains the
 // wait-list, promotes entries seen exactly `occ` times and grows X/Z (the caller grows P).
 // assoc: per-observation output for this filter or nullptr.
@@ -124,39 +177,34 @@ __device__ __forceinline__ void front_phase_b(FrontSlot& s, const FrontParams& f
         if (assoc) assoc[o] = -1;
         wait_list_update(s, fp, f, o);
     }
-    if (s.promote) {  // ekf.cpp:190-203
-        s.promote = 0;
-        float* wr = fp.wrange + (size_t)f * ASLAM_MAX_WAIT;
-        float* wb = fp.wbearing + (size_t)f * ASLAM_MAX_WAIT;
-        uint32_t* wh = fp.whits + (size_t)f * ASLAM_MAX_WAIT;
-        uint32_t fresh = 0;
-        for (uint32_t w = 0; w < s.wcount; ++w) fresh += (wh[w] == (uint32_t)fp.occ);
-        if (fresh) {
-            const uint32_t cacheN = s.N;
-            const uint32_t newN = cacheN + 2 * fresh;
-            const bool accept = newN < (uint32_t)fp.cap;  // ekf.cpp:263
-            uint32_t k = cacheN;
-            for (uint32_t w = 0; w < s.wcount; ++w) {
-                if (wh[w] != (uint32_t)fp.occ) continue;
-                wh[w] += 1;  // ekf.cpp:195: bumped even when the batch is then rejected
-                if (!accept) continue;
-                const double r = (double)wr[w], b = (double)wb[w];
-                Z[k] = r;
-                Z[k + 1] = b;
-                double sn, cs;
-                sincos(__dadd_rn(Z[2], b), &sn, &cs);  // ekf.cpp:287-288
-                X[k] = __dadd_rn(Z[0], __dmul_rn(r, cs));
-                X[k + 1] = __dadd_rn(Z[1], __dmul_rn(r, sn));
-                k += 2;
-            }
-            if (accept) {
-                s.grew_from = cacheN;
-                s.N = newN;
-            } else {
-                s.status |= ASLAM_ST_CAP_REJECTED;
-            }
+    front_promote(s, fp, X, Z, f);
+}
+
+// Phase B split for a TRACK-mode phase A. The Z writes of the associated observations are independent
+// of the wait-list (which only reads floats computed in phase A), so they run on all the filter's
+// threads: observation o writes iff it is the last one associated with its landmark -- exactly what
+// survives the reference's sequential loop (ekf.cpp:175-181).
+__device__ __forceinline__ void front_phase_b_assoc(const FrontSlot& s, double* Z,
+                                                    int32_t* assoc, int lane, int width) {
+    for (uint32_t o = lane; o < s.nobs; o += width) {
+        const bool hit = s.ohit[o];  // not re-derived from s.N: the serial half may be growing it right now
+        const int32_t corr = s.ocorr[o];
+        if (hit && s.owner[corr >> 1] == (int32_t)o + 1) {
+            Z[3 + corr] = (double)s.orng[o];
+            Z[4 + corr] = (double)s.obrg[o];
         }
+        if (assoc) assoc[o] = hit ? corr : -1;
     }
+}
+// ... and the order-dependent rest on one thread: wait-list hits/appends in observation order, promotion.
+__device__ __forceinline__ void front_phase_b_wait(FrontSlot& s, const FrontParams& fp, double* X, double* Z,
+                                                   uint32_t f) {
+    s.grew_from = 0;
+    if (s.unassoc) {
+        for (uint32_t o = 0; o < s.nobs; ++o)
+            if (!s.ohit[o]) wait_list_update(s, fp, f, o);
+    }
+    front_promote(s, fp, X, Z, f);
 }
 
 }  // namespace aslam

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
             s.fr.nobs = cnt;
         }
         __syncthreads();
-        front_phase_a(s.fr, kp.fp, s.X, s.Z, kp.in.range, kp.in.bearing, f, tid, UTHREADS);
+        front_phase_a(s.fr, kp.fp, s.X, s.Z, kp.in.range, kp.in.bearing, s.fr.obs_base, f, tid, UTHREADS);
         __syncthreads();
         if (tid == 0) {
             int32_t* assoc = nullptr;

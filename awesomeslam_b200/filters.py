@@ -146,6 +146,17 @@ class BatchedFilter:
         capi.check(self._lib.aslam_filter_read_state(self._h, capi.ptr(X_out)))
         self._keep.clear()
 
+    def read_state_async(self, X_out):
+        """Pipelined read of param.X: returns a ticket at once; X_out (keep it alive, ideally pinned) is
+        complete after read_wait(ticket) or sync(). Does not stall the next run_host/run_device call."""
+        assert X_out.dtype == np.float64 and X_out.size == self.batch * self.ld and X_out.flags["C_CONTIGUOUS"]
+        t = C.c_uint64(0)
+        capi.check(self._lib.aslam_filter_read_state_async(self._h, capi.ptr(X_out), C.byref(t)))
+        return int(t.value)
+
+    def read_wait(self, ticket):
+        capi.check(self._lib.aslam_filter_read_wait(self._h, ticket))
+
     def get_aux(self):
         B, ld = self.batch, self.ld
         Z = np.zeros((B, ld), np.float64)

@@ -138,7 +138,9 @@ aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const asla
                                      const float* d_range, const float* d_bearing, uint32_t obs_per_filter);
 
 /* Same replay from HOST buffers (the end-to-end entry point): copies the `steps` messages to the
- * device on the handle's stream, then runs them as one launch. Asynchronous. */
+ * device, then runs them as one launch. Asynchronous: the copy is enqueued on a second stream into
+ * one of two staging blocks, so the transfer of call k+1 overlaps the kernel of call k; the host
+ * buffers must stay valid until aslam_filter_sync (pinned memory for a truly asynchronous copy). */
 aslam_status aslam_filter_run_host(aslam_filter* h, uint32_t steps, const aslam_odom* odom, const float* range,
                                    const float* bearing, uint32_t obs_per_filter);
 /* Number of filter-step kernels this handle has launched (bench.py's gpu_launches). */
@@ -156,6 +158,11 @@ aslam_status aslam_filter_get_state(aslam_filter* h, double* X, double* P, uint3
                                     uint32_t* status);
 /* param.X only, into a caller buffer [batch][ld] (pinned memory for the end-to-end path). */
 aslam_status aslam_filter_read_state(aslam_filter* h, double* X);
+/* Pipelined form of the same read (the publish half of cbOdom, ekf.cpp:97-98, without stalling the
+ * next message): returns at once; X is complete after aslam_filter_read_wait(h, *ticket) or
+ * aslam_filter_sync. At most two reads may be outstanding per destination buffer pair. */
+aslam_status aslam_filter_read_state_async(aslam_filter* h, double* X, uint64_t* ticket);
+aslam_status aslam_filter_read_wait(aslam_filter* h, uint64_t ticket);
 /* Z [batch][ld]; EKF only: a00/a10 [batch] = A(0,0), A(1,0) (ekf.cpp:210-211) */
 aslam_status aslam_filter_get_aux(aslam_filter* h, double* Z, double* a00, double* a10);
 /* wait-list export: count [batch]; range/bearing/hits [batch][ASLAM_MAX_WAIT] */

@@ -149,6 +149,35 @@ def test_batched_split_launch_equals_one_launch(aslam):
     a.close(); b.close()
 
 
+def test_pipelined_host_path_equals_one_launch(aslam):
+    """run_host without a sync in between (double-buffered staging, copy stream) plus the pipelined
+    read_state_async / read_wait: every intermediate X equals the one a synchronous replay of the same
+    prefix gives, and the final state is bit-identical to the single-launch replay."""
+    lmx, lmy = aslam.map_cfg3()
+    B, T, L, C = 96, 48, 16, 6
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=7)
+    a = aslam.BatchedFilter("ekf", B, 0, max_state_dim=36)
+    b = aslam.BatchedFilter("ekf", B, 0, max_state_dim=36)
+    ref = aslam.BatchedFilter("ekf", B, 0, max_state_dim=36)
+    a.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+    outs = [np.zeros((B, b.ld)) for _ in range(T // C)]
+    tickets = []
+    for i, k in enumerate(range(0, T, C)):
+        sl = slice(k, k + C)
+        b.run_host(C, rp.x[sl], rp.y[sl], rp.yaw[sl], rp.vx[sl], rp.az[sl], rp.dt[sl], rp.range[sl], rp.bearing[sl], L)
+        tickets.append(b.read_state_async(outs[i]))
+    for i, k in enumerate(range(0, T, C)):
+        b.read_wait(tickets[i])
+        sl = slice(k, k + C)
+        ref.run_host(C, rp.x[sl], rp.y[sl], rp.yaw[sl], rp.vx[sl], rp.az[sl], rp.dt[sl], rp.range[sl], rp.bearing[sl], L)
+        assert np.array_equal(outs[i], ref.get_state(want_P=False, want_assoc=False)["X"]), i
+    b.sync()
+    sa, sb = a.get_state(), b.get_state()
+    assert np.array_equal(sa["X"], sb["X"]) and np.array_equal(sa["P"], sb["P"]) and np.array_equal(sa["N"], sb["N"])
+    assert np.array_equal(outs[-1], sb["X"])
+    a.close(); b.close(); ref.close()
+
+
 def test_single_filter_class_mirror(aslam, orc):
     """The reference-named class: cbSensorLandmark / cbOdom, Landmarks out (common.h:93-108)."""
     lmx, lmy = aslam.map_cfg1()
