@@ -172,7 +172,7 @@ def reference_arm(args):
         "gpu_launches": 0,
         "note": "reference (ROS1 + Eigen3) cannot be built in this image; this is the CPU oracle port of its filter math",
     }
-    print(json.dumps(line))
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------ GPU legs
@@ -401,8 +401,27 @@ def ukf_large_leg(args, torch, dev):
                          "peak_source": "aslam_probe_dmma_tflops (DMMA chain, this run)"}}
 
 
+_REAL_STDOUT = None
+
+
+def _claim_stdout():
+    """Route fd 1 to stderr for the whole run and keep the real stdout for the ONE JSON line: libraries
+    (NCCL prints its version banner to stdout on some boxes) must not add lines to it."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
     args = parse()
+    _claim_stdout()
     if args.impl == "reference":
         reference_arm(args)
         return
@@ -482,7 +501,7 @@ def main():
         line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": nthr, "kind": "port",
                                 "sample": "cfg3 filters x 120 messages from reset, OpenMP over filters, %.1f s" % sec}
         line["speedup_e2e_vs_cpu"] = e2e / ups
-    print(json.dumps(line))
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
