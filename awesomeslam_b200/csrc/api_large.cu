@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdlib>
+#include <cstring>
 #include <new>
 #include <vector>
 
@@ -11,8 +12,9 @@
 #include "large.hpp"
 
 namespace aslam {
-aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m);
-aslam_status large_ekf_phase2(aslam_large* h);
+aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m,
+                              bool peer = false);
+aslam_status large_ekf_phase2(aslam_large* h, bool peer = false);
 aslam_status large_ukf_create(aslam_large* h);
 void large_ukf_destroy(aslam_large* h);
 aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m);
@@ -130,7 +132,9 @@ aslam_status aslam_large_destroy(aslam_large* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ukf) large_ukf_destroy(h);
-    void* ptrs[] = {h->P, h->X, h->A, h->ctx, h->d_obs, h->exch, h->hp, h->K};
+    for (int p = 0; p < LARGE_MAX_PEERS; ++p)
+        if (h->peer_ipc[p] && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
+    void* ptrs[] = {h->P, h->X, h->A, h->ctx, h->d_obs, h->exch, h->hp, h->K, h->peer_block};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -221,6 +225,78 @@ aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out) {
     if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
     ASLAM_CUDA(cudaSetDevice(h->device));
     aslam_status rc = large_ekf_phase2(h);
+    if (rc != ASLAM_OK) return rc;
+    return fetch_assoc(h, assoc_out);
+}
+
+static size_t peer_block_bytes(const aslam_large* h) {
+    return (size_t)4 * LARGE_QMAX * h->n * sizeof(double) + LARGE_MAX_PEERS * sizeof(unsigned long long);
+}
+
+aslam_status aslam_large_peer_export(aslam_large* h, void* ipc_handle64, void** block) {
+    if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the ABI carries the IPC handle as 64 opaque bytes");
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    if (!h->peer_block) {
+        ASLAM_CUDA(cudaMalloc((void**)&h->peer_block, peer_block_bytes(h)));
+        ASLAM_CUDA(cudaMemset(h->peer_block, 0, peer_block_bytes(h)));
+        ASLAM_CUDA(cudaDeviceSynchronize());
+    }
+    if (ipc_handle64) ASLAM_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(ipc_handle64), h->peer_block));
+    if (block) *block = h->peer_block;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_peer_attach(aslam_large* h, uint32_t world, uint32_t rank, const void* ipc_handles,
+                                     void* const* blocks) {
+    if (!h || h->kind != ASLAM_KIND_EKF || !h->peer_block || world == 0 || world > (uint32_t)LARGE_MAX_PEERS ||
+        rank >= world || (!ipc_handles && !blocks)) {
+        set_error("peer_attach: export first; 1 <= world <= 8; pass ipc_handles or blocks");
+        return ASLAM_ERR_ARG;
+    }
+    if (h->peer_world) {
+        set_error("peer_attach: already attached");
+        return ASLAM_ERR_ARG;
+    }
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    for (uint32_t p = 0; p < world; ++p) {
+        if (p == rank) {
+            h->peer_base[p] = h->peer_block;
+        } else if (blocks) {
+            h->peer_base[p] = static_cast<unsigned char*>(blocks[p]);
+            cudaPointerAttributes at{};
+            if (cudaPointerGetAttributes(&at, blocks[p]) == cudaSuccess && at.device != h->device) {
+                const cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                    set_error("peer_attach: no peer access between the two devices");
+                    return ASLAM_ERR_CUDA;
+                }
+                cudaGetLastError();
+            }
+        } else {
+            cudaIpcMemHandle_t hd;
+            memcpy(&hd, static_cast<const unsigned char*>(ipc_handles) + (size_t)p * 64, 64);
+            void* ptr = nullptr;
+            ASLAM_CUDA(cudaIpcOpenMemHandle(&ptr, hd, cudaIpcMemLazyEnablePeerAccess));
+            h->peer_base[p] = static_cast<unsigned char*>(ptr);
+            h->peer_ipc[p] = true;
+        }
+    }
+    h->peer_world = world;
+    h->peer_rank = rank;
+    h->peer_epoch = 0;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_step_fused(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                                    const float* range, const float* bearing, uint32_t m, int32_t* assoc_out) {
+    if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    aslam_status rc = stage_obs(h, range, bearing, m);
+    if (rc != ASLAM_OK) return rc;
+    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m, true);
+    if (rc != ASLAM_OK) return rc;
+    rc = large_ekf_phase2(h, true);
     if (rc != ASLAM_OK) return rc;
     return fetch_assoc(h, assoc_out);
 }

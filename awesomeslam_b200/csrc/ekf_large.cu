@@ -265,11 +265,14 @@ __global__ void large_gather_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t
 
 // Exchange buffer for q <= QT (QT = 20 or 40): same values as large_gather_kernel, arranged for latency (context in
 // shared memory, 2 q independent loads per thread, H_o's fixed row structure with static register indices).
-template <int QT>
+// PEER: instead of the local buffer (zeros where this rank owns nothing, summed by the caller), every value this
+// rank owns is stored into the exchange buffer of EVERY rank (peer memory over NVLink), then the CTA publishes its
+// stores (system-scope fence) and bumps this rank's arrival counter on every destination.
+template <int QT, bool PEER>
 __global__ void __launch_bounds__(256) large_gather_fast_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp,
                                                                const double* __restrict__ P,
                                                                const LargeCtx* __restrict__ ctx, uint32_t q_ub,
-                                                               double* __restrict__ E) {
+                                                               double* __restrict__ E, const PeerSet ps) {
     __shared__ double s_hval[QT][5];
     __shared__ int s_rows[QT];
     const int q = ctx->q;
@@ -282,7 +285,7 @@ __global__ void __launch_bounds__(256) large_gather_fast_kernel(uint32_t n, uint
     }
     __syncthreads();
     const uint32_t t = blockIdx.x * 256 + tid;
-    if (t >= n) return;
+    if (t < n) {
     const bool mine = t >= rb && t < re;
     double raw[QT], colv[QT];
 #pragma unroll
@@ -315,14 +318,38 @@ __global__ void __launch_bounds__(256) large_gather_fast_kernel(uint32_t n, uint
         pht[kb] = sb;
     }
     if ((QT - 3) % 2) pht[QT - 1] = 0.0;
+    if constexpr (!PEER) {
 #pragma unroll
-    for (int k = 0; k < QT; ++k) {
-        if (k < (int)q_ub) {
-            E[(size_t)k * n + t] = raw[k];
-            E[(size_t)(q_ub + k) * n + t] = pht[k];
+        for (int k = 0; k < QT; ++k) {
+            if (k < (int)q_ub) {
+                E[(size_t)k * n + t] = raw[k];
+                E[(size_t)(q_ub + k) * n + t] = pht[k];
+            }
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < QT; ++k) {
+            if (k < q) {
+                const uint32_t r = (uint32_t)s_rows[k];
+                const bool own_row = r >= rb && r < re;
+                for (int p = 0; p < ps.world; ++p) {
+                    if (own_row) ps.E[p][(size_t)k * n + t] = raw[k];
+                    if (mine) ps.E[p][(size_t)(q_ub + k) * n + t] = pht[k];
+                }
+            }
+        }
+    }
+    }
+    if constexpr (PEER) {
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence_system();
+            for (int p = 0; p < ps.world; ++p) atomicAdd_system(ps.flag[p] + ps.rank, 1ULL);
         }
     }
 }
+
 
 // ------------------------------------------------------------------------------------------
 // Gain. Every CTA rebuilds S = H_o P H_o' + R_o and inverts it in shared memory (Gauss-Jordan with
@@ -432,10 +459,34 @@ __global__ void __launch_bounds__(256) large_gain_kernel(uint32_t n, const Large
 // values of the exchange buffer with independent (unrolled) loads, then does all arithmetic from registers and shared
 // memory. H_o has the fixed structure pose rows = identity, then (range, bearing) pairs -- ekf.cpp:124-132 -- so
 // H_o P for landmark pair c needs only raw rows 0, 1, 2, 3+2c, 4+2c: static register indices.
-template <int QT>
-__global__ void __launch_bounds__(256) large_gain_fast_kernel(uint32_t n, const LargeCtx* __restrict__ ctx, uint32_t q_ub,
+// PEER: the exchange buffer is filled by the gather kernels of all ranks; wait (bounded) until every source's
+// arrival counter has reached this step's target, then read it past L1 (ld.cg: the lines came in over NVLink).
+template <bool PEER>
+__device__ __forceinline__ double ld_exch(const double* p) {
+    if constexpr (PEER)
+        return __ldcg(p);
+    else
+        return *p;
+}
+
+template <int QT, bool PEER>
+__global__ void __launch_bounds__(256) large_gain_fast_kernel(uint32_t n, LargeCtx* __restrict__ ctx, uint32_t q_ub,
                                                              const double* __restrict__ E, double* __restrict__ hp,
-                                                             double* __restrict__ K, double* __restrict__ X) {
+                                                             double* __restrict__ K, double* __restrict__ X,
+                                                             const unsigned long long* flags, unsigned long long target,
+                                                             int world) {
+    if constexpr (PEER) {
+        if ((int)threadIdx.x < world) {
+            unsigned long long v = 0;
+            for (int it = 0; it < 4000000; ++it) {
+                asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + threadIdx.x) : "memory");
+                if (v >= target) break;
+                __nanosleep(256);
+            }
+            if (v < target) atomicOr(&ctx->status, (uint32_t)ASLAM_ST_PEER_TIMEOUT);
+        }
+        __syncthreads();
+    }
     __shared__ double S[QT * QT];
     __shared__ double s_hval[QT][5];
     __shared__ int s_hk[QT][5], s_hcol[QT][5], s_hnnz[QT], piv[QT];
@@ -464,7 +515,7 @@ __global__ void __launch_bounds__(256) large_gain_fast_kernel(uint32_t n, const 
     __syncthreads();
     for (int idx = tid; idx < QT * QT; idx += 256) {
         const int k1 = idx / QT, k2 = idx % QT;
-        S[idx] = (k1 < q && k2 < q) ? E[(size_t)k1 * n + s_rows[k2]] : 0.0;  // Psub, staged in S
+        S[idx] = (k1 < q && k2 < q) ? ld_exch<PEER>(E + (size_t)k1 * n + s_rows[k2]) : 0.0;  // Psub, staged in S
     }
     __syncthreads();
     for (int idx = tid; idx < QT * QT; idx += 256) {
@@ -542,8 +593,8 @@ __global__ void __launch_bounds__(256) large_gain_fast_kernel(uint32_t n, const 
     double raw[QT], pht[QT];
 #pragma unroll
     for (int k = 0; k < QT; ++k) {
-        raw[k] = k < q ? E[(size_t)k * n + t] : 0.0;
-        pht[k] = k < q ? E[(size_t)(q_ub + k) * n + t] : 0.0;
+        raw[k] = k < q ? ld_exch<PEER>(E + (size_t)k * n + t) : 0.0;
+        pht[k] = k < q ? ld_exch<PEER>(E + (size_t)(q_ub + k) * n + t) : 0.0;
     }
     // H_o P column t
     double hpv[QT];
@@ -938,8 +989,21 @@ __global__ void __launch_bounds__(256) large_update_generic_kernel(uint32_t n, u
 // ---------------------------------------------------------------------------------- host side
 uint32_t large_ekf_qt(uint32_t q_ub) { return q_ub <= 20 ? 20u : (q_ub <= 40 ? 40u : 132u); }
 
+// Per-step view of the mapped peer blocks: the parity-selected exchange buffer and the counters of every rank.
+static PeerSet peer_set(const aslam_large* h, uint64_t epoch) {
+    PeerSet ps{};
+    ps.world = (int32_t)h->peer_world;
+    ps.rank = (int32_t)h->peer_rank;
+    const size_t ebytes = (size_t)2 * LARGE_QMAX * h->n * sizeof(double);
+    for (uint32_t p = 0; p < h->peer_world; ++p) {
+        ps.E[p] = reinterpret_cast<double*>(h->peer_base[p] + (epoch & 1) * ebytes);
+        ps.flag[p] = reinterpret_cast<unsigned long long*>(h->peer_base[p] + 2 * ebytes);
+    }
+    return ps;
+}
+
 aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
-                              uint32_t m) {
+                              uint32_t m, bool peer) {
     FrontArgs a;
     a.ox = x; a.oy = y; a.vx = vx; a.az = az; a.yaw = yaw; a.dt = dt;
     a.m = m;
@@ -952,12 +1016,26 @@ aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, dou
     large_front_kernel<<<1, 1024, 0, h->stream>>>(a, n, h->X, h->A, h->d_obs, h->ctx);
     large_predict_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A,
                                                     (double)h->cfg.ekf_kq);
-    if (a.q_ub <= 20)
-        large_gather_fast_kernel<20><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub,
-                                                                h->exch);
+    if (peer) {
+        // the step's epoch (1-based) picks the buffer parity; phase2 waits for epoch * nb arrivals per source
+        if (a.q_ub > 40 || !h->peer_world) {
+            set_error("fused large step: needs peer_attach and at most 18 observations per message");
+            return ASLAM_ERR_UNSUPPORTED;
+        }
+        h->peer_epoch += 1;
+        const PeerSet ps = peer_set(h, h->peer_epoch);
+        if (a.q_ub <= 20)
+            large_gather_fast_kernel<20, true><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P,
+                                                                          h->ctx, a.q_ub, nullptr, ps);
+        else
+            large_gather_fast_kernel<40, true><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P,
+                                                                          h->ctx, a.q_ub, nullptr, ps);
+    } else if (a.q_ub <= 20)
+        large_gather_fast_kernel<20, false><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx,
+                                                                       a.q_ub, h->exch, PeerSet{});
     else if (a.q_ub <= 40)
-        large_gather_fast_kernel<40><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub,
-                                                                h->exch);
+        large_gather_fast_kernel<40, false><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx,
+                                                                       a.q_ub, h->exch, PeerSet{});
     else
         large_gather_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub, h->exch);
     ASLAM_CUDA(cudaGetLastError());
@@ -966,7 +1044,7 @@ aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, dou
     return ASLAM_OK;
 }
 
-aslam_status large_ekf_phase2(aslam_large* h) {
+aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
     const uint32_t n = h->n, nb = (n + 255) / 256, q_ub = h->q_host;
     const uint32_t QT = large_ekf_qt(q_ub);
     const size_t smem = (size_t)q_ub * q_ub * sizeof(double);
@@ -975,10 +1053,23 @@ aslam_status large_ekf_phase2(aslam_large* h) {
         ASLAM_CUDA(cudaFuncSetAttribute(large_gain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set = smem;
     }
-    if (QT == 20)
-        large_gain_fast_kernel<20><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X);
+    if (peer) {
+        const PeerSet ps = peer_set(h, h->peer_epoch);
+        const double* E = ps.E[h->peer_rank];
+        const unsigned long long* flags = ps.flag[h->peer_rank];
+        const unsigned long long target = (unsigned long long)h->peer_epoch * nb;  // nb gather CTAs per rank and step
+        if (QT == 20)
+            large_gain_fast_kernel<20, true><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, E, h->hp, h->K, h->X, flags, target,
+                                                                        (int)h->peer_world);
+        else
+            large_gain_fast_kernel<40, true><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, E, h->hp, h->K, h->X, flags, target,
+                                                                        (int)h->peer_world);
+    } else if (QT == 20)
+        large_gain_fast_kernel<20, false><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X, nullptr, 0,
+                                                                     0);
     else if (QT == 40)
-        large_gain_fast_kernel<40><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X);
+        large_gain_fast_kernel<40, false><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X, nullptr, 0,
+                                                                     0);
     else
         large_gain_kernel<<<nb, 256, smem, h->stream>>>(n, h->ctx, q_ub, h->exch, QT, h->hp, h->K, h->X);
     const uint32_t nrows = h->row_end - h->row_begin;

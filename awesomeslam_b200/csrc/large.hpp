@@ -24,6 +24,16 @@ struct LargeCtx {
     uint32_t status;
 };
 
+// Fused exchange of the row-sharded large-map EKF: every rank maps the exchange block of every
+// other rank (CUDA IPC over NVLink, or plain pointers inside one process) and the gather kernel stores each
+// value it owns straight into all of them; one arrival counter per (destination, source) pair orders the step.
+constexpr int LARGE_MAX_PEERS = 8;
+struct PeerSet {
+    double* E[LARGE_MAX_PEERS];                 // this step's (parity-selected) exchange buffer of rank p
+    unsigned long long* flag[LARGE_MAX_PEERS];  // rank p's arrival counters, indexed by source rank
+    int32_t world, rank;
+};
+
 }  // namespace aslam
 
 struct aslam_large {
@@ -47,6 +57,12 @@ struct aslam_large {
     uint64_t launches = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the streaming update kernel of the last step
     bool timed = false;
+    // fused peer exchange: block = [E parity 0][E parity 1][LARGE_MAX_PEERS arrival counters]
+    unsigned char* peer_block = nullptr;        // own block (cudaMalloc)
+    unsigned char* peer_base[aslam::LARGE_MAX_PEERS] = {};  // every rank's block as mapped here
+    bool peer_ipc[aslam::LARGE_MAX_PEERS] = {};  // mapped with cudaIpcOpenMemHandle (to be closed)
+    uint32_t peer_world = 0, peer_rank = 0;
+    uint64_t peer_epoch = 0;                    // fused steps taken so far (all ranks step in lockstep)
     // UKF large-map state lives in ukf_large.cu's own struct, reached through `ukf`
     void* ukf = nullptr;
 };

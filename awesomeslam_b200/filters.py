@@ -352,6 +352,36 @@ class LargeFilter:
         capi.check(self._lib.aslam_large_step_phase2(self._h, capi.ptr(assoc)))
         return None if assoc is None else assoc[:self._m]
 
+    # sharded EKF, fused exchange: peer stores over NVLink + arrival counters, no collective call
+    def peer_export(self):
+        """(64-byte CUDA IPC handle, raw device pointer) of this handle's exchange block."""
+        hd = (C.c_ubyte * 64)()
+        blk = C.c_void_p()
+        capi.check(self._lib.aslam_large_peer_export(self._h, C.cast(hd, C.c_void_p), C.byref(blk)))
+        return bytes(hd), int(blk.value)
+
+    def peer_attach(self, world, rank, ipc_handles=None, blocks=None):
+        """ipc_handles: list of `world` 64-byte handles (ranks in other processes) or blocks: list of `world`
+        raw device pointers (ranks in this process). All ranks attach, then barrier, before the first step."""
+        hbuf, barr = None, None
+        if ipc_handles is not None:
+            assert len(ipc_handles) == world and all(len(b) == 64 for b in ipc_handles)
+            hbuf = C.create_string_buffer(b"".join(ipc_handles), 64 * world)
+        if blocks is not None:
+            assert len(blocks) == world
+            barr = (C.c_void_p * world)(*blocks)
+        capi.check(self._lib.aslam_large_peer_attach(self._h, world, rank, C.cast(hbuf, C.c_void_p) if hbuf else None,
+                                                     barr))
+
+    def step_fused(self, x, y, yaw, vx, az, dt, rng, brg, want_assoc=True):
+        rng = capi.as_np(rng, np.float32)
+        brg = capi.as_np(brg, np.float32)
+        self._m = rng.size
+        assoc = np.zeros(max(self._m, 1), np.int32) if want_assoc else None
+        capi.check(self._lib.aslam_large_step_fused(self._h, x, y, np.float32(yaw), vx, az, np.float32(dt),
+                                                    capi.ptr(rng), capi.ptr(brg), rng.size, capi.ptr(assoc)))
+        return None if assoc is None else assoc[:self._m]
+
     def last_kernel_ms(self):
         ms = C.c_float()
         capi.check(self._lib.aslam_large_last_kernel_ms(self._h, C.byref(ms)))

@@ -293,43 +293,74 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
     rng, brg, idx = A.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8)
     stream = torch.cuda.ExternalStream(f.stream, device=dev)
     exch = None
+    ODOM = (0.0, 0.0, 0.0, 0.05, 0.1, 1.0)
 
-    def step():
+    def step_single():
+        f.step(*ODOM, rng, brg, want_assoc=False)
+
+    def step_nccl():
         nonlocal exch
-        if world == 1:
-            f.step(0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
-        else:
-            f.step_phase1(0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg)
-            if exch is None:
-                p, c = f.exchange_buffer()
-                exch = torch.as_tensor(_DevArray(p, c), device=dev)
-            dist.all_reduce(exch)
-            f.step_phase2(want_assoc=False)
+        f.step_phase1(*ODOM, rng, brg)
+        if exch is None:
+            p, c = f.exchange_buffer()
+            exch = torch.as_tensor(_DevArray(p, c), device=dev)
+        dist.all_reduce(exch)
+        f.step_phase2(want_assoc=False)
 
-    with torch.cuda.stream(stream):
-        for _ in range(max(W, 3)):
-            step()
-        f.sync()
+    def step_fused():
+        f.step_fused(*ODOM, rng, brg, want_assoc=False)
+
+    def timed(step):
+        with torch.cuda.stream(stream):
+            for _ in range(max(W, 3)):
+                step()
+            f.sync()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            l0 = f.launch_count
+            e0.record()
+            for _ in range(K):
+                step()
+            e1.record()
+            f.sync()
+            torch.cuda.synchronize(dev)
+            ms = e0.elapsed_time(e1) / K
+            launches = f.launch_count - l0
+            kms = []
+            for _ in range(K):
+                step()
+                kms.append(f.last_kernel_ms())
+            f.sync()
         if world > 1:
             dist.barrier()
-        torch.cuda.synchronize(dev)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = f.launch_count
-        e0.record()
-        for _ in range(K):
-            step()
-        e1.record()
-        f.sync()
-        torch.cuda.synchronize(dev)
-        ms = e0.elapsed_time(e1) / K
-        launches = f.launch_count - l0
-        kms = []
-        for _ in range(K):
-            step()
-            kms.append(f.last_kernel_ms())
+        return ms, launches, kms
+
+    exchange, nccl_ms = "none (one GPU)", None
+    if world == 1:
+        ms, launches, kms = timed(step_single)
+    else:
+        # comparison point: phase1 -> NCCL all-reduce of the exchange buffer -> phase2
+        nccl_ms, launches, kms = timed(step_nccl)
+        ms, exchange = nccl_ms, "NCCL all-reduce of the [2q][n] exchange buffer"
+        try:  # the fused exchange: CUDA IPC peer mappings, stores + arrival counters inside the kernels
+            hd, _ = f.peer_export()
+            handles = [None] * world
+            dist.all_gather_object(handles, hd)
+            f.peer_attach(world, rank, ipc_handles=handles)
+            dist.barrier()
+            ms, launches, kms = timed(step_fused)
+            assert f.status()[0] == 0, "fused exchange timed out"
+            exchange = "fused: peer stores over NVLink + arrival counters in the gather/gain kernels (no collective call)"
+        except Exception as e:  # noqa: BLE001  (reported, and the NCCL numbers stand)
+            sys.stderr.write("fused exchange unavailable: %r\n" % (e,))
     t = torch.tensor([ms, float(np.mean(kms))], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tn = torch.tensor([nccl_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tn, op=dist.ReduceOp.MAX)
+        nccl_ms = float(tn.item())
     ms, kernel_ms = float(t[0].item()), float(t[1].item())
     X, _ = f.get_state(want_P=False)
     assert np.all(np.isfinite(X))
@@ -339,7 +370,8 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
     achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
     return {
         "workload": "cfg4: large-map EKF n=8195 (4096 landmarks), q=19 rows of H per step, FP64 P%s"
-                    % ("" if world == 1 else ", rows sharded over %d GPUs + 1 NCCL all-reduce/step" % world),
+                    % ("" if world == 1 else ", rows sharded over %d GPUs, one exchange per step" % world),
+        "exchange": exchange, "ms_per_step_nccl_exchange": nccl_ms,
         "steps_per_s": 1e3 / ms, "ms_per_step": ms, "launches_per_step": launches / K,
         "roofline": {"bound": "hbm", "kernel": "large_update_ws_kernel<2,20,8,5>", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,

@@ -52,7 +52,8 @@ enum {
     ASLAM_ST_LLT_FAILED = 1u << 1,    /* UKF: Paug not positive definite this step (ukf.cpp:280) */
     ASLAM_ST_NONFINITE = 1u << 2,     /* X or P holds a NaN/Inf */
     ASLAM_ST_WAIT_OVERFLOW = 1u << 3, /* wait-list exceeded ASLAM_MAX_WAIT (reference: unbounded) */
-    ASLAM_ST_OBS_OVERFLOW = 1u << 4   /* more than ASLAM_MAX_OBS observations in one message */
+    ASLAM_ST_OBS_OVERFLOW = 1u << 4,  /* more than ASLAM_MAX_OBS observations in one message */
+    ASLAM_ST_PEER_TIMEOUT = 1u << 5   /* fused exchange: a peer's rows did not arrive within the spin bound */
 };
 
 #define ASLAM_MAX_WAIT 256u /* capacity of the per-filter new-landmark wait-list */
@@ -210,6 +211,21 @@ aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float y
                                      uint32_t* q_out);
 aslam_status aslam_large_exchange_buffer(aslam_large* h, double** d_buf, size_t* count);
 aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out);
+/* Fused form of the same exchange (no NCCL call, no host round trip between the phases): every rank's
+ * gather kernel stores the values it owns straight into the exchange block of EVERY rank over NVLink
+ * peer memory and bumps an arrival counter there; the gain kernel of each rank spins (bounded;
+ * ASLAM_ST_PEER_TIMEOUT on expiry) until all sources have arrived. Set-up, once per handle:
+ *   peer_export: allocates this handle's exchange block, returns its CUDA IPC handle (64 bytes) and,
+ *                for ranks living in the same process, the raw device pointer (either may be NULL);
+ *   peer_attach: `ipc_handles` = world x 64 bytes gathered from all ranks (other processes), or
+ *                `blocks` = world device pointers (same process); entry `rank` is this handle itself.
+ * All ranks must have attached before the first fused step (barrier), step in lockstep, and must not
+ * destroy a handle while a peer may still write to it. Supports m <= 18 observations per message. */
+aslam_status aslam_large_peer_export(aslam_large* h, void* ipc_handle64, void** block);
+aslam_status aslam_large_peer_attach(aslam_large* h, uint32_t world, uint32_t rank, const void* ipc_handles,
+                                     void* const* blocks);
+aslam_status aslam_large_step_fused(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                                    const float* range, const float* bearing, uint32_t m, int32_t* assoc_out);
 /* Kernels this handle has launched so far. */
 uint64_t aslam_large_launch_count(aslam_large* h);
 /* Device time (CUDA events on the handle's stream) of the dominant kernel of the LAST step: the

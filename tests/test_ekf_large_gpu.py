@@ -133,6 +133,71 @@ def test_large_ekf_row_sharded_two_handles_one_gpu(aslam, orc):
         f.close()
 
 
+@pytest.mark.parametrize("cuts", [(70,), (41, 97)])
+def test_large_ekf_fused_peer_exchange_one_gpu(aslam, cuts):
+    """The fused exchange (peer stores + arrival counters inside the gather / gain kernels, no collective call):
+    2 and 3 row shards as handles of ONE process on one GPU, attached through raw block pointers. Each value has
+    one owner that stores it into every shard's buffer, so the result is BIT-IDENTICAL to the unsharded handle,
+    for several consecutive steps (both buffer parities, growing counters)."""
+    tx, ty, X0, G, d = aslam.large_map_state(9, seed=6)
+    P0 = aslam.dense_P(G, d)
+    n = X0.size
+    edges = (0,) + tuple(cuts) + (n,)
+    full = aslam.LargeFilter("ekf", n)
+    shards = [aslam.LargeFilter("ekf", n, row_begin=edges[i], row_end=edges[i + 1]) for i in range(len(edges) - 1)]
+    for f in [full] + shards:
+        f.load_state_colmajor(X0, P0)
+    blocks = [f.peer_export()[1] for f in shards]
+    for r, f in enumerate(shards):
+        f.peer_attach(len(shards), r, blocks=blocks)
+    for t, (px, py, pth, v, w) in enumerate(_trajectory(5)):
+        rng, brg, idx = aslam.large_observations(tx, ty, (px, py, pth), m=8, seed=50 + t)
+        a_full = full.step(px, py, np.float32(pth), v, w, 1.0, rng, brg)
+        # enqueue every shard before waiting on any of them: a shard's gain kernel spins until all have arrived
+        for f in shards:
+            f.step_fused(px, py, np.float32(pth), v, w, 1.0, rng, brg, want_assoc=False)
+        X, P = full.get_state()
+        for i, f in enumerate(shards):
+            Xs, Ps = f.get_state()
+            assert f.status()[0] == 0
+            assert np.array_equal(X, Xs), (t, i)
+            assert np.array_equal(P[edges[i]:edges[i + 1]], Ps), (t, i)
+    for f in [full] + shards:
+        f.close()
+
+
+def test_large_ekf_fused_peer_exchange_two_gpus(aslam):
+    """Same on two physical GPUs of one box (peer access over NVLink, handles of one process): rows [0,k) on
+    cuda:0, [k,n) on cuda:1, bit-identical to the unsharded handle. Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    tx, ty, X0, G, d = aslam.large_map_state(16, seed=6)
+    P0 = aslam.dense_P(G, d)
+    n = X0.size
+    k = n // 2
+    full = aslam.LargeFilter("ekf", n, 0)
+    shards = [aslam.LargeFilter("ekf", n, 0, row_begin=0, row_end=k), aslam.LargeFilter("ekf", n, 1, row_begin=k, row_end=n)]
+    edges = (0, k, n)
+    for f in [full] + shards:
+        f.load_state_colmajor(X0, P0)
+    blocks = [f.peer_export()[1] for f in shards]
+    for r, f in enumerate(shards):
+        f.peer_attach(2, r, blocks=blocks)
+    for t, (px, py, pth, v, w) in enumerate(_trajectory(6)):
+        rng, brg, idx = aslam.large_observations(tx, ty, (px, py, pth), m=8, seed=50 + t)
+        full.step(px, py, np.float32(pth), v, w, 1.0, rng, brg)
+        for f in shards:
+            f.step_fused(px, py, np.float32(pth), v, w, 1.0, rng, brg, want_assoc=False)
+        X, P = full.get_state()
+        for i, f in enumerate(shards):
+            Xs, Ps = f.get_state()
+            assert f.status()[0] == 0
+            assert np.array_equal(X, Xs) and np.array_equal(P[edges[i]:edges[i + 1]], Ps), (t, i)
+    for f in [full] + shards:
+        f.close()
+
+
 def test_cfg4_full_size_one_step(aslam, orc):
     """config 4 at BASELINE size: 4096 landmarks, n = 8195, 8 observed (q = 19), two steps against
     the oracle (O(q n^2) on the host cores), plus the symmetry property of the updated P."""
