@@ -22,8 +22,9 @@
 // SURVEY.md section 6.2.) One __syncthreads per block; V and dx are double-buffered.
 #include <cuda_runtime.h>
 
-#include "frontend.cuh"
-#include "internal.hpp"
+#include <cstdlib>
+
+#include "ekf_batched_common.cuh"
 
 namespace aslam {
 
@@ -38,25 +39,6 @@ struct Geo {
     static_assert(NP % CPT == 0, "NP must be a multiple of CPT");
 };
 
-// One message of one filter, staged in shared memory by cp.async one step ahead of its use.
-struct __align__(16) MsgBuf {
-    double ox, oy, vx, az;
-    float yaw, dt;
-    uint32_t base, cnt;
-    float rng[ASLAM_MAX_OBS];
-    float brg[ASLAM_MAX_OBS];
-};
-
-__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
-                 : "memory");
-}
-__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
-                 : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
 template <int NP>
 struct __align__(16) EkfSlot {
     double V[2][NP * 4];  // block rows of H_g P: pitch 4 for the pose block, 2 for landmark blocks
@@ -70,45 +52,6 @@ struct __align__(16) EkfSlot {
     MsgBuf msg[2];        // this step's message and the next one (in flight)
     FrontSlot fr;
 };
-
-struct EkfParams {
-    BatchState st;
-    BatchInput in;
-    FrontParams fp;
-    double kq, kr_pose, kr_lm, kp_lm;
-};
-
-// Start the asynchronous copy of message `step` of filter f into m: the six odometry fields by six
-// threads, the observation list spread over the filter's threads. No register is held across the wait.
-template <int TPF>
-__device__ __forceinline__ void prefetch_message(MsgBuf& m, const BatchInput& in, uint32_t batch, uint32_t f,
-                                                 uint32_t step, int ct) {
-    const size_t si = (size_t)step * batch + f;
-    uint32_t base, cnt;
-    if (in.offsets) {
-        base = in.offsets[f];
-        cnt = in.offsets[f + 1] - base;
-    } else {
-        base = (uint32_t)(si * in.obs_per_filter);
-        cnt = in.obs_per_filter;
-    }
-    if (ct == 6) {
-        m.base = base;
-        m.cnt = cnt;
-    }
-    if (cnt > ASLAM_MAX_OBS) cnt = ASLAM_MAX_OBS;
-    if (ct < 4) {
-        const double* src = ct == 0 ? in.ox : ct == 1 ? in.oy : ct == 2 ? in.vx : in.az;
-        cp_async8(&m.ox + ct, src + si);
-    } else if (ct < 6) {
-        const float* src = ct == 4 ? in.yaw : in.dt;
-        cp_async4(&m.yaw + (ct - 4), src + si);
-    }
-    for (uint32_t o = ct; o < cnt; o += TPF) {
-        cp_async4(&m.rng[o], in.range + base + o);
-        cp_async4(&m.brg[o], in.bearing + base + o);
-    }
-}
 
 template <int NP, int CPT>
 __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(const EkfParams kp) {
@@ -486,7 +429,12 @@ aslam_status launch_ekf_batched(const aslam_config& cfg, const BatchState& st, c
     kp.kp_lm = (double)cfg.ukf_kp_landmark_pose;  // ekf.cpp:277
     switch (st.ld) {
         case 30: return launch_t<30, 2>(kp, stream);
-        case 36: return launch_t<36, 2>(kp, stream);
+        case 36: {
+            // cfg3 size: ASLAM_EKF_KERNEL=mma selects the warp-per-filter DMMA kernel (ekf_batched_mma.cu)
+            const char* variant = std::getenv("ASLAM_EKF_KERNEL");  // read per launch: tests switch it
+            if (variant && variant[0] == 'm') return launch_ekf_batched_mma36(kp, stream);
+            return launch_t<36, 2>(kp, stream);
+        }
         case 48: return launch_t<48, 2>(kp, stream);
         case 64: return launch_t<64, 1>(kp, stream);
         default: set_error("ekf_batched: unsupported padded dim"); return ASLAM_ERR_UNSUPPORTED;

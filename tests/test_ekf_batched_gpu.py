@@ -131,6 +131,32 @@ def test_cfg3_batched_ekf_subset(aslam, orc):
     f.close()
 
 
+@pytest.mark.parametrize("nlm", [16, 8, 5, 1])
+def test_cfg3_warp_per_filter_dmma_kernel(aslam, orc, nlm, monkeypatch):
+    """The cfg3-size kernel (padded dimension 36: one warp per filter, covariance update on the FP64 tensor pipe,
+    ekf_batched_mma.cu) from reset -- wait-list, promotion and growth included -- against the oracle: 16 landmarks
+    (N = 35, every tile in use), 8 (N = 19), 5 (N = 13: the last landmark pair has one member) and 1 (N = 5)."""
+    monkeypatch.setenv("ASLAM_EKF_KERNEL", "mma")
+    lmx, lmy = aslam.map_cfg3()
+    lmx, lmy = lmx[:nlm], lmy[:nlm]
+    B, T, L = 128, 120, nlm
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=0x5EED0000 + nlm)
+    f = aslam.BatchedFilter("ekf", B, 0, max_state_dim=36)
+    assert f.ld == 36
+    f.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+    s = f.get_state()
+    cfg = orc.default_config(max_state_dim=36)
+    sec, X, P, N = orc.run_batch("ekf", cfg, B, T, L, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range,
+                                 rp.bearing, 0, f.ld)
+    assert np.array_equal(s["N"], N) and np.all(N == 3 + 2 * nlm)
+    assert not np.any(s["status"])
+    ex = [relerr(s["X"][b], X[b]) for b in range(B)]
+    ep = [relerr(s["P"][b], P[b]) for b in range(B)]
+    print("dmma kernel, %d landmarks: worst relerr X %.3e P %.3e" % (nlm, max(ex), max(ep)))
+    assert max(ex) <= TOL_F64 and max(ep) <= TOL_F64
+    f.close()
+
+
 def test_batched_split_launch_equals_one_launch(aslam):
     """Replaying 40 steps as 1 launch or as 4 x 10 gives bit-identical state (idempotent staging)."""
     lmx, lmy = aslam.map_cfg3()
