@@ -21,8 +21,12 @@ constexpr int BS = CHOL_BS;
 // its registers. Writes L over the lower triangle of A and inv(L) (pitch 64, zero above the diagonal and beyond bs) to
 // `inv`. k0: global index of the block's first row (for the failure report: Eigen's LLT stops at the first x <= 0).
 __global__ void __launch_bounds__(256) chol_panel_kernel(double* A, size_t ld, int bs, double* inv, int* fail, int k0) {
-    __shared__ double col[2][BS];
-    __shared__ double xrow[2][BS];
+    // One barrier per FOUR columns: the owners publish block column kb of A (64 x 4) and block row kb of X (4 x 64);
+    // every working thread then factors the 4 x 4 pivot block itself (D = Ld Ld', M = Ld^-1), forms its own rows of
+    // the panel L_i = A_i Ld^-T, the panel rows of its columns L_j, and the eliminated pivot rows of X (M X_kb), and
+    // applies both rank-4 updates to its registers. 16 barriers and 16 short rsqrt chains instead of 64 of each.
+    __shared__ __align__(16) double cb[2][BS][4];
+    __shared__ __align__(16) double xr[2][4][BS];
     const int tid = threadIdx.x, ti = tid >> 4, tj = tid & 15;
     double a[4][4], x[4][4];
 #pragma unroll
@@ -34,52 +38,152 @@ __global__ void __launch_bounds__(256) chol_panel_kernel(double* A, size_t ld, i
             x[r][c] = i == j ? 1.0 : 0.0;
         }
     for (int kb = 0; kb < BS / 4; ++kb) {
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-            const int k = 4 * kb + kk, buf = kk & 1;
-            if (tj == kb) {
-#pragma unroll
-                for (int r = 0; r < 4; ++r) col[buf][4 * ti + r] = a[r][kk];
-            }
-            if (ti == kb) {
-#pragma unroll
-                for (int c = 0; c < 4; ++c) xrow[buf][4 * tj + c] = x[kk][c];
-            }
-            __syncthreads();
-            double akk = col[buf][k];
-            if (!(akk > 0.0)) {
-                if (tid == 0 && k < bs) atomicCAS(fail, -1, k0 + k);
-                akk = akk == 0.0 ? 1.0 : fabs(akk);
-            }
-            const double rd = rsqrt(akk), d = akk * rd;  // a few ulp from sqrt/divide: far inside the FP64 tolerance
-            double li[4], lj[4], xk[4];
+        const int buf = kb & 1;
+        if (tj == kb) {
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-                li[r] = col[buf][4 * ti + r] * rd;
-                lj[r] = col[buf][4 * tj + r] * rd;
-                xk[r] = xrow[buf][4 * tj + r] * rd;
+                *reinterpret_cast<double2*>(&cb[buf][4 * ti + r][0]) = make_double2(a[r][0], a[r][1]);
+                *reinterpret_cast<double2*>(&cb[buf][4 * ti + r][2]) = make_double2(a[r][2], a[r][3]);
             }
+        }
+        if (ti == kb) {
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-                const int i = 4 * ti + r;
+                *reinterpret_cast<double2*>(&xr[buf][r][4 * tj]) = make_double2(x[r][0], x[r][1]);
+                *reinterpret_cast<double2*>(&xr[buf][r][4 * tj + 2]) = make_double2(x[r][2], x[r][3]);
+            }
+        }
+        __syncthreads();
+        if (!(tj <= ti && ti >= kb)) continue;  // upper block triangle and finished rows have nothing to do
+        // ---- pivot block: lower triangle of D, Cholesky with Eigen's failure rule reported per column
+        double d[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const double2 v01 = *reinterpret_cast<const double2*>(&cb[buf][4 * kb + r][0]);
+            const double2 v23 = *reinterpret_cast<const double2*>(&cb[buf][4 * kb + r][2]);
+            d[r][0] = v01.x;
+            d[r][1] = v01.y;
+            d[r][2] = v23.x;
+            d[r][3] = v23.y;
+        }
+        double m[4][4];  // M = Ld^-1 (lower); iv[k] = 1 / Ld[k][k]
+        double l[4][4];
+        double iv[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            double piv = d[k][k];
+#pragma unroll
+            for (int q = 0; q < k; ++q) piv = fma(-l[k][q], l[k][q], piv);
+            if (!(piv > 0.0)) {
+                if (ti == kb && tj == kb && 4 * kb + k < bs) atomicCAS(fail, -1, k0 + 4 * kb + k);
+                piv = piv == 0.0 ? 1.0 : fabs(piv);
+            }
+            iv[k] = rsqrt(piv);  // a few ulp from sqrt/divide: far inside the FP64 tolerance
+            l[k][k] = piv * iv[k];
+#pragma unroll
+            for (int i = k + 1; i < 4; ++i) {
+                double v = d[i][k];
+#pragma unroll
+                for (int q = 0; q < k; ++q) v = fma(-l[i][q], l[k][q], v);
+                l[i][k] = v * iv[k];
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            m[i][i] = iv[i];
+#pragma unroll
+            for (int j = 0; j < i; ++j) {
+                double v = 0.0;
+#pragma unroll
+                for (int q = j; q < i; ++q) v = fma(l[i][q], m[q][j], v);
+                m[i][j] = -v * iv[i];
+            }
+        }
+        // ---- eliminated pivot rows of X for this thread's columns: Xk = M X_kb (needed by tj <= kb only)
+        double xk[4][4];
+        if (tj <= kb) {
+            double xo[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const double2 v01 = *reinterpret_cast<const double2*>(&xr[buf][r][4 * tj]);
+                const double2 v23 = *reinterpret_cast<const double2*>(&xr[buf][r][4 * tj + 2]);
+                xo[r][0] = v01.x;
+                xo[r][1] = v01.y;
+                xo[r][2] = v23.x;
+                xo[r][3] = v23.y;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    const int j = 4 * tj + c;
-                    if (i > k && j > k) a[r][c] = fma(-li[r], lj[c], a[r][c]);
-                    if (i > k) x[r][c] = fma(-li[r], xk[c], x[r][c]);
+                    double v = m[k][0] * xo[0][c];
+#pragma unroll
+                    for (int q = 1; q <= k; ++q) v = fma(m[k][q], xo[q][c], v);
+                    xk[k][c] = v;
+                }
+        }
+        if (ti == kb) {
+            // pivot block row: X rows replaced; the diagonal block of A becomes Ld
+            if (tj == kb) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int c = 0; c <= r; ++c) a[r][c] = l[r][c];
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) x[r][c] = xk[r][c];
+            continue;
+        }
+        // ---- rows below the pivot block: L_i = A_i Ld^-T
+        double li[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const double2 v01 = *reinterpret_cast<const double2*>(&cb[buf][4 * ti + r][0]);
+            const double2 v23 = *reinterpret_cast<const double2*>(&cb[buf][4 * ti + r][2]);
+            const double ar[4] = {v01.x, v01.y, v23.x, v23.y};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                double v = ar[0] * m[k][0];
+#pragma unroll
+                for (int q = 1; q <= k; ++q) v = fma(ar[q], m[k][q], v);
+                li[r][k] = v;
+            }
+        }
+        if (tj > kb) {  // trailing block of A: needs the panel rows of this thread's columns as well
+            double lj[4][4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const double2 v01 = *reinterpret_cast<const double2*>(&cb[buf][4 * tj + c][0]);
+                const double2 v23 = *reinterpret_cast<const double2*>(&cb[buf][4 * tj + c][2]);
+                const double ar[4] = {v01.x, v01.y, v23.x, v23.y};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    double v = ar[0] * m[k][0];
+#pragma unroll
+                    for (int q = 1; q <= k; ++q) v = fma(ar[q], m[k][q], v);
+                    lj[c][k] = v;
                 }
             }
-            if (tj == kb) {  // column k of L
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const int i = 4 * ti + r;
-                    if (i > k) a[r][kk] = li[r];
-                    if (i == k) a[r][kk] = d;
-                }
-            }
-            if (ti == kb) {  // row k of inv(L)
+            for (int r = 0; r < 4; ++r)
 #pragma unroll
-                for (int c = 0; c < 4; ++c) x[kk][c] = xk[c];
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) a[r][c] = fma(-li[r][k], lj[c][k], a[r][c]);
+        } else {  // tj <= kb: X, and for tj == kb the panel block itself
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) x[r][c] = fma(-li[r][k], xk[k][c], x[r][c]);
+            if (tj == kb) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) a[r][c] = li[r][c];
             }
         }
     }
