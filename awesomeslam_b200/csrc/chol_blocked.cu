@@ -247,28 +247,50 @@ __global__ void symmetrize_kernel(double* A, size_t ld, int n) {
 
 }  // namespace
 
+// Right-looking with one block column of lookahead: after L21 of panel k, the NEXT block column of the trailing matrix
+// is updated first (a narrow GEMM), the one-CTA panel kernel of block k+1 then runs on a side stream while the rest
+// of the trailing update keeps the other SMs busy on the caller's stream; the two meet again before L21 of k+1.
 aslam_status cholesky_lower(cudaStream_t st, double* A, size_t ld, int n, double* inv_blocks, int* d_fail,
                             uint64_t* launches) {
+    static thread_local cudaStream_t side = nullptr;
+    static thread_local cudaEvent_t ev_col = nullptr, ev_panel = nullptr;
+    if (!side) {
+        ASLAM_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+        ASLAM_CUDA(cudaEventCreateWithFlags(&ev_col, cudaEventDisableTiming));
+        ASLAM_CUDA(cudaEventCreateWithFlags(&ev_panel, cudaEventDisableTiming));
+    }
+    chol_panel_kernel<<<1, 256, 0, st>>>(A, ld, n < BS ? n : BS, inv_blocks, d_fail, 0);
+    ASLAM_CUDA(cudaGetLastError());
+    if (launches) ++*launches;
     for (int k0 = 0; k0 < n; k0 += BS) {
         const int bs = n - k0 < BS ? n - k0 : BS;
-        double* A11 = A + (size_t)k0 * ld + k0;
-        double* inv = inv_blocks + (size_t)(k0 / BS) * BS * BS;
-        chol_panel_kernel<<<1, 256, 0, st>>>(A11, ld, bs, inv, d_fail, k0);
-        ASLAM_CUDA(cudaGetLastError());
-        if (launches) ++*launches;
         const int rs = n - k0 - bs;
         if (rs <= 0) break;
+        double* inv = inv_blocks + (size_t)(k0 / BS) * BS * BS;
         double* A21 = A + (size_t)(k0 + bs) * ld + k0;
         double* A22 = A + (size_t)(k0 + bs) * ld + (k0 + bs);
         Epilogue e;  // L21 = A21 inv(L11)'  (in place: one CTA owns all 64 columns of its row block, K = 64 <= 4 slabs)
         aslam_status rc = dgemm_nt(st, rs, bs, bs, A21, ld, inv, BS, A21, ld, e, launches);
         if (rc != ASLAM_OK) return rc;
+        const int nb = rs < BS ? rs : BS;  // width of the next block column
         Epilogue t;  // A22 -= L21 L21'
         t.alpha = -1.0;
         t.beta = 1.0;
-        t.lower_only = true;
-        rc = dgemm_nt(st, rs, rs, bs, A21, ld, A21, ld, A22, ld, t, launches);
+        rc = dgemm_nt(st, rs, nb, bs, A21, ld, A21, ld, A22, ld, t, launches);  // next block column first
         if (rc != ASLAM_OK) return rc;
+        ASLAM_CUDA(cudaEventRecord(ev_col, st));
+        ASLAM_CUDA(cudaStreamWaitEvent(side, ev_col, 0));
+        chol_panel_kernel<<<1, 256, 0, side>>>(A22, ld, nb, inv + (size_t)BS * BS, d_fail, k0 + bs);
+        ASLAM_CUDA(cudaGetLastError());
+        if (launches) ++*launches;
+        ASLAM_CUDA(cudaEventRecord(ev_panel, side));
+        if (rs > nb) {  // the rest of the trailing matrix, lower tiles only, concurrently with the panel
+            t.lower_only = true;
+            double* L2 = A21 + (size_t)nb * ld;
+            rc = dgemm_nt(st, rs - nb, rs - nb, bs, L2, ld, L2, ld, A22 + (size_t)nb * ld + nb, ld, t, launches);
+            if (rc != ASLAM_OK) return rc;
+        }
+        ASLAM_CUDA(cudaStreamWaitEvent(st, ev_panel, 0));
     }
     return ASLAM_OK;
 }
