@@ -107,6 +107,14 @@ SIGNATURES = {
     "aslam_large_step_phase1": (_i32, [_vp, _f64, _f64, _f32, _f64, _f64, _f32, _vp, _vp, _u32, C.POINTER(_u32)]),
     "aslam_large_exchange_buffer": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "aslam_large_step_phase2": (_i32, [_vp, _vp]),
+    "aslam_laser_config_default": (None, [_vp]),
+    "aslam_laser_create": (_i32, [_vp, _u32, _i32, C.POINTER(_vp)]),
+    "aslam_laser_destroy": (_i32, [_vp]),
+    "aslam_laser_extract": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp]),
+    "aslam_laser_extract_device": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp]),
+    "aslam_laser_sync": (_i32, [_vp]),
+    "aslam_laser_stream": (_vp, [_vp]),
+    "aslam_laser_launch_count": (C.c_uint64, [_vp]),
     "aslam_large_peer_export": (_i32, [_vp, _vp, C.POINTER(_vp)]),
     "aslam_large_peer_attach": (_i32, [_vp, _u32, _u32, _vp, C.POINTER(_vp)]),
     "aslam_large_step_fused": (_i32, [_vp, _f64, _f64, _f32, _f64, _f64, _f32, _vp, _vp, _u32, _vp]),

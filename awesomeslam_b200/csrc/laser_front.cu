@@ -1,0 +1,448 @@
+// Laser front end on the GPU: the reference's sensor_landmark node
+// (awesome_slam/src/sensor_landmark/sensor_landmark.cpp:59-298) for a batch of LaserScans -- bearing2pose, gap
+// clustering at MIN_DIST_THRESH, the inscribed-angle circle test (Xavier et al. 2005, :147-186), the Chernov
+// hyper-fit (:192-298) and Circle::toLaserData (include/awesome_slam/structures.h:126-133) -- producing the
+// (range, bearing) lists the filters consume (cbSensorLandmark, src/ekf/ekf.cpp:102-114).
+//
+// One warp per scan. Lanes project the 360 rays and mark the cluster breaks in parallel; lane 0 walks the break flags
+// (the reference's loop drops the point that opens every cluster after the first and never evaluates the trailing
+// run: reproduced as written); then every candidate cluster is classified and fitted by one lane, and the accepted
+// ones are compacted in scan order with a ballot. Float sites of the reference stay float (explicit _rn intrinsics;
+// the library is built with -fmad=false); the 4 x 4 eigen-problems are cyclic Jacobi in registers.
+// The sin/cos tables are built on the HOST exactly as LandMarks::initialize does (:50-57) and uploaded.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <new>
+
+#include "device_math.cuh"
+#include "internal.hpp"
+
+namespace aslam {
+
+namespace {
+
+constexpr int RAYS = 360;
+constexpr int MAXC = 96;   // candidate clusters per scan (a cluster needs > 3 points: at most 360 / 5)
+constexpr int LWPB = 4;    // warps (scans) per CTA
+
+struct LaserParams {
+    float thresh, std_max, min_mean, max_mean;
+    int min_pts;
+};
+
+struct __align__(16) ScanSlot {
+    float px[RAYS], py[RAYS];
+    unsigned char brk[RAYS + 8];
+    short cstart[MAXC], clen[MAXC];
+    int ncand;
+};
+
+// cyclic Jacobi, symmetric 4 x 4: A = V diag(w) V'
+__device__ __forceinline__ void jacobi4(double (&A)[4][4], double (&V)[4][4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) V[i][j] = i == j ? 1.0 : 0.0;
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        double off = 0.0, diag = 0.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (i == j)
+                    diag += A[i][j] * A[i][j];
+                else
+                    off += A[i][j] * A[i][j];
+            }
+        if (off <= 1e-60 * diag || off == 0.0) break;
+#pragma unroll
+        for (int p = 0; p < 3; ++p)
+#pragma unroll
+            for (int q = p + 1; q < 4; ++q) {
+                if (A[p][q] != 0.0) {
+                    const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
+                    const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+                    const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const double akp = A[k][p], akq = A[k][q];
+                        A[k][p] = c * akp - s * akq;
+                        A[k][q] = s * akp + c * akq;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const double apk = A[p][k], aqk = A[q][k];
+                        A[p][k] = c * apk - s * aqk;
+                        A[q][k] = s * apk + c * aqk;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const double vkp = V[k][p], vkq = V[k][q];
+                        V[k][p] = c * vkp - s * vkq;
+                        V[k][q] = s * vkp + c * vkq;
+                    }
+                }
+            }
+    }
+}
+
+// sensor_landmark.cpp:147-186 on points [s0, s0 + n) of the scan
+__device__ __forceinline__ bool classify(const ScanSlot& s, const LaserParams& lp, int s0, int n) {
+    const float x1 = s.px[s0], y1 = s.py[s0], x2 = s.px[s0 + n - 1], y2 = s.py[s0 + n - 1];
+    const float c = euler_distance(x1, y1, x2, y2);
+    const float cc = __fmul_rn(c, c);
+    float sum = 0.0f;
+    for (int i = 1; i < n - 1; ++i) {
+        const float x = s.px[s0 + i], y = s.py[s0 + i];
+        const float a = euler_distance(x1, y1, x, y), b = euler_distance(x2, y2, x, y);
+        const float num = __fsub_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), cc);
+        const float den = __fmul_rn(__fmul_rn(2.0f, a), b);
+        // acosf of the reference's libm, taken as the correctly rounded value of the double routine
+        const float angle = (float)acos((double)__fdiv_rn(num, den));
+        sum = __fadd_rn(sum, angle);
+    }
+    const float mean = __fdiv_rn(sum, (float)(n - 2));
+    float variance = 0.0f;
+    for (int i = 1; i < n - 1; ++i) {  // the angles are recomputed instead of stored (same values)
+        const float x = s.px[s0 + i], y = s.py[s0 + i];
+        const float a = euler_distance(x1, y1, x, y), b = euler_distance(x2, y2, x, y);
+        const float num = __fsub_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), cc);
+        const float den = __fmul_rn(__fmul_rn(2.0f, a), b);
+        const float angle = (float)acos((double)__fdiv_rn(num, den));
+        const double d = (double)__fsub_rn(angle, mean);
+        variance = (float)__dadd_rn((double)variance, __dmul_rn(d, d));  // pow(float, 2) is a double (:174)
+    }
+    const float sd = (float)sqrt(__ddiv_rn((double)variance, 5.0));  // (:177)
+    return sd < lp.std_max && mean > lp.min_mean && mean < lp.max_mean;
+}
+
+// sensor_landmark.cpp:192-298 (hyper-fit) + structures.h:126-133 on points [s0, s0 + n)
+__device__ __forceinline__ void fit(const ScanSlot& s, int s0, int n, float& out_range, float& out_bearing) {
+    float x_mean = 0.0f, y_mean = 0.0f, z_mean = 0.0f;
+    for (int i = 0; i < n; ++i) {
+        x_mean = __fadd_rn(x_mean, s.px[s0 + i]);
+        y_mean = __fadd_rn(y_mean, s.py[s0 + i]);
+    }
+    x_mean = __fdiv_rn(x_mean, (float)n);
+    y_mean = __fdiv_rn(y_mean, (float)n);
+    for (int i = 0; i < n; ++i) {
+        const float x = __fsub_rn(s.px[s0 + i], x_mean), y = __fsub_rn(s.py[s0 + i], y_mean);
+        z_mean = __fadd_rn(z_mean, __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)));
+    }
+    z_mean = __fdiv_rn(z_mean, (float)n);
+    // G = Z'Z for Z = [z x y 1]
+    double G[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) G[a][b] = 0.0;
+    for (int i = 0; i < n; ++i) {
+        const float x = __fsub_rn(s.px[s0 + i], x_mean), y = __fsub_rn(s.py[s0 + i], y_mean);
+        const float z = __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y));
+        const double row[4] = {(double)z, (double)x, (double)y, 1.0};
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) G[a][b] = __dadd_rn(G[a][b], __dmul_rn(row[a], row[b]));
+    }
+    double V[4][4];
+    jacobi4(G, V);
+    double sv[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) sv[i] = sqrt(G[i][i] > 0.0 ? G[i][i] : 0.0);
+    double sv_min = sv[0];
+#pragma unroll
+    for (int i = 1; i < 4; ++i) sv_min = sv[i] < sv_min ? sv[i] : sv_min;
+    double A[4];
+    if (sv_min > 10e-12) {  // (:256)
+        const double hz = (double)__fmul_rn(-2.0f, z_mean);  // H^-1(3,3) (:245)
+        // Y = V Sigma V'
+        double Y[4][4], T[4][4], Q[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) acc += V[a][k] * sv[k] * V[b][k];
+                Y[a][b] = acc;
+            }
+        // T = Y H^-1 with H^-1 = [0 0 0 1/2; 0 1 0 0; 0 0 1 0; 1/2 0 0 hz]
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            T[a][0] = Y[a][3] * 0.5;
+            T[a][1] = Y[a][1];
+            T[a][2] = Y[a][2];
+            T[a][3] = Y[a][0] * 0.5 + Y[a][3] * hz;
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b <= a; ++b) {  // the eigen-solver reads the lower triangle
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) acc += T[a][k] * Y[k][b];
+                Q[a][b] = acc;
+                Q[b][a] = acc;
+            }
+        double E[4][4];
+        jacobi4(Q, E);
+        // eigenvector of the smallest positive eigenvalue (< 99999), first one in ascending order (:259-283)
+        int col = -1;
+        double best = 99999.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const double ev = Q[i][i];
+            if (ev > 0.0 && ev < best) {
+                best = ev;
+                col = i;
+            }
+        }
+        if (col < 0) {  // no positive eigenvalue: the reference keeps smallest_id = 0, the most negative one
+            double lo = Q[0][0];
+            col = 0;
+#pragma unroll
+            for (int i = 1; i < 4; ++i)
+                if (Q[i][i] < lo) {
+                    lo = Q[i][i];
+                    col = i;
+                }
+        }
+        // A = Y^-1 A_star = V Sigma^-1 V' A_star
+        double t4[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            double d = 0.0;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                double e = E[a][0];
+                if (col == 1) e = E[a][1];
+                if (col == 2) e = E[a][2];
+                if (col == 3) e = E[a][3];
+                d += V[a][k] * e;
+            }
+            t4[k] = d / sv[k];
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            double acc = 0.0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc += V[a][k] * t4[k];
+            A[a] = acc;
+        }
+    } else {  // A = V.col(3): the singular vector of the smallest singular value
+        int im = 0;
+#pragma unroll
+        for (int i = 1; i < 4; ++i)
+            if (sv[i] < sv[im]) im = i;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            double e = V[a][0];
+            if (im == 1) e = V[a][1];
+            if (im == 2) e = V[a][2];
+            if (im == 3) e = V[a][3];
+            A[a] = e;
+        }
+    }
+    const float a = (float)(-A[1] / (2.0 * A[0]));
+    const float b = (float)(-A[2] / (2.0 * A[0]));
+    const double cx = (double)__fadd_rn(a, x_mean), cy = (double)__fadd_rn(b, y_mean);
+    out_range = (float)sqrt(__dadd_rn(__dmul_rn(cx, cx), __dmul_rn(cy, cy)));
+    out_bearing = (float)atan2(cy, cx);
+}
+
+__global__ void __launch_bounds__(LWPB * 32) laser_extract_kernel(const float* __restrict__ ranges, uint32_t nscan,
+                                                                 const float* __restrict__ cos_map,
+                                                                 const float* __restrict__ sin_map, LaserParams lp,
+                                                                 float* __restrict__ out_range,
+                                                                 float* __restrict__ out_bearing,
+                                                                 int32_t* __restrict__ counts) {
+    __shared__ ScanSlot slots[LWPB];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t scan = blockIdx.x * LWPB + warp;
+    if (scan >= nscan) return;  // whole warp; no CTA barrier in this kernel
+    ScanSlot& s = slots[warp];
+    const float* r = ranges + (size_t)scan * RAYS;
+    for (int t = lane; t < RAYS; t += 32) {  // bearing2pose (:136-142)
+        const float d = r[t];
+        s.px[t] = __fmul_rn(d, cos_map[t]);
+        s.py[t] = __fmul_rn(d, sin_map[t]);
+    }
+    __syncwarp();
+    // first and last ray on the same object: the reference's assert(theta < 359) fires (:82)
+    if (euler_distance(s.px[0], s.py[0], s.px[RAYS - 1], s.py[RAYS - 1]) < lp.thresh) {
+        if (lane == 0) counts[scan] = -1;
+        return;
+    }
+    for (int t = 1 + lane; t < RAYS; t += 32)
+        s.brk[t] = !(euler_distance(s.px[t - 1], s.py[t - 1], s.px[t], s.py[t]) < lp.thresh);
+    __syncwarp();
+    if (lane == 0) {  // (:85-124): cluster k = rays [start, t) evaluated at break t; the next one starts at t + 1
+        int start = 0, nc = 0;
+        for (int t = 1; t < RAYS; ++t) {
+            if (s.brk[t]) {
+                const int len = t - start;
+                if (len > lp.min_pts && nc < MAXC) {
+                    s.cstart[nc] = (short)start;
+                    s.clen[nc] = (short)len;
+                    ++nc;
+                }
+                start = t + 1;
+            }
+        }
+        s.ncand = nc;
+    }
+    __syncwarp();
+    const int nc = s.ncand;
+    int total = 0;
+    for (int base = 0; base < nc; base += 32) {
+        const int cnd = base + lane;
+        bool ok = false;
+        float rg = 0.0f, bg = 0.0f;
+        if (cnd < nc) {
+            const int s0 = s.cstart[cnd], n = s.clen[cnd];
+            ok = classify(s, lp, s0, n);
+            if (ok) fit(s, s0, n, rg, bg);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        const int slot = total + __popc(m & ((1u << lane) - 1u));
+        if (ok && slot < (int)ASLAM_LASER_MAX_LANDMARKS) {
+            out_range[(size_t)scan * ASLAM_LASER_MAX_LANDMARKS + slot] = rg;
+            out_bearing[(size_t)scan * ASLAM_LASER_MAX_LANDMARKS + slot] = bg;
+        }
+        total += __popc(m);
+    }
+    if (lane == 0) counts[scan] = total;
+}
+
+}  // namespace
+
+}  // namespace aslam
+
+using namespace aslam;
+
+struct aslam_laser {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    uint32_t max_scans = 0;
+    LaserParams lp;
+    float* d_cos = nullptr;
+    float* d_sin = nullptr;
+    float* d_ranges = nullptr;   // staging for the host entry point
+    float* d_range_out = nullptr;
+    float* d_bearing_out = nullptr;
+    int32_t* d_counts = nullptr;
+    uint64_t launches = 0;
+};
+
+extern "C" {
+
+void aslam_laser_config_default(aslam_laser_config* c) {
+    if (!c) return;
+    c->deg2rad = 0.01745329251f;  // config.h:40
+    c->min_dist_thresh = 0.5f;    // config.h:43
+    c->std_max = 0.4f;            // config.h:48
+    c->min_mean = 1.5f;           // config.h:49
+    c->max_mean = 3.0f;           // config.h:50
+    c->min_cluster_points = 3;    // config.h:51
+}
+
+aslam_status aslam_laser_create(const aslam_laser_config* cfg, uint32_t max_scans, int32_t device, aslam_laser** out) {
+    if (!out || max_scans == 0) return ASLAM_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("laser create: no CUDA device (this library has no CPU path)");
+        return ASLAM_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) return ASLAM_ERR_ARG;
+    aslam_laser_config c;
+    if (cfg)
+        c = *cfg;
+    else
+        aslam_laser_config_default(&c);
+    ASLAM_CUDA(cudaSetDevice(device));
+    aslam_laser* h = new (std::nothrow) aslam_laser;
+    if (!h) return ASLAM_ERR_ARG;
+    h->device = device;
+    h->max_scans = max_scans;
+    h->lp.thresh = c.min_dist_thresh;
+    h->lp.std_max = c.std_max;
+    h->lp.min_mean = c.min_mean;
+    h->lp.max_mean = c.max_mean;
+    h->lp.min_pts = c.min_cluster_points;
+    // LandMarks::initialize (sensor_landmark.cpp:50-57): float argument, float sin / cos of the host libm
+    float hc[RAYS], hs[RAYS];
+    for (int th = 0; th < RAYS; ++th) {
+        hs[th] = std::sin(c.deg2rad * static_cast<float>(th));
+        hc[th] = std::cos(c.deg2rad * static_cast<float>(th));
+    }
+    bool ok = cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    const size_t ob = (size_t)max_scans * ASLAM_LASER_MAX_LANDMARKS * sizeof(float);
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_cos, sizeof(hc)), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_sin, sizeof(hs)), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_ranges, (size_t)max_scans * RAYS * sizeof(float)), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_range_out, ob), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_bearing_out, ob), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_counts, (size_t)max_scans * sizeof(int32_t)), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMemcpy(h->d_cos, hc, sizeof(hc), cudaMemcpyHostToDevice), "tables");
+    ok = ok && cuda_ok(cudaMemcpy(h->d_sin, hs, sizeof(hs), cudaMemcpyHostToDevice), "tables");
+    if (!ok) {
+        aslam_laser_destroy(h);
+        return ASLAM_ERR_CUDA;
+    }
+    *out = h;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_laser_destroy(aslam_laser* h) {
+    if (!h) return ASLAM_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    void* ptrs[] = {h->d_cos, h->d_sin, h->d_ranges, h->d_range_out, h->d_bearing_out, h->d_counts};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_laser_extract_device(aslam_laser* h, const float* d_ranges, uint32_t nscan, float* d_range_out,
+                                        float* d_bearing_out, int32_t* d_counts) {
+    if (!h || !d_ranges || !d_range_out || !d_bearing_out || !d_counts) return ASLAM_ERR_ARG;
+    if (nscan == 0) return ASLAM_OK;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const uint32_t grid = (nscan + LWPB - 1) / LWPB;
+    laser_extract_kernel<<<grid, LWPB * 32, 0, h->stream>>>(d_ranges, nscan, h->d_cos, h->d_sin, h->lp, d_range_out,
+                                                           d_bearing_out, d_counts);
+    ASLAM_CUDA(cudaGetLastError());
+    h->launches += 1;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_laser_extract(aslam_laser* h, const float* ranges, uint32_t nscan, float* range_out,
+                                 float* bearing_out, int32_t* counts) {
+    if (!h || !ranges || !range_out || !bearing_out || !counts || nscan > h->max_scans) return ASLAM_ERR_ARG;
+    if (nscan == 0) return ASLAM_OK;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    ASLAM_CUDA(cudaMemcpyAsync(h->d_ranges, ranges, (size_t)nscan * RAYS * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    const aslam_status rc = aslam_laser_extract_device(h, h->d_ranges, nscan, h->d_range_out, h->d_bearing_out, h->d_counts);
+    if (rc != ASLAM_OK) return rc;
+    const size_t ob = (size_t)nscan * ASLAM_LASER_MAX_LANDMARKS * sizeof(float);
+    ASLAM_CUDA(cudaMemcpyAsync(range_out, h->d_range_out, ob, cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(bearing_out, h->d_bearing_out, ob, cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaMemcpyAsync(counts, h->d_counts, (size_t)nscan * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_laser_sync(aslam_laser* h) {
+    if (!h) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+void* aslam_laser_stream(aslam_laser* h) { return h ? (void*)h->stream : nullptr; }
+uint64_t aslam_laser_launch_count(aslam_laser* h) { return h ? h->launches : 0; }
+
+}  // extern "C"

@@ -396,3 +396,55 @@ class LargeFilter:
     @property
     def launch_count(self):
         return int(self._lib.aslam_large_launch_count(self._h))
+
+
+class LandMarks:
+    """Host mirror of the reference's sensor_landmark node (aslam::LandMarks, sensor_landmark.h:49-89): `callback`
+    takes LaserScans (360 ranges each, +inf = no return) and returns what the node publishes on
+    out/landmarks/sensor -- per scan the (range, bearing) lists of the fitted cylinders -- computed by the CUDA
+    kernel of csrc/laser_front.cu through the C ABI."""
+
+    MAX_LANDMARKS = 32
+
+    def __init__(self, max_scans=1, device=0):
+        self._lib = capi.lib()
+        self._h = C.c_void_p()
+        self.max_scans = int(max_scans)
+        capi.check(self._lib.aslam_laser_create(None, self.max_scans, device, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._lib.aslam_laser_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    @property
+    def stream(self):
+        return self._lib.aslam_laser_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return int(self._lib.aslam_laser_launch_count(self._h))
+
+    def sync(self):
+        capi.check(self._lib.aslam_laser_sync(self._h))
+
+    def callback(self, ranges):
+        """ranges: [nscan, 360] float32 (or [360]). Returns (range [nscan, 32], bearing [nscan, 32], counts [nscan]);
+        counts = -1 where the reference's assert(theta < 359) fires."""
+        ranges = capi.as_np(ranges, np.float32).reshape(-1, 360)
+        ns = ranges.shape[0]
+        rg = np.zeros((ns, self.MAX_LANDMARKS), np.float32)
+        bg = np.zeros((ns, self.MAX_LANDMARKS), np.float32)
+        cnt = np.zeros(ns, np.int32)
+        capi.check(self._lib.aslam_laser_extract(self._h, capi.ptr(ranges), ns, capi.ptr(rg), capi.ptr(bg), capi.ptr(cnt)))
+        return rg, bg, cnt
+
+    def callback_device(self, d_ranges, nscan, d_range_out, d_bearing_out, d_counts):
+        """Device pointers (ints); asynchronous on the handle's stream."""
+        capi.check(self._lib.aslam_laser_extract_device(self._h, d_ranges, nscan, d_range_out, d_bearing_out, d_counts))

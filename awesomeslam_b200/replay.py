@@ -116,3 +116,46 @@ def large_observations(tx, ty, pose, m=8, seed=0, sigma_r=0.01, sigma_b=0.005):
     r = dist[idx] + sigma_r * rng.standard_normal(m)
     b = br + sigma_b * rng.standard_normal(m)
     return r.astype(np.float32), b.astype(np.float32), idx
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Synthetic LaserScan generator: the Gazebo LDS model of the reference's robot -- 360 rays, one
+# per degree, 0.12 m .. 3.5 m, Gaussian range noise sigma = 0.01 m (turtlebot3_burger/model.sdf:94-119) -- against the
+# map's cylinders of radius 0.25 m (models/awesome_cylinder/model.sdf:18-22). Rays without a return carry +inf, as
+# Gazebo publishes them. Host-side test/bench input, plain numpy.
+# ---------------------------------------------------------------------------------------------------------------
+LASER_RAYS = 360
+LASER_MIN, LASER_MAX, LASER_SIGMA, CYL_RADIUS = 0.12, 3.5, 0.01, 0.25
+
+
+def laser_scans(lmx, lmy, poses, seed=0, sigma=LASER_SIGMA, radius=CYL_RADIUS):
+    """poses: [B, 3] (x, y, yaw) -> ranges [B, 360] float32."""
+    poses = np.asarray(poses, np.float64).reshape(-1, 3)
+    B = poses.shape[0]
+    lm = np.stack([np.asarray(lmx, np.float64), np.asarray(lmy, np.float64)], axis=1)  # [L, 2]
+    ang = poses[:, 2:3] + np.deg2rad(np.arange(LASER_RAYS, dtype=np.float64))[None, :]  # [B, 360]
+    dx, dy = np.cos(ang), np.sin(ang)
+    best = np.full((B, LASER_RAYS), np.inf)
+    for l in range(lm.shape[0]):  # ray-circle intersection, nearest positive root
+        cx = lm[l, 0] - poses[:, 0:1]
+        cy = lm[l, 1] - poses[:, 1:2]
+        b = dx * cx + dy * cy
+        disc = b * b - (cx * cx + cy * cy - radius * radius)
+        with np.errstate(invalid="ignore"):
+            t = b - np.sqrt(disc)
+        hit = (disc >= 0) & (t > 0)
+        best = np.where(hit & (t < best), t, best)
+    rng = np.random.default_rng(seed)
+    noisy = best + sigma * rng.standard_normal(best.shape)
+    out = np.where((best >= LASER_MIN) & (best <= LASER_MAX), noisy, np.inf)
+    return out.astype(np.float32)
+
+
+def laser_poses(B, seed=0, spread=0.6):
+    """Robot poses around the origin whose ray 0 / ray 359 do not graze a cylinder of the cfg1 map (the reference
+    aborts when the first and the last ray fall on the same object, sensor_landmark.cpp:82): yaw in (20, 70) deg."""
+    rng = np.random.default_rng(seed)
+    x = spread * (rng.random(B) - 0.5)
+    y = spread * (rng.random(B) - 0.5)
+    yaw = np.deg2rad(20.0 + 50.0 * rng.random(B))
+    return np.stack([x, y, yaw], axis=1)

@@ -253,6 +253,40 @@ aslam_status aslam_dense_trsm(void* stream, double* d_B, size_t ldb, int32_t m, 
 /* Measured throughput of the FP64 tensor pipe (DMMA) of `device`, TFLOP/s. */
 aslam_status aslam_probe_dmma_tflops(int32_t device, double* tflops);
 
+/* ---------------------------------------------------------------- laser front end -------- */
+/* The step in front of the filters: the reference's sensor_landmark node,
+ * awesome_slam/src/sensor_landmark/sensor_landmark.cpp -- LandMarks::callback (:59-133), bearing2pose
+ * (:136-142), circleClassification (:147-186), circleFitting (:192-298) and Circle::toLaserData
+ * (include/awesome_slam/structures.h:126-133) -- for a batch of LaserScans: 360 ranges per scan (one ray per
+ * degree, +inf = no return, as Gazebo publishes them) in, the (range, bearing) list of the fitted cylinders out,
+ * in scan order, exactly what cbSensorLandmark (src/ekf/ekf.cpp:102-114) receives. */
+#define ASLAM_LASER_RAYS 360u
+#define ASLAM_LASER_MAX_LANDMARKS 32u /* output slots per scan */
+typedef struct aslam_laser aslam_laser;
+typedef struct aslam_laser_config { /* include/awesome_slam/config.h:40-51 */
+    float deg2rad;                  /* DEG2RAD */
+    float min_dist_thresh;          /* MIN_DIST_THRESH */
+    float std_max;                  /* STD */
+    float min_mean;                 /* MIN_MEAN */
+    float max_mean;                 /* MAX_MEAN */
+    int32_t min_cluster_points;     /* MIN_CLUSTER_POINTS */
+} aslam_laser_config;
+void aslam_laser_config_default(aslam_laser_config* c);
+/* LandMarks::LandMarks + initialize (:38-57): the sin / cos tables are built on the host, as the reference does. */
+aslam_status aslam_laser_create(const aslam_laser_config* cfg, uint32_t max_scans, int32_t device, aslam_laser** out);
+aslam_status aslam_laser_destroy(aslam_laser* h);
+/* LandMarks::callback for nscan scans, host buffers: ranges [nscan][360]; range_out / bearing_out
+ * [nscan][ASLAM_LASER_MAX_LANDMARKS]; counts [nscan] = landmarks published for the scan, or -1 where the reference's
+ * assert(theta < 359) (:82) fires (first and last ray on the same object). Synchronous. */
+aslam_status aslam_laser_extract(aslam_laser* h, const float* ranges, uint32_t nscan, float* range_out,
+                                 float* bearing_out, int32_t* counts);
+/* Same with device buffers, asynchronous on the handle's stream (aslam_laser_sync / aslam_laser_stream). */
+aslam_status aslam_laser_extract_device(aslam_laser* h, const float* d_ranges, uint32_t nscan, float* d_range_out,
+                                        float* d_bearing_out, int32_t* d_counts);
+aslam_status aslam_laser_sync(aslam_laser* h);
+void* aslam_laser_stream(aslam_laser* h);
+uint64_t aslam_laser_launch_count(aslam_laser* h);
+
 /* ---------------------------------------------------------------- synthetic replay ------- */
 /* Deterministic replay generator of SURVEY.md sec. 8d (host code, no GPU needed):
  * map (lm_x, lm_y)[L]; `warm` stationary steps then vx, az constant, dt = 1.0f;

@@ -472,3 +472,104 @@ def ukf_large_step(X, Z, P, ox, oy, yaw, vx, az, dt, rng, brg):
     Xn = mean + K @ dz
     Pn = Pp - K @ S @ K.T
     return Xn, Z, Pn, np.array(assoc, np.int32), fail
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Laser front end: independent numpy restatement of sensor_landmark.cpp, used only to cross-check
+# oracle/laser_front.hpp. numpy.linalg.svd / eigh / solve stand in for Eigen's JacobiSVD / SelfAdjointEigenSolver /
+# colPivHouseholderQr; float32 arithmetic is done with numpy float32 scalars.
+# ------------------------------------------------------------------------------------------------------------------
+_F = np.float32
+
+
+def _laser_tables():
+    th = np.arange(360, dtype=np.float32)
+    ang = (_F(0.01745329251) * th).astype(np.float32)
+    return np.sin(ang).astype(np.float32), np.cos(ang).astype(np.float32)
+
+
+def _ldist(p, q):
+    dx = _F(np.float64(p[0]) - np.float64(q[0]))
+    dy = _F(np.float64(p[1]) - np.float64(q[1]))
+    return np.sqrt(_F(_F(dx * dx) + _F(dy * dy)))
+
+
+def laser_classify(pts):
+    """sensor_landmark.cpp:147-186"""
+    p1, p2 = pts[0], pts[-1]
+    ang = []
+    s = _F(0)
+    with np.errstate(all="ignore"):
+        for p in pts[1:-1]:
+            c, a, b = _ldist(p1, p2), _ldist(p1, p), _ldist(p2, p)
+            num = _F(_F(_F(a * a) + _F(b * b)) - _F(c * c))
+            v = np.arccos(_F(num / _F(_F(2) * a * b)))
+            ang.append(_F(v))
+            s = _F(s + _F(v))
+        mean = _F(s / _F(len(pts) - 2))
+        var = _F(0)
+        for v in ang:
+            var = _F(np.float64(var) + np.float64(_F(v - mean)) ** 2)
+        sd = _F(np.sqrt(np.float64(var) / 5.0))
+    return bool(sd < _F(0.4) and mean > _F(1.5) and mean < _F(3.0))
+
+
+def laser_fit(pts):
+    """sensor_landmark.cpp:192-298 + structures.h:126-133 -> (range, bearing) float32"""
+    n = len(pts)
+    xm = _F(0)
+    ym = _F(0)
+    for p in pts:
+        xm = _F(xm + _F(p[0]))
+        ym = _F(ym + _F(p[1]))
+    xm = _F(xm / _F(n))
+    ym = _F(ym / _F(n))
+    q = [(_F(_F(p[0]) - xm), _F(_F(p[1]) - ym)) for p in pts]
+    z = [_F(_F(a * a) + _F(b * b)) for a, b in q]
+    zm = _F(0)
+    for v in z:
+        zm = _F(zm + v)
+    zm = _F(zm / _F(n))
+    Z = np.array([[np.float64(z[i]), np.float64(q[i][0]), np.float64(q[i][1]), 1.0] for i in range(n)])
+    Hinv = np.array([[0, 0, 0, 0.5], [0, 1, 0, 0], [0, 0, 1, 0], [0.5, 0, 0, np.float64(_F(_F(-2) * zm))]], dtype=np.float64)
+    U, sv, Vt = np.linalg.svd(Z, full_matrices=False)
+    V = Vt.T
+    if sv[3] > 10e-12:
+        Y = V @ np.diag(sv) @ V.T
+        Q = Y @ Hinv @ Y
+        ev, E = np.linalg.eigh(Q)
+        sid, sev = 0, _F(99999)
+        for i in range(4):
+            if ev[i] > 0 and ev[i] < np.float64(sev):
+                sid, sev = i, _F(ev[i])
+        A = np.linalg.solve(Y, E[:, sid])
+    else:
+        A = V[:, 3]
+    a = _F(-A[1] / (2 * A[0]))
+    b = _F(-A[2] / (2 * A[0]))
+    cx, cy = np.float64(_F(a + xm)), np.float64(_F(b + ym))
+    return _F(np.sqrt(cx * cx + cy * cy)), _F(np.arctan2(cy, cx))
+
+
+def laser_extract(ranges):
+    """sensor_landmark.cpp:59-133 for one scan of 360 float32 ranges -> list of (range, bearing), or None where
+    the reference's assert(theta < 359) fires."""
+    sin_map, cos_map = _laser_tables()
+    with np.errstate(all="ignore"):
+        px = (ranges.astype(np.float32) * cos_map).astype(np.float32)
+        py = (ranges.astype(np.float32) * sin_map).astype(np.float32)
+        pts = list(zip(px, py))
+        if _ldist(pts[0], pts[359]) < _F(0.5):
+            return None
+        out, cluster, p1 = [], [pts[0]], pts[0]
+        for th in range(1, 360):
+            p2 = pts[th]
+            if _ldist(p1, p2) < _F(0.5):
+                cluster.append(p2)
+            elif len(cluster) > 3 and laser_classify(cluster):
+                out.append(laser_fit(cluster))
+                cluster = []
+            else:
+                cluster = []
+            p1 = p2
+    return out

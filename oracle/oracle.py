@@ -169,5 +169,20 @@ def ekf_large_step(cfg, X, P_colmajor, a00, a10, x, y, yaw, vx, az, dt, rng, brg
     return q, assoc[:rng.size], A0.value, A1.value
 
 
+def laser_extract(ranges, cap=32):
+    """Laser front end over scans [nscan, 360] float32 -> (range [nscan, cap], bearing [nscan, cap], counts [nscan],
+    seconds). counts = -1 where the reference's assert(theta < 359) fires."""
+    ranges = np.ascontiguousarray(ranges, np.float32).reshape(-1, 360)
+    ns = ranges.shape[0]
+    out_r = np.zeros((ns, cap), np.float32)
+    out_b = np.zeros((ns, cap), np.float32)
+    cnt = np.zeros(ns, np.int32)
+    l = lib()
+    l.orc_laser_extract.restype = C.c_double
+    l.orc_laser_extract.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    sec = l.orc_laser_extract(_p(ranges), ns, cap, _p(out_r), _p(out_b), _p(cnt))
+    return out_r, out_b, cnt, sec
+
+
 def num_threads():
     return int(lib().orc_num_threads())

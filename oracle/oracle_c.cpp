@@ -5,6 +5,7 @@
 #include <cstring>
 #include <memory>
 
+#include "laser_front.hpp"
 #include "slam_filters.hpp"
 
 #ifdef _OPENMP
@@ -382,6 +383,18 @@ int orc_ekf_large_step(const orc_config* cc, uint32_t n, double* X, double* P, d
             Pm(i, j) -= s;
         }
     return q;
+}
+
+// Laser front end (laser_front.hpp) over `nscan` scans of 360 ranges, OpenMP over scans. out_range / out_bearing:
+// [nscan][cap]; counts [nscan] (-1: the reference's assert fires). Returns the wall time in seconds.
+double orc_laser_extract(const float* ranges, int nscan, int cap, float* out_range, float* out_bearing, int* counts) {
+    const LaserConfig cfg;
+    laser_extract(cfg, ranges, out_range, out_bearing, 0);  // builds the sin / cos tables before the parallel loop
+    const auto t0 = std::chrono::steady_clock::now();
+#pragma omp parallel for schedule(static)
+    for (int s = 0; s < nscan; ++s)
+        counts[s] = laser_extract(cfg, ranges + (size_t)s * 360, out_range + (size_t)s * cap, out_bearing + (size_t)s * cap, cap);
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
 int orc_num_threads(void) {
