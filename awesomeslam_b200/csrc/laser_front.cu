@@ -44,43 +44,48 @@ __device__ __forceinline__ void jacobi4(double (&A)[4][4], double (&V)[4][4]) {
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) V[i][j] = i == j ? 1.0 : 0.0;
+    // classical cyclic Jacobi: the rotated entry is set to exactly 0; from the 4th sweep on an entry too small to
+    // change either of its diagonal neighbours is dropped; ends when the off-diagonal part is exactly zero
     for (int sweep = 0; sweep < 30; ++sweep) {
-        double off = 0.0, diag = 0.0;
+        double off = 0.0;
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 3; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if (i == j)
-                    diag += A[i][j] * A[i][j];
-                else
-                    off += A[i][j] * A[i][j];
-            }
-        if (off <= 1e-60 * diag || off == 0.0) break;
+            for (int j = i + 1; j < 4; ++j) off += fabs(A[i][j]);
+        if (off == 0.0) break;
 #pragma unroll
         for (int p = 0; p < 3; ++p)
 #pragma unroll
             for (int q = p + 1; q < 4; ++q) {
                 if (A[p][q] != 0.0) {
-                    const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
-                    const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-                    const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+                    const double g = 100.0 * fabs(A[p][q]);
+                    if (sweep > 3 && fabs(A[p][p]) + g == fabs(A[p][p]) && fabs(A[q][q]) + g == fabs(A[q][q])) {
+                        A[p][q] = 0.0;
+                        A[q][p] = 0.0;
+                    } else {
+                        const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
+                        const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+                        const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const double akp = A[k][p], akq = A[k][q];
-                        A[k][p] = c * akp - s * akq;
-                        A[k][q] = s * akp + c * akq;
-                    }
+                        for (int k = 0; k < 4; ++k) {
+                            const double akp = A[k][p], akq = A[k][q];
+                            A[k][p] = c * akp - s * akq;
+                            A[k][q] = s * akp + c * akq;
+                        }
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const double apk = A[p][k], aqk = A[q][k];
-                        A[p][k] = c * apk - s * aqk;
-                        A[q][k] = s * apk + c * aqk;
-                    }
+                        for (int k = 0; k < 4; ++k) {
+                            const double apk = A[p][k], aqk = A[q][k];
+                            A[p][k] = c * apk - s * aqk;
+                            A[q][k] = s * apk + c * aqk;
+                        }
+                        A[p][q] = 0.0;
+                        A[q][p] = 0.0;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const double vkp = V[k][p], vkq = V[k][q];
-                        V[k][p] = c * vkp - s * vkq;
-                        V[k][q] = s * vkp + c * vkq;
+                        for (int k = 0; k < 4; ++k) {
+                            const double vkp = V[k][p], vkq = V[k][q];
+                            V[k][p] = c * vkp - s * vkq;
+                            V[k][q] = s * vkp + c * vkq;
+                        }
                     }
                 }
             }

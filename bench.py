@@ -451,6 +451,52 @@ def _emit(line):
     out.flush()
 
 
+def laser_leg(args, torch, dev):
+    """the laser front end. 65,536 synthetic LDS scans of the cfg3 map (one per filter of the batch);
+    device-resident scans/s (CUDA events on the handle's stream), the same through host buffers (copy in, lists out),
+    and the oracle on the host cores over a bounded sample. Algorithmic bytes per scan: 360 ranges in (1,440 B) +
+    2 x 32 floats + 1 count out (260 B)."""
+    import awesomeslam_b200 as A
+    from oracle import oracle as O
+    B = 65536
+    lmx, lmy = A.map_cfg3()
+    base = A.laser_scans(lmx, lmy, A.laser_poses(4096, seed=77), seed=78)
+    sc = np.tile(base, (B // base.shape[0], 1))
+    lm = A.LandMarks(max_scans=B, device=dev.index)
+    stream = torch.cuda.ExternalStream(lm.stream, device=dev)
+    d_sc = torch.from_numpy(sc).to(dev)
+    d_r = torch.empty((B, 32), dtype=torch.float32, device=dev)
+    d_b = torch.empty((B, 32), dtype=torch.float32, device=dev)
+    d_c = torch.empty((B,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize(dev)
+    reps = 5
+    with torch.cuda.stream(stream):
+        for _ in range(2):
+            lm.callback_device(d_sc.data_ptr(), B, d_r.data_ptr(), d_b.data_ptr(), d_c.data_ptr())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            lm.callback_device(d_sc.data_ptr(), B, d_r.data_ptr(), d_b.data_ptr(), d_c.data_ptr())
+        e1.record()
+        lm.sync()
+        ms = e0.elapsed_time(e1) / reps
+    t0 = time.perf_counter()
+    rg, bg, cnt = lm.callback(sc)
+    host_s = time.perf_counter() - t0
+    sample = sc[:4096]
+    org, obg, ocnt, sec = O.laser_extract(sample)
+    assert np.array_equal(cnt[:4096], ocnt) and np.array_equal(d_c.cpu().numpy(), cnt)
+    same = all(np.array_equal(rg[i, :ocnt[i]], org[i, :ocnt[i]]) for i in range(0, 4096, 64))
+    lm.close()
+    return {"workload": "laser front end: 65,536 LDS scans (360 rays) of the cfg3 map -> (range, bearing) lists",
+            "scans_per_s": B / (ms * 1e-3), "ms_per_batch": ms, "landmarks_per_scan": float(cnt.mean()),
+            "hbm_gbs": B * (1440 + 260) / (ms * 1e-3) / 1e9,
+            "e2e_scans_per_s": B / host_s, "e2e_api": "aslam_laser_extract (pageable host buffers, synchronous)",
+            "cpu_baseline": {"value": 4096 / sec, "unit": "scans/s", "cores": O.num_threads(), "kind": "port",
+                             "sample": "4,096 of the 65,536 scans, OpenMP over scans"},
+            "matches_oracle_on_sample": bool(same)}
+
+
 def main():
     args = parse()
     _claim_stdout()
@@ -491,6 +537,9 @@ def main():
     ukf_large = None
     if rank == 0 and not args.no_large:
         ukf_large = ukf_large_leg(args, torch, dev)
+    laser = None
+    if rank == 0 and not args.no_large:
+        laser = laser_leg(args, torch, dev)
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -528,6 +577,8 @@ def main():
         line["roofline"] = None
     if ukf_large:
         line["large_map_ukf"] = ukf_large
+    if laser is not None:
+        line["laser_front"] = laser
     if not args.no_cpu:
         ups, nthr, sec = cpu_leg(256 if (os.cpu_count() or 1) < 16 else 1024, 120)
         line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": nthr, "kind": "port",

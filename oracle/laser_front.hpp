@@ -46,14 +46,23 @@ inline void jacobi4(const double Ain[4][4], double w[4], double V[4][4]) {
             A[i][j] = Ain[i][j];
             V[i][j] = i == j ? 1.0 : 0.0;
         }
+    // Classical cyclic Jacobi: a rotation annihilates A[p][q] (set to exactly 0 afterwards); from the 4th sweep on an
+    // off-diagonal entry that no longer changes either of its diagonal entries is dropped. Ends when the
+    // off-diagonal part is exactly zero.
     for (int sweep = 0; sweep < 30; ++sweep) {
-        double off = 0.0, diag = 0.0;
-        for (int i = 0; i < 4; ++i)
-            for (int j = 0; j < 4; ++j) (i == j ? diag : off) += A[i][j] * A[i][j];
-        if (off <= 1e-60 * diag || off == 0.0) break;
+        double off = 0.0;
+        for (int i = 0; i < 3; ++i)
+            for (int j = i + 1; j < 4; ++j) off += std::fabs(A[i][j]);
+        if (off == 0.0) break;
         for (int p = 0; p < 3; ++p)
             for (int q = p + 1; q < 4; ++q) {
                 if (A[p][q] == 0.0) continue;
+                const double g = 100.0 * std::fabs(A[p][q]);
+                if (sweep > 3 && std::fabs(A[p][p]) + g == std::fabs(A[p][p]) &&
+                    std::fabs(A[q][q]) + g == std::fabs(A[q][q])) {
+                    A[p][q] = A[q][p] = 0.0;
+                    continue;
+                }
                 const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
                 const double t = (theta >= 0 ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
                 const double c = 1.0 / std::sqrt(t * t + 1.0), s = t * c;
@@ -67,6 +76,7 @@ inline void jacobi4(const double Ain[4][4], double w[4], double V[4][4]) {
                     A[p][k] = c * apk - s * aqk;
                     A[q][k] = s * apk + c * aqk;
                 }
+                A[p][q] = A[q][p] = 0.0;
                 for (int k = 0; k < 4; ++k) {
                     const double vkp = V[k][p], vkq = V[k][q];
                     V[k][p] = c * vkp - s * vkq;
