@@ -4,9 +4,9 @@
 // hyper-fit (:192-298) and Circle::toLaserData (include/awesome_slam/structures.h:126-133) -- producing the
 // (range, bearing) lists the filters consume (cbSensorLandmark, src/ekf/ekf.cpp:102-114).
 //
-// One warp per scan. Lanes project the 360 rays and mark the cluster breaks in parallel; lane 0 walks the break flags
-// (the reference's loop drops the point that opens every cluster after the first and never evaluates the trailing
-// run: reproduced as written); then every candidate cluster is classified and fitted by one lane, and the accepted
+// One warp per scan. Lanes project the 360 rays, mark the cluster breaks and pair consecutive breaks into candidate
+// clusters with ballots (the reference's loop drops the point that opens every cluster after the first and never
+// evaluates the trailing run: reproduced as written); then every candidate cluster is classified and fitted by one lane, and the accepted
 // ones are compacted in scan order with a ballot. Float sites of the reference stay float (explicit _rn intrinsics;
 // the library is built with -fmad=false); the 4 x 4 eigen-problems are cyclic Jacobi in registers.
 // The sin/cos tables are built on the HOST exactly as LandMarks::initialize does (:50-57) and uploaded.
@@ -33,7 +33,6 @@ struct LaserParams {
 
 struct __align__(16) ScanSlot {
     float px[RAYS], py[RAYS];
-    unsigned char brk[RAYS + 8];
     short cstart[MAXC], clen[MAXC];
     int ncand;
 };
@@ -280,23 +279,31 @@ __global__ void __launch_bounds__(LWPB * 32) laser_extract_kernel(const float* _
         if (lane == 0) counts[scan] = -1;
         return;
     }
-    for (int t = 1 + lane; t < RAYS; t += 32)
-        s.brk[t] = !(euler_distance(s.px[t - 1], s.py[t - 1], s.px[t], s.py[t]) < lp.thresh);
-    __syncwarp();
-    if (lane == 0) {  // (:85-124): cluster k = rays [start, t) evaluated at break t; the next one starts at t + 1
-        int start = 0, nc = 0;
-        for (int t = 1; t < RAYS; ++t) {
-            if (s.brk[t]) {
-                const int len = t - start;
-                if (len > lp.min_pts && nc < MAXC) {
-                    s.cstart[nc] = (short)start;
-                    s.clen[nc] = (short)len;
-                    ++nc;
-                }
-                start = t + 1;
+    // (:85-124) A break at ray t (the step from t-1 to t is not below the threshold; NaN counts) closes the cluster
+    // [start, t) and the next one starts at t + 1: the candidates are the pairs of consecutive breaks (b, t) with
+    // t - b - 1 > MIN_CLUSTER_POINTS (first cluster: start = 0). Every lane looks at one ray per round; the previous
+    // break comes from the ballot of its round or from the running last break of the earlier rounds; candidates are
+    // appended in scan order (ballot + prefix count).
+    {
+        int last_break = -1, nc = 0;  // warp-uniform
+        for (int base = 1; base < RAYS; base += 32) {
+            const int t = base + lane;
+            const bool brk = t < RAYS && !(euler_distance(s.px[t - 1], s.py[t - 1], s.px[t], s.py[t]) < lp.thresh);
+            const unsigned m = __ballot_sync(0xffffffffu, brk);
+            const unsigned below = m & ((1u << lane) - 1u);
+            const int prev = below ? base + (31 - __clz(below)) : last_break;
+            const int start = prev + 1;  // prev = -1: the first cluster starts at ray 0
+            const bool cand = brk && (t - start) > lp.min_pts;
+            const unsigned cm = __ballot_sync(0xffffffffu, cand);
+            const int slot = nc + __popc(cm & ((1u << lane) - 1u));
+            if (cand && slot < MAXC) {
+                s.cstart[slot] = (short)start;
+                s.clen[slot] = (short)(t - start);
             }
+            nc += __popc(cm);
+            if (m) last_break = base + (31 - __clz(m));
         }
-        s.ncand = nc;
+        if (lane == 0) s.ncand = nc < MAXC ? nc : MAXC;
     }
     __syncwarp();
     const int nc = s.ncand;

@@ -4,6 +4,7 @@
   python tools/prof_target.py ukf [B] [msgs]       batched UKF kernel
   python tools/prof_target.py large [side] [m]     cfg4 large-map EKF step (side^2 landmarks)
   python tools/prof_target.py ukf_large [side]     cfg5 large-map UKF step
+  python tools/prof_target.py laser [B]            laser front end, B scans of the cfg3 map
 """
 import os
 import sys
@@ -54,10 +55,22 @@ def ukf_large(side):
     print("ukf_large n", X0.size)
 
 
+def laser(B):
+    lmx, lmy = A.map_cfg3()
+    base = A.laser_scans(lmx, lmy, A.laser_poses(4096, seed=77), seed=78)
+    sc = np.tile(base, (max(B // 4096, 1), 1))
+    lm = A.LandMarks(max_scans=sc.shape[0])
+    for _ in range(3):
+        rg, bg, cnt = lm.callback(sc)
+    print("laser scans", sc.shape[0], "landmarks/scan", float(cnt.mean()))
+
+
 if __name__ == "__main__":
     mode = sys.argv[1]
     arg = [int(v) for v in sys.argv[2:]]
-    if mode in ("batched", "ukf"):
+    if mode == "laser":
+        laser(arg[0] if arg else 65536)
+    elif mode in ("batched", "ukf"):
         batched("ekf" if mode == "batched" else "ukf", arg[0] if arg else 65536, arg[1] if len(arg) > 1 else 8)
     elif mode == "large":
         large(arg[0] if arg else 64, arg[1] if len(arg) > 1 else 8)
