@@ -112,6 +112,8 @@ SIGNATURES = {
     "aslam_laser_destroy": (_i32, [_vp]),
     "aslam_laser_extract": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp]),
     "aslam_laser_extract_device": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp]),
+    "aslam_laser_synthesize": (_i32, [_vp, _vp, _vp, _u32, _vp, _vp, _u32, _f64, _f64, _vp]),
+    "aslam_laser_synthesize_device": (_i32, [_vp, _vp, _vp, _u32, _vp, _vp, _u32, _f64, _f64, _vp]),
     "aslam_laser_sync": (_i32, [_vp]),
     "aslam_laser_stream": (_vp, [_vp]),
     "aslam_laser_launch_count": (C.c_uint64, [_vp]),

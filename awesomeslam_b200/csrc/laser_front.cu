@@ -328,6 +328,35 @@ __global__ void __launch_bounds__(LWPB * 32) laser_extract_kernel(const float* _
     if (lane == 0) counts[scan] = total;
 }
 
+// the Gazebo LDS model as arithmetic -- one thread per ray: ray k of a scan leaves the sensor at
+// yaw + k degrees, hits the nearest cylinder (radius r) of the map, returns inside [rmin, rmax] get sigma * noise
+// added, everything else is +inf (what Gazebo publishes for "no return").
+__global__ void __launch_bounds__(256) laser_synth_kernel(const double* __restrict__ lm_x, const double* __restrict__ lm_y,
+                                                         uint32_t L, const double* __restrict__ poses,
+                                                         const float* __restrict__ noise, uint32_t nscan, double sigma,
+                                                         double radius, double rmin, double rmax,
+                                                         float* __restrict__ ranges) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)nscan * RAYS) return;
+    const uint32_t scan = (uint32_t)(idx / RAYS), k = (uint32_t)(idx % RAYS);
+    const double px = poses[3 * (size_t)scan], py = poses[3 * (size_t)scan + 1], yaw = poses[3 * (size_t)scan + 2];
+    double sn, cs;
+    sincos(yaw + (double)k * (3.14159265358979323846 / 180.0), &sn, &cs);
+    double best = INFINITY;
+    for (uint32_t l = 0; l < L; ++l) {
+        const double cx = lm_x[l] - px, cy = lm_y[l] - py;
+        const double b = cs * cx + sn * cy;
+        const double disc = b * b - (cx * cx + cy * cy - radius * radius);
+        if (disc >= 0.0) {
+            const double t = b - sqrt(disc);
+            if (t > 0.0 && t < best) best = t;
+        }
+    }
+    float out = INFINITY;
+    if (best >= rmin && best <= rmax) out = (float)(best + sigma * (noise ? (double)noise[idx] : 0.0));
+    ranges[idx] = out;
+}
+
 }  // namespace
 
 }  // namespace aslam
@@ -447,6 +476,48 @@ aslam_status aslam_laser_extract(aslam_laser* h, const float* ranges, uint32_t n
     ASLAM_CUDA(cudaMemcpyAsync(counts, h->d_counts, (size_t)nscan * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
     ASLAM_CUDA(cudaStreamSynchronize(h->stream));
     return ASLAM_OK;
+}
+
+aslam_status aslam_laser_synthesize_device(aslam_laser* h, const double* d_lm_x, const double* d_lm_y, uint32_t L,
+                                           const double* d_poses, const float* d_noise, uint32_t nscan, double sigma,
+                                           double radius, float* d_ranges) {
+    if (!h || !d_lm_x || !d_lm_y || !d_poses || !d_ranges) return ASLAM_ERR_ARG;
+    if (nscan == 0) return ASLAM_OK;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t total = (size_t)nscan * RAYS;
+    laser_synth_kernel<<<(unsigned)((total + 255) / 256), 256, 0, h->stream>>>(d_lm_x, d_lm_y, L, d_poses, d_noise, nscan,
+                                                                              sigma, radius, 0.12, 3.5, d_ranges);
+    ASLAM_CUDA(cudaGetLastError());
+    h->launches += 1;
+    return ASLAM_OK;
+}
+
+aslam_status aslam_laser_synthesize(aslam_laser* h, const double* lm_x, const double* lm_y, uint32_t L, const double* poses,
+                                    const float* noise, uint32_t nscan, double sigma, double radius, float* ranges) {
+    if (!h || !lm_x || !lm_y || !poses || !ranges || nscan > h->max_scans) return ASLAM_ERR_ARG;
+    if (nscan == 0) return ASLAM_OK;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    double* d_map = nullptr;   // [2][L] map, then [nscan][3] poses
+    float* d_noise = nullptr;
+    const size_t total = (size_t)nscan * RAYS;
+    ASLAM_CUDA(cudaMalloc((void**)&d_map, ((size_t)2 * L + (size_t)3 * nscan) * sizeof(double)));
+    aslam_status rc = ASLAM_OK;
+    if (noise && !cuda_ok(cudaMalloc((void**)&d_noise, total * sizeof(float)), "cudaMalloc")) rc = ASLAM_ERR_CUDA;
+    const cudaMemcpyKind k = cudaMemcpyHostToDevice;
+    if (rc == ASLAM_OK && !cuda_ok(cudaMemcpyAsync(d_map, lm_x, L * sizeof(double), k, h->stream), "copy")) rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK && !cuda_ok(cudaMemcpyAsync(d_map + L, lm_y, L * sizeof(double), k, h->stream), "copy")) rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK && !cuda_ok(cudaMemcpyAsync(d_map + 2 * L, poses, (size_t)3 * nscan * sizeof(double), k, h->stream), "copy"))
+        rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK && noise && !cuda_ok(cudaMemcpyAsync(d_noise, noise, total * sizeof(float), k, h->stream), "copy"))
+        rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK)
+        rc = aslam_laser_synthesize_device(h, d_map, d_map + L, L, d_map + 2 * L, d_noise, nscan, sigma, radius, h->d_ranges);
+    if (rc == ASLAM_OK && !cuda_ok(cudaMemcpyAsync(ranges, h->d_ranges, total * sizeof(float), cudaMemcpyDeviceToHost, h->stream), "copy"))
+        rc = ASLAM_ERR_CUDA;
+    if (!cuda_ok(cudaStreamSynchronize(h->stream), "sync") && rc == ASLAM_OK) rc = ASLAM_ERR_CUDA;
+    cudaFree(d_map);
+    if (d_noise) cudaFree(d_noise);
+    return rc;
 }
 
 aslam_status aslam_laser_sync(aslam_laser* h) {

@@ -445,6 +445,20 @@ class LandMarks:
         capi.check(self._lib.aslam_laser_extract(self._h, capi.ptr(ranges), ns, capi.ptr(rg), capi.ptr(bg), capi.ptr(cnt)))
         return rg, bg, cnt
 
+    def synthesize(self, lmx, lmy, poses, noise=None, sigma=0.01, radius=0.25):
+        """Synthetic LDS scans on the GPU (the Gazebo stand-in): poses [nscan, 3] (x, y, yaw), noise [nscan, 360]
+        standard-normal float32 or None -> ranges [nscan, 360] float32 (+inf = no return)."""
+        lmx = capi.as_np(lmx, np.float64)
+        lmy = capi.as_np(lmy, np.float64)
+        poses = capi.as_np(poses, np.float64).reshape(-1, 3)
+        ns = poses.shape[0]
+        if noise is not None:
+            noise = capi.as_np(noise, np.float32).reshape(ns, 360)
+        out = np.zeros((ns, 360), np.float32)
+        capi.check(self._lib.aslam_laser_synthesize(self._h, capi.ptr(lmx), capi.ptr(lmy), lmx.size, capi.ptr(poses),
+                                                    capi.ptr(noise), ns, float(sigma), float(radius), capi.ptr(out)))
+        return out
+
     def callback_device(self, d_ranges, nscan, d_range_out, d_bearing_out, d_counts):
         """Device pointers (ints); asynchronous on the handle's stream."""
         capi.check(self._lib.aslam_laser_extract_device(self._h, d_ranges, nscan, d_range_out, d_bearing_out, d_counts))

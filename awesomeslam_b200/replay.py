@@ -128,8 +128,9 @@ LASER_RAYS = 360
 LASER_MIN, LASER_MAX, LASER_SIGMA, CYL_RADIUS = 0.12, 3.5, 0.01, 0.25
 
 
-def laser_scans(lmx, lmy, poses, seed=0, sigma=LASER_SIGMA, radius=CYL_RADIUS):
-    """poses: [B, 3] (x, y, yaw) -> ranges [B, 360] float32."""
+def laser_scans(lmx, lmy, poses, seed=0, sigma=LASER_SIGMA, radius=CYL_RADIUS, noise=None):
+    """poses: [B, 3] (x, y, yaw) -> ranges [B, 360] float32. noise: [B, 360] standard-normal values to use instead
+    of drawing them from `seed` (the CUDA generator aslam_laser_synthesize takes the same array)."""
     poses = np.asarray(poses, np.float64).reshape(-1, 3)
     B = poses.shape[0]
     lm = np.stack([np.asarray(lmx, np.float64), np.asarray(lmy, np.float64)], axis=1)  # [L, 2]
@@ -145,17 +146,23 @@ def laser_scans(lmx, lmy, poses, seed=0, sigma=LASER_SIGMA, radius=CYL_RADIUS):
             t = b - np.sqrt(disc)
         hit = (disc >= 0) & (t > 0)
         best = np.where(hit & (t < best), t, best)
-    rng = np.random.default_rng(seed)
-    noisy = best + sigma * rng.standard_normal(best.shape)
+    if noise is None:
+        noise = np.random.default_rng(seed).standard_normal(best.shape)
+    noisy = best + sigma * np.asarray(noise, np.float64).reshape(best.shape)
     out = np.where((best >= LASER_MIN) & (best <= LASER_MAX), noisy, np.inf)
     return out.astype(np.float32)
 
 
-def laser_poses(B, seed=0, spread=0.6):
-    """Robot poses around the origin whose ray 0 / ray 359 do not graze a cylinder of the cfg1 map (the reference
-    aborts when the first and the last ray fall on the same object, sensor_landmark.cpp:82): yaw in (20, 70) deg."""
+LASER_POSES_CFG3 = dict(spread=0.2, yaw_deg=(19.0, 26.0))  # ray 0 between the 0 and 45 degree cylinders
+
+
+def laser_poses(B, seed=0, spread=0.6, yaw_deg=(20.0, 70.0)):
+    """Robot poses around the origin whose ray 0 / ray 359 do not graze a cylinder (the reference aborts when the
+    first and the last ray fall on the same object, sensor_landmark.cpp:82). Defaults suit the cfg1 map (cylinders
+    at 0, 90, 180, 270 degrees and on the diagonals at 4.2 m, out of range); for the cfg3 map, which also has
+    cylinders on the diagonals at 2.1 m, use LASER_POSES_CFG3."""
     rng = np.random.default_rng(seed)
     x = spread * (rng.random(B) - 0.5)
     y = spread * (rng.random(B) - 0.5)
-    yaw = np.deg2rad(20.0 + 50.0 * rng.random(B))
+    yaw = np.deg2rad(yaw_deg[0] + (yaw_deg[1] - yaw_deg[0]) * rng.random(B))
     return np.stack([x, y, yaw], axis=1)

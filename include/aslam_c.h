@@ -283,6 +283,17 @@ aslam_status aslam_laser_extract(aslam_laser* h, const float* ranges, uint32_t n
 /* Same with device buffers, asynchronous on the handle's stream (aslam_laser_sync / aslam_laser_stream). */
 aslam_status aslam_laser_extract_device(aslam_laser* h, const float* d_ranges, uint32_t nscan, float* d_range_out,
                                         float* d_bearing_out, int32_t* d_counts);
+/* Synthetic LaserScans, standing in for Gazebo's LDS plugin: 360 rays, one per degree from the
+ * sensor's yaw, against cylinders of `radius` at (lm_x, lm_y)[L] (models/awesome_cylinder/model.sdf:18-22: 0.25 m);
+ * returns inside 0.12 .. 3.5 m get sigma * noise added (turtlebot3_burger/model.sdf:94-119: sigma 0.01), every other
+ * ray is +inf. poses [nscan][3] = x, y, yaw (double); noise [nscan][360] standard-normal floats or NULL; ranges
+ * [nscan][360]. Host buffers / device buffers (asynchronous on the handle's stream). */
+aslam_status aslam_laser_synthesize(aslam_laser* h, const double* lm_x, const double* lm_y, uint32_t L,
+                                    const double* poses, const float* noise, uint32_t nscan, double sigma,
+                                    double radius, float* ranges);
+aslam_status aslam_laser_synthesize_device(aslam_laser* h, const double* d_lm_x, const double* d_lm_y, uint32_t L,
+                                           const double* d_poses, const float* d_noise, uint32_t nscan, double sigma,
+                                           double radius, float* d_ranges);
 aslam_status aslam_laser_sync(aslam_laser* h);
 void* aslam_laser_stream(aslam_laser* h);
 uint64_t aslam_laser_launch_count(aslam_laser* h);

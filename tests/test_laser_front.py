@@ -15,7 +15,7 @@ def _wall():
 
 def _scans(aslam, B, seed, cfg3=False):
     lmx, lmy = aslam.map_cfg3() if cfg3 else aslam.map_cfg1()
-    poses = aslam.laser_poses(B, seed=seed)
+    poses = aslam.laser_poses(B, seed=seed, **(aslam.replay.LASER_POSES_CFG3 if cfg3 else {}))
     return aslam.laser_scans(lmx, lmy, poses, seed=seed + 1), poses, lmx, lmy
 
 
@@ -116,3 +116,23 @@ def test_laser_to_filter_pipeline(aslam, orc):
         assert d.min() < 0.08
     lm.close()
     e.close()
+
+
+@pytest.mark.gpu
+def test_synthetic_scan_kernel_matches_numpy_generator(aslam):
+    """the CUDA scan generator (one thread per ray, ray-cylinder intersection) against the numpy
+    generator on the same poses and the same noise array: identical hit pattern, ranges equal to one float ulp."""
+    lmx, lmy = aslam.map_cfg3()
+    B = 256
+    poses = aslam.laser_poses(B, seed=9, **aslam.replay.LASER_POSES_CFG3)
+    noise = np.random.default_rng(10).standard_normal((B, 360)).astype(np.float32)
+    ref = aslam.laser_scans(lmx, lmy, poses, noise=noise)
+    lm = aslam.LandMarks(max_scans=B)
+    got = lm.synthesize(lmx, lmy, poses, noise=noise)
+    assert np.array_equal(np.isfinite(got), np.isfinite(ref)) and np.isfinite(ref).sum() > 50 * B
+    f = np.isfinite(ref)
+    assert np.max(np.abs(got[f] - ref[f]) / ref[f]) <= 1.2e-7
+    # and the scans it makes are good scans: the front end finds the cylinders in range
+    rg, bg, cnt = lm.callback(got)
+    assert np.all(cnt >= 3)
+    lm.close()

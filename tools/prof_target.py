@@ -57,7 +57,7 @@ def ukf_large(side):
 
 def laser(B):
     lmx, lmy = A.map_cfg3()
-    base = A.laser_scans(lmx, lmy, A.laser_poses(4096, seed=77), seed=78)
+    base = A.laser_scans(lmx, lmy, A.laser_poses(4096, seed=77, **A.replay.LASER_POSES_CFG3), seed=78)
     sc = np.tile(base, (max(B // 4096, 1), 1))
     lm = A.LandMarks(max_scans=sc.shape[0])
     for _ in range(3):
