@@ -72,6 +72,9 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
         A((void**)&h->hp, (size_t)n * 132 * sizeof(double));
         A((void**)&h->K, (size_t)132 * n * sizeof(double));
     }
+    if (rc == ASLAM_OK && !cuda_ok(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(&h->ev_ctx_free, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
     if (rc == ASLAM_OK && !cuda_ok(cudaEventCreate(&h->ev0), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
     if (rc == ASLAM_OK && !cuda_ok(cudaEventCreate(&h->ev1), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
     if (rc == ASLAM_OK) {
@@ -92,15 +95,22 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
     return ASLAM_OK;
 }
 
+// EKF handles stage the observations on the side stream (the front kernel that reads them runs there), behind the
+// event that says the previous step no longer needs the context / observation buffers.
 aslam_status stage_obs(aslam_large* h, const float* range, const float* bearing, uint32_t m) {
+    cudaStream_t st = h->stream;
+    if (h->kind == ASLAM_KIND_EKF) {
+        st = h->side;
+        ASLAM_CUDA(cudaStreamWaitEvent(st, h->ev_ctx_free, 0));
+    }
     if (m > ASLAM_MAX_OBS) {
         set_error("large step: more than ASLAM_MAX_OBS observations in one message");
         return ASLAM_ERR_ARG;
     }
     if (m && (!range || !bearing)) return ASLAM_ERR_ARG;
     if (m) {
-        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs, range, m * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs + ASLAM_MAX_OBS, bearing, m * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs, range, m * sizeof(float), cudaMemcpyHostToDevice, st));
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs + ASLAM_MAX_OBS, bearing, m * sizeof(float), cudaMemcpyHostToDevice, st));
     }
     h->m_last = m;
     return ASLAM_OK;
@@ -130,8 +140,12 @@ aslam_status aslam_large_ukf_create(const aslam_config* cfg, uint32_t n, int32_t
 aslam_status aslam_large_destroy(aslam_large* h) {
     if (!h) return ASLAM_OK;
     cudaSetDevice(h->device);
+    if (h->side) cudaStreamSynchronize(h->side);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ukf) large_ukf_destroy(h);
+    if (h->ev_ctx_free) cudaEventDestroy(h->ev_ctx_free);
+    if (h->ev_front) cudaEventDestroy(h->ev_front);
+    if (h->side) cudaStreamDestroy(h->side);
     for (int p = 0; p < LARGE_MAX_PEERS; ++p)
         if (h->peer_ipc[p] && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
     void* ptrs[] = {h->P, h->X, h->A, h->ctx, h->d_obs, h->exch, h->hp, h->K, h->peer_block};

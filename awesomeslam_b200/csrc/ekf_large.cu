@@ -1013,7 +1013,12 @@ aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, dou
     a.kr_pose = (double)h->cfg.ekf_kr;
     a.kr_lm = (double)h->cfg.ukf_kr;  // ekf.cpp:278 (UKF constant, as written)
     const uint32_t n = h->n, nb = (n + 255) / 256;
-    large_front_kernel<<<1, 1024, 0, h->stream>>>(a, n, h->X, h->A, h->d_obs, h->ctx);
+    // front on the side stream (stage_obs already made it wait for ev_ctx_free): it overlaps the previous step's
+    // streaming update; predict / gather need both the front's context and the updated P
+    ASLAM_CUDA(cudaStreamWaitEvent(h->side, h->ev_ctx_free, 0));
+    large_front_kernel<<<1, 1024, 0, h->side>>>(a, n, h->X, h->A, h->d_obs, h->ctx);
+    ASLAM_CUDA(cudaEventRecord(h->ev_front, h->side));
+    ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_front, 0));
     large_predict_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A,
                                                     (double)h->cfg.ekf_kq);
     if (peer) {
@@ -1073,6 +1078,8 @@ aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
     else
         large_gain_kernel<<<nb, 256, smem, h->stream>>>(n, h->ctx, q_ub, h->exch, QT, h->hp, h->K, h->X);
     const uint32_t nrows = h->row_end - h->row_begin;
+    // X and the context are final for this step once the gain kernel is done (the fast update kernels read neither)
+    if (QT == 20 || QT == 40) ASLAM_CUDA(cudaEventRecord(h->ev_ctx_free, h->stream));
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
     if (QT == 20 || QT == 40) {
         int sms = 148;
@@ -1136,6 +1143,7 @@ aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
         dim3 grid((nrows + 255) / 256, (n + 31) / 32);
         large_update_generic_kernel<<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp, QT,
                                                                h->ctx);
+        ASLAM_CUDA(cudaEventRecord(h->ev_ctx_free, h->stream));  // this kernel reads the context
     }
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, h->stream));
     ASLAM_CUDA(cudaGetLastError());

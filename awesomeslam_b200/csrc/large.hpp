@@ -56,6 +56,10 @@ struct aslam_large {
     uint32_t m_last = 0;
     uint64_t launches = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the streaming update kernel of the last step
+    // EKF: the front kernel of step k+1 (association, pose predict, H rows; it needs X and the context, not P) runs
+    // on `side` behind ev_ctx_free, so it overlaps the streaming update of step k; the main stream joins at ev_front
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_ctx_free = nullptr, ev_front = nullptr;
     bool timed = false;
     // fused peer exchange: block = [E parity 0][E parity 1][LARGE_MAX_PEERS arrival counters]
     unsigned char* peer_block = nullptr;        // own block (cudaMalloc)
