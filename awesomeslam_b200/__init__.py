@@ -5,6 +5,7 @@ the C ABI of include/aslam_c.h). Importing this package does not need a GPU; cre
 does, and there is no CPU fallback.
 """
 from . import capi  # noqa: F401
+from . import export  # noqa: F401
 from .filters import BatchedFilter, EKFSlam, UKFSlam, Odometry, LargeFilter, LandMarks  # noqa: F401
 from .replay import (Replay, load_landmarks_yaml, map_cfg1, map_cfg3, large_map_state, dense_P,  # noqa: F401
                      large_observations, laser_scans, laser_poses)
