@@ -11,6 +11,18 @@
 
 namespace aslam {
 
+// 1 / x for a well-scaled positive x (the determinant of an innovation covariance): the hardware seed
+// (MUFU.RCP64H, about 20 bits) and two Newton steps -- full double precision to the last bit or two, without the
+// special-case path of the IEEE division. Only used where the result feeds FP64 arithmetic under the 1e-9 contract,
+// never at one of the reference's float cast sites.
+__device__ __forceinline__ double fast_rcp(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    r = fma(fma(-x, r, 1.0), r, r);
+    r = fma(fma(-x, r, 1.0), r, r);
+    return r;
+}
+
 // tools.h:44-50 normalizeAngle: float in, float out, fmodf (exact on the device), 2*PI is a
 // float product.
 __device__ __forceinline__ float normalize_angle(float theta, float pi) {

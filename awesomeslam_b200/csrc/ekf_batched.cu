@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
             const double c01 = S[1][2] * S[2][0] - S[1][0] * S[2][2];
             const double c02 = S[1][0] * S[2][1] - S[1][1] * S[2][0];
             const double det = S[0][0] * c00 + S[0][1] * c01 + S[0][2] * c02;
-            const double id = 1.0 / det;
+            const double id = fast_rcp(det);
             double Si[3][3];
             Si[0][0] = c00 * id;
             Si[1][0] = c01 * id;
@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                 const double S01 = fma(hb, w0.x - wa.x, fma(hd, w1.x - wb.x, -w2.x));
                 const double S10 = fma(ha, w0.y - wa.y, hc * (w1.y - wb.y));
                 const double S11 = fma(hb, w0.y - wa.y, fma(hd, w1.y - wb.y, -w2.y)) + kp.kr_lm;
-                const double id = 1.0 / (S00 * S11 - S01 * S10);
+                const double id = fast_rcp(S00 * S11 - S01 * S10);
                 const double i00 = S11 * id, i01 = -S01 * id, i10 = -S10 * id, i11 = S00 * id;
                 // innovation against the running state: y = Y0_g - H_g dx
                 const double d0 = s.dl[buf][0], d1 = s.dl[buf][1], d2 = s.dl[buf][2];
