@@ -228,12 +228,7 @@ bool make_map(CUtensorMap* m, const double* base, int rows, int K, size_t ld, in
 template <int BM, int BN, int WARPS_M, int WARPS_N>
 aslam_status launch(cudaStream_t st, const double* A, size_t lda, const double* B, size_t ldb, const GemmParams& p) {
     using G = Geo<BM, BN, WARPS_M, WARPS_N>;
-    static bool attr = false;
-    if (!attr) {
-        ASLAM_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
-        attr = true;
-    }
+    ASLAM_DYN_SMEM((dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N>), G::SMEM);
     CUtensorMap ta, tb;
     if (!make_map(&ta, A, p.M, p.K, lda, BM) || !make_map(&tb, B, p.N, p.K, ldb, BN)) return ASLAM_ERR_CUDA;
     dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);

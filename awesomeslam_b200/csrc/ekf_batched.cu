@@ -397,12 +397,7 @@ template <int NP, int CPT>
 aslam_status launch_t(const EkfParams& kp, cudaStream_t stream) {
     using G = Geo<NP, CPT>;
     const size_t smem = sizeof(EkfSlot<NP>) * G::FPB;
-    static bool attr_set = false;
-    if (!attr_set) {
-        ASLAM_CUDA(cudaFuncSetAttribute(ekf_batched_kernel<NP, CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)smem));
-        attr_set = true;
-    }
+    ASLAM_DYN_SMEM((ekf_batched_kernel<NP, CPT>), smem);
     const uint32_t grid = (kp.st.batch + G::FPB - 1) / G::FPB;
     ekf_batched_kernel<NP, CPT><<<grid, G::THREADS, smem, stream>>>(kp);
     ASLAM_CUDA(cudaGetLastError());

@@ -410,11 +410,7 @@ __global__ void __launch_bounds__(WPB * 32, 3) ekf_batched_mma_kernel(const EkfP
 
 aslam_status launch_ekf_batched_mma36(const EkfParams& kp, cudaStream_t stream) {
     const size_t smem = sizeof(MmaSlot) * WPB;
-    static bool attr_set = false;
-    if (!attr_set) {
-        ASLAM_CUDA(cudaFuncSetAttribute(ekf_batched_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
+    ASLAM_DYN_SMEM(ekf_batched_mma_kernel, smem);
     const uint32_t grid = (kp.st.batch + WPB - 1) / WPB;
     ekf_batched_mma_kernel<<<grid, WPB * 32, smem, stream>>>(kp);
     ASLAM_CUDA(cudaGetLastError());

@@ -1053,11 +1053,8 @@ aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
     const uint32_t n = h->n, nb = (n + 255) / 256, q_ub = h->q_host;
     const uint32_t QT = large_ekf_qt(q_ub);
     const size_t smem = (size_t)q_ub * q_ub * sizeof(double);
-    static size_t smem_set = 0;
-    if (smem > 48 * 1024 && smem > smem_set) {
-        ASLAM_CUDA(cudaFuncSetAttribute(large_gain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
-    }
+    // generic gain kernel: the opt-in is sized for the largest q it can be asked for, once per device
+    if (smem > 48 * 1024) ASLAM_DYN_SMEM(large_gain_kernel, (size_t)LARGE_QMAX * LARGE_QMAX * sizeof(double));
     if (peer) {
         const PeerSet ps = peer_set(h, h->peer_epoch);
         const double* E = ps.E[h->peer_rank];
@@ -1110,32 +1107,17 @@ aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
         } else if (QT == 20 && !(variant && variant[0] == 'b')) {  // default; ASLAM_LARGE_UPDATE=bulk: the one-barrier kernel
             using G = BulkGeo<2, 20, 8, 5>;
             constexpr size_t WS_SMEM = G::SMEM + 5 * sizeof(uint64_t);
-            static bool set = false;
-            if (!set) {
-                ASLAM_CUDA(cudaFuncSetAttribute(large_update_ws_kernel<2, 20, 8, 5>,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WS_SMEM));
-                set = true;
-            }
+            ASLAM_DYN_SMEM((large_update_ws_kernel<2, 20, 8, 5>), WS_SMEM);
             large_update_ws_kernel<2, 20, 8, 5><<<grid, 288, WS_SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
                                                                                   h->K, h->hp, cols_per_cta);
         } else if (QT == 20) {
             using G = BulkGeo<2, 20, 8, 5>;
-            static bool set = false;
-            if (!set) {
-                ASLAM_CUDA(cudaFuncSetAttribute(large_update_bulk_kernel<2, 20, 8, 5>,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
-                set = true;
-            }
+            ASLAM_DYN_SMEM((large_update_bulk_kernel<2, 20, 8, 5>), G::SMEM);
             large_update_bulk_kernel<2, 20, 8, 5><<<grid, 256, G::SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
                                                                                     h->K, h->hp, cols_per_cta);
         } else {
             using G = BulkGeo<1, 40, 16, 5>;
-            static bool set = false;
-            if (!set) {
-                ASLAM_CUDA(cudaFuncSetAttribute(large_update_bulk_kernel<1, 40, 16, 5>,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM));
-                set = true;
-            }
+            ASLAM_DYN_SMEM((large_update_bulk_kernel<1, 40, 16, 5>), G::SMEM);
             large_update_bulk_kernel<1, 40, 16, 5><<<grid, 256, G::SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
                                                                                      h->K, h->hp, cols_per_cta);
         }

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <string>
 
 #include "../../include/aslam_c.h"
@@ -14,6 +15,28 @@ bool cuda_ok(cudaError_t e, const char* what);
 #define ASLAM_CUDA(call)                                  \
     do {                                                  \
         if (!::aslam::cuda_ok((call), #call)) return ASLAM_ERR_CUDA; \
+    } while (0)
+
+// cudaFuncSetAttribute applies to the current device only: a process-wide "already set" flag would leave the second
+// device of a process that holds handles on several GPUs without the shared-memory opt-in. One bit per device.
+struct PerDeviceOnce {
+    std::atomic<uint64_t> done{0};
+    bool pending(int* dev) {
+        if (cudaGetDevice(dev) != cudaSuccess || *dev < 0 || *dev >= 64) return true;
+        return ((done.load(std::memory_order_acquire) >> *dev) & 1ull) == 0;
+    }
+    void mark(int dev) {
+        if (dev >= 0 && dev < 64) done.fetch_or(1ull << dev, std::memory_order_release);
+    }
+};
+#define ASLAM_DYN_SMEM(kernel, bytes)                                                                              \
+    do {                                                                                                           \
+        static ::aslam::PerDeviceOnce once_;                                                                       \
+        int dev_ = -1;                                                                                             \
+        if (once_.pending(&dev_)) {                                                                                \
+            ASLAM_CUDA(cudaFuncSetAttribute((kernel), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            once_.mark(dev_);                                                                                      \
+        }                                                                                                          \
     } while (0)
 
 // Device-resident state of a batch of filters. Layout in HBM (ld = padded state dim NP):

@@ -401,11 +401,7 @@ aslam_status launch_ukf_batched(const aslam_config& cfg, const BatchState& st, c
     kp.std_a = cfg.ukf_std_a;
     kp.std_yaw = cfg.ukf_std_yaw;
     const size_t smem = sizeof(UkfSlot);
-    static bool attr_set = false;
-    if (!attr_set) {
-        ASLAM_CUDA(cudaFuncSetAttribute(ukf_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
+    ASLAM_DYN_SMEM(ukf_batched_kernel, smem);
     ukf_batched_kernel<<<st.batch, UTHREADS, smem, stream>>>(kp);
     ASLAM_CUDA(cudaGetLastError());
     return ASLAM_OK;

@@ -175,6 +175,27 @@ def test_batched_split_launch_equals_one_launch(aslam):
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("kind", ["ekf", "ukf"])
+def test_handles_on_two_devices_of_one_process(aslam, kind):
+    """One process holding handles on cuda:0 and cuda:1 (the shared-memory opt-in of a kernel is per device): the
+    same replay gives bit-identical state on both. Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    lmx, lmy = aslam.map_cfg1()  # 8 landmarks: inside the reference's cap of 30 for both kinds
+    B, T, L = 48, 20, 8
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=21)
+    out = []
+    for dev in (0, 1):
+        f = aslam.BatchedFilter(kind, B, dev, max_state_dim=36 if kind == "ekf" else 30)  # UKF: the reference's cap
+        f.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+        out.append(f.get_state())
+        f.close()
+    assert np.array_equal(out[0]["X"], out[1]["X"], equal_nan=True)
+    assert np.array_equal(out[0]["P"], out[1]["P"], equal_nan=True)
+    assert np.array_equal(out[0]["N"], out[1]["N"]) and int(out[0]["N"].max()) == 19
+
+
 def test_pipelined_host_path_equals_one_launch(aslam):
     """run_host without a sync in between (double-buffered staging, copy stream) plus the pipelined
     read_state_async / read_wait: every intermediate X equals the one a synchronous replay of the same
