@@ -147,7 +147,7 @@ def reference_arm(args):
     import awesomeslam_b200 as A
     from oracle import oracle as O
     O.build()
-    sample = 256
+    sample = 256 if (os.cpu_count() or 1) < 16 else 2048
     lmx, lmy = A.map_cfg3()
     total_msgs = WARM_MSGS + (args.warmup + args.steps) * FUSE
     rp = A.Replay(lmx, lmy, sample, total_msgs, seed0=A.replay.SEED_CFG3)
@@ -392,6 +392,55 @@ def _ncu_traffic():
         return None
 
 
+def large_cpu_leg(steps=10):
+    """cfg4 on the host cores: the oracle's row-subset joint update (the same formula the kernels run), full size,
+    OpenMP over the columns of P. Returns the cpu_baseline object of the large_map leg."""
+    import time
+    import awesomeslam_b200 as A
+    from oracle import oracle as O
+    O.build()
+    tx, ty, X0, G, d = A.large_map_state(64)
+    P = A.dense_P(G, d)
+    X = X0.copy()
+    rng, brg, idx = A.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8)
+    cfg = O.default_config(max_state_dim=1 << 20)
+    a00, a10 = 1.0, 0.0
+    sec = []
+    for it in range(steps + 1):
+        t0 = time.perf_counter()
+        q, assoc, a00, a10 = O.ekf_large_step(cfg, X, P, a00, a10, 0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg, 0)
+        sec.append(time.perf_counter() - t0)
+    assert q == 19 and np.all(np.isfinite(X))
+    t = float(np.mean(sec[1:]))
+    return {"value": 1.0 / t, "unit": "steps/s", "cores": O.num_threads(), "kind": "port",
+            "sample": "%d full-size steps (n=8195, q=19) after one warm-up step, %.2f s each" % (steps, t)}
+
+
+def ukf_large_cpu_leg():
+    """cfg5 on one host core: the oracle's verbatim UKFSlam::slam. A full-size step takes minutes (280 s measured in
+    the build container), so the bounded sample is ONE step at n = 515 (256 landmarks, same recipe), scaled by n^3 --
+    an extrapolation that favours the CPU (at full size the rank-1 sweeps no longer fit the caches)."""
+    import time
+    import awesomeslam_b200 as A
+    from oracle import oracle as O, np_restatement as R
+    O.build()
+    side = 16
+    tx, ty, X0, G, d = A.large_map_state(side, pitch=100.0 / side)
+    P0 = A.dense_P(G, d)
+    rng, brg, idx = A.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8)
+    o = O.Filter("ukf", max_state_dim=100000)
+    o.load_state(X0, R.measurement(X0.size, X0), P0)
+    o.set_observations(rng, brg)
+    t0 = time.perf_counter()
+    o.step(0.01, -0.01, 0.002, 0.05, 0.1, 1.0)
+    t = time.perf_counter() - t0
+    assert o.llt_fail() == -1
+    scale = (2051.0 / X0.size) ** 3
+    return {"value": 1.0 / (t * scale), "unit": "steps/s", "cores": 1, "kind": "port",
+            "sample": "one step at n=%d (%.2f s) x (2051/%d)^3 = %.0f s per full-size step (extrapolated)"
+                      % (X0.size, t, X0.size, t * scale)}
+
+
 def ukf_large_leg(args, torch, dev):
     """cfg5: large-map UKF, n = 2051 (1024 landmarks, 4107 sigma points), one message from the supplied positive
     definite state per step (a second consecutive message of the reference UKF already finds P indefinite, SURVEY 3.2:
@@ -537,6 +586,10 @@ def main():
     ukf_large = None
     if rank == 0 and not args.no_large:
         ukf_large = ukf_large_leg(args, torch, dev)
+        if not args.no_cpu:
+            ukf_large["cpu_baseline"] = ukf_large_cpu_leg()
+            if large is not None and world == 1:
+                large["cpu_baseline"] = large_cpu_leg()
     laser = None
     if rank == 0 and not args.no_large:
         laser = laser_leg(args, torch, dev)
@@ -580,9 +633,11 @@ def main():
     if laser is not None:
         line["laser_front"] = laser
     if not args.no_cpu:
-        ups, nthr, sec = cpu_leg(256 if (os.cpu_count() or 1) < 16 else 1024, 120)
+        cpu_filters, cpu_msgs = (1024 if (os.cpu_count() or 1) < 16 else 4096), 240
+        ups, nthr, sec = cpu_leg(cpu_filters, cpu_msgs)
         line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": nthr, "kind": "port",
-                                "sample": "cfg3 filters x 120 messages from reset, OpenMP over filters, %.1f s" % sec}
+                                "sample": "%d of the 65,536 cfg3 filters x %d messages from reset, OpenMP over filters, "
+                                          "%.1f s" % (cpu_filters, cpu_msgs, sec)}
         line["speedup_e2e_vs_cpu"] = e2e / ups
     _emit(line)
     if world > 1:

@@ -1,0 +1,30 @@
+#!/bin/bash
+# One-GPU evidence run for profiles/: tests, smoke, the bench lines (never under a profiler), then the ncu passes of
+# B200_PROFILING.md (launch list + one --set full capture per top kernel). Usage on the GPU box:
+#   bash tools/evidence.sh TAG        -> gpurun_out/TAG_*
+# Each ncu pass runs only after the same command exited 0 without ncu.
+set -u
+T=${1:-ev}
+O=gpurun_out
+mkdir -p $O
+NCU="ncu --set full --clock-control none --import-source on"
+
+timeout 900 python -m pytest tests -m gpu -q > $O/${T}_tests.log 2>&1; echo "tests rc=$?" | tee -a $O/${T}_tests.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/${T}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/${T}_smoke.log
+timeout 900 python bench.py > $O/${T}_bench.json 2> $O/${T}_bench.err; echo "bench rc=$?"
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/${T}_ref.json 2> $O/${T}_ref.err; echo "ref rc=$?"
+
+if timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu > /dev/null 2> $O/${T}_pre.err; then
+  timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/${T}_launches.csv \
+    python bench.py --steps 3 --warmup 3 --no-cpu > $O/${T}_ncu.log 2>&1; echo "launch list rc=$?"
+fi
+if timeout 300 python tools/prof_target.py large 64 8 > /dev/null 2>&1; then
+  timeout 900 $NCU -k regex:large_update -c 3 -o $O/${T}_large -f python tools/prof_target.py large 64 8 > $O/${T}_ncu_large.log 2>&1; echo "large rc=$?"
+fi
+if timeout 300 python tools/prof_target.py batched 65536 8 > /dev/null 2>&1; then
+  timeout 900 $NCU -k regex:ekf_batched -s 1 -c 2 -o $O/${T}_batched -f python tools/prof_target.py batched 65536 8 > $O/${T}_ncu_b.log 2>&1; echo "batched rc=$?"
+fi
+if timeout 300 python tools/prof_target.py laser 65536 > /dev/null 2>&1; then
+  timeout 900 $NCU -k regex:laser_extract -s 1 -c 2 -o $O/${T}_laser -f python tools/prof_target.py laser 65536 > $O/${T}_ncu_laser.log 2>&1; echo "laser rc=$?"
+fi
+ls -la $O | grep ${T}_
