@@ -532,101 +532,107 @@ __global__ void __launch_bounds__(256) large_gain_fast_kernel(uint32_t n, LargeC
         S[idx] = sum + (a == b ? s_rdiag[a] : 0.0);
     }
     __syncthreads();
-    if (tid < 32) {  // in-place Gauss-Jordan with partial pivoting, one warp, lane = row (+32)
-        const int lane = tid;
-        for (int k = 0; k < q; ++k) {
-            double best = -1.0;
-            int p = k;
-            for (int i = k + lane; i < q; i += 32) {
-                const double v = fabs(S[i * QT + k]);
-                if (v > best) {
-                    best = v;
-                    p = i;
-                }
-            }
-            for (int off = 16; off; off >>= 1) {
-                const double ob = __shfl_xor_sync(0xffffffffu, best, off);
-                const int op = __shfl_xor_sync(0xffffffffu, p, off);
-                if (ob > best || (ob == best && op < p)) {
-                    best = ob;
-                    p = op;
-                }
-            }
-            if (lane == 0) piv[k] = p;
-            if (p != k)
-                for (int j = lane; j < q; j += 32) {
-                    const double t = S[k * QT + j];
-                    S[k * QT + j] = S[p * QT + j];
-                    S[p * QT + j] = t;
-                }
-            __syncwarp();
-            const double d = 1.0 / S[k * QT + k];
-            __syncwarp();
-            for (int j = lane; j < q; j += 32) S[k * QT + j] = (j == k ? 1.0 : S[k * QT + j]) * d;
-            __syncwarp();
-            for (int i = lane; i < q; i += 32) {
-                if (i == k) continue;
-                const double f = S[i * QT + k];
-                for (int j = 0; j < q; ++j)
-                    if (j != k) S[i * QT + j] = fma(-f, S[k * QT + j], S[i * QT + j]);
-                S[i * QT + k] = -f * S[k * QT + k];
-            }
-            __syncwarp();
+    // Column t of the exchange buffer and of H_o P: independent of S^-1, so the loads are in flight (and H_o P is
+    // stored) while the inversion below runs.
+    const uint32_t t = blockIdx.x * 256 + tid;
+    const bool valid = t < n;
+    const uint32_t tc = valid ? t : n - 1;
+    double pht[QT];
+    {
+        double raw[QT];
+#pragma unroll
+        for (int k = 0; k < QT; ++k) {
+            raw[k] = k < q ? ld_exch<PEER>(E + (size_t)k * n + tc) : 0.0;
+            pht[k] = k < q ? ld_exch<PEER>(E + (size_t)(q_ub + k) * n + tc) : 0.0;
         }
+        double hpv[QT];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) hpv[k] = s_hval[k][0] * raw[k];
+#pragma unroll
+        for (int c = 0; c < (QT - 3) / 2; ++c) {
+            const int kr = 3 + 2 * c, kb = kr + 1;
+            // same summation order as the generic kernel: entries e = 0.. of the row, left to right
+            double sr = 0.0, sb = 0.0;
+            sr += s_hval[kr][0] * raw[0];
+            sr += s_hval[kr][1] * raw[1];
+            sr += s_hval[kr][2] * raw[kr];
+            sr += s_hval[kr][3] * raw[kb];
+            sb += s_hval[kb][0] * raw[0];
+            sb += s_hval[kb][1] * raw[1];
+            sb += s_hval[kb][2] * raw[2];
+            sb += s_hval[kb][3] * raw[kr];
+            sb += s_hval[kb][4] * raw[kb];
+            hpv[kr] = sr;
+            hpv[kb] = sb;
+        }
+        if ((QT - 3) % 2) hpv[QT - 1] = 0.0;
+        if (valid) {
+            double* hpo = hp + (size_t)t * QT;
+#pragma unroll
+            for (int k = 0; k < QT; k += 2) *reinterpret_cast<double2*>(hpo + k) = make_double2(hpv[k], hpv[k + 1]);
+        }
+    }
+    // Gauss-Jordan inversion with partial pivoting (what `S.inverse()` of ekf.cpp:301 does through PartialPivLU, as
+    // one in-place sweep), the whole CTA on it: every thread finds the pivot of column k itself (broadcast reads, no
+    // shuffle chain), the eliminated matrix goes to the other buffer (no read/write hazard), ONE barrier per pivot.
+    // The arithmetic per element is the one-warp version's, so the result is bit-identical to it.
+    double* cur = S;
+    double* nxt = T;
+    for (int k = 0; k < q; ++k) {
+        double best = -1.0;
+        int p = k;
+        for (int i = k; i < q; ++i) {
+            const double v = fabs(cur[i * QT + k]);
+            if (v > best) {  // first maximum
+                best = v;
+                p = i;
+            }
+        }
+        if (tid == 0) piv[k] = p;
+        const double d = 1.0 / cur[p * QT + k];
+        for (int idx = tid; idx < QT * QT; idx += 256) {
+            const int i = idx / QT, j = idx % QT;
+            double out = cur[idx];
+            if (i < q && j < q) {
+                const double pkj = (j == k ? 1.0 : cur[p * QT + j]) * d;  // row k after the swap and the scaling
+                if (i == k) {
+                    out = pkj;
+                } else {
+                    const int r = i == p ? k : i;  // row p holds the old row k after the swap
+                    const double f = cur[r * QT + k];
+                    out = j == k ? -f * pkj : fma(-f, pkj, cur[r * QT + j]);
+                }
+            }
+            nxt[idx] = out;
+        }
+        __syncthreads();
+        double* sw = cur;
+        cur = nxt;
+        nxt = sw;
+    }
+    // undo the row swaps on the columns (k = q-1 .. 0), composed into one column permutation
+    if (tid == 0) {
+        for (int c = 0; c < q; ++c) s_rows[c] = c;  // s_rows is free: Psub has been read
         for (int k = q - 1; k >= 0; --k) {
-            const int p = piv[k];
-            if (p != k)
-                for (int i = lane; i < q; i += 32) {
-                    const double t = S[i * QT + k];
-                    S[i * QT + k] = S[i * QT + p];
-                    S[i * QT + p] = t;
-                }
-            __syncwarp();
+            const int p = piv[k], a = s_rows[k];
+            s_rows[k] = s_rows[p];
+            s_rows[p] = a;
         }
-        // padding rows / columns of S^-1 must not contribute
-        for (int idx = lane; idx < QT * QT; idx += 32)
-            if (idx / QT >= q || idx % QT >= q) S[idx] = 0.0;
     }
     __syncthreads();
-    const uint32_t t = blockIdx.x * 256 + tid;
-    if (t >= n) return;
-    double raw[QT], pht[QT];
-#pragma unroll
-    for (int k = 0; k < QT; ++k) {
-        raw[k] = k < q ? ld_exch<PEER>(E + (size_t)k * n + t) : 0.0;
-        pht[k] = k < q ? ld_exch<PEER>(E + (size_t)(q_ub + k) * n + t) : 0.0;
+    for (int idx = tid; idx < QT * QT; idx += 256) {
+        const int i = idx / QT, c = idx % QT;
+        nxt[idx] = (i < q && c < q) ? cur[i * QT + s_rows[c]] : 0.0;  // padding must not contribute
     }
-    // H_o P column t
-    double hpv[QT];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) hpv[k] = s_hval[k][0] * raw[k];
-#pragma unroll
-    for (int c = 0; c < (QT - 3) / 2; ++c) {
-        const int kr = 3 + 2 * c, kb = kr + 1;
-        // same summation order as the generic kernel: entries e = 0.. of the row, left to right
-        double sr = 0.0, sb = 0.0;
-        sr += s_hval[kr][0] * raw[0];
-        sr += s_hval[kr][1] * raw[1];
-        sr += s_hval[kr][2] * raw[kr];
-        sr += s_hval[kr][3] * raw[kb];
-        sb += s_hval[kb][0] * raw[0];
-        sb += s_hval[kb][1] * raw[1];
-        sb += s_hval[kb][2] * raw[2];
-        sb += s_hval[kb][3] * raw[kr];
-        sb += s_hval[kb][4] * raw[kb];
-        hpv[kr] = sr;
-        hpv[kb] = sb;
-    }
-    if ((QT - 3) % 2) hpv[QT - 1] = 0.0;
-    double* hpo = hp + (size_t)t * QT;
-#pragma unroll
-    for (int k = 0; k < QT; k += 2) *reinterpret_cast<double2*>(hpo + k) = make_double2(hpv[k], hpv[k + 1]);
+    __syncthreads();
+    const double* Sinv = nxt;
+    if (!valid) return;
     double dx = 0.0;
 #pragma unroll
     for (int k = 0; k < QT; ++k) {  // K row t
         double sum = 0.0;
 #pragma unroll
-        for (int e = 0; e < QT; ++e) sum += pht[e] * S[e * QT + k];
+        for (int e = 0; e < QT; ++e) sum += pht[e] * Sinv[e * QT + k];
         dx += sum * s_y[k];
         K[(size_t)k * n + t] = sum;
     }
