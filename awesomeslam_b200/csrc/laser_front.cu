@@ -37,6 +37,19 @@ struct __align__(16) ScanSlot {
     int ncand;
 };
 
+// The points of one cluster, as the classification and the fit read them: from the scan's slot in shared memory, or
+// recomputed from the ranges in global memory (the same float product as bearing2pose, :136-142).
+struct SlotPoints {
+    const float *px, *py;
+    __device__ __forceinline__ float x(int i) const { return px[i]; }
+    __device__ __forceinline__ float y(int i) const { return py[i]; }
+};
+struct RangePoints {
+    const float *r, *c, *s;
+    __device__ __forceinline__ float x(int i) const { return __fmul_rn(__ldg(r + i), __ldg(c + i)); }
+    __device__ __forceinline__ float y(int i) const { return __fmul_rn(__ldg(r + i), __ldg(s + i)); }
+};
+
 // cyclic Jacobi, symmetric 4 x 4: A = V diag(w) V'
 __device__ __forceinline__ void jacobi4(double (&A)[4][4], double (&V)[4][4]) {
 #pragma unroll
@@ -91,14 +104,15 @@ __device__ __forceinline__ void jacobi4(double (&A)[4][4], double (&V)[4][4]) {
     }
 }
 
-// sensor_landmark.cpp:147-186 on points [s0, s0 + n) of the scan
-__device__ __forceinline__ bool classify(const ScanSlot& s, const LaserParams& lp, int s0, int n) {
-    const float x1 = s.px[s0], y1 = s.py[s0], x2 = s.px[s0 + n - 1], y2 = s.py[s0 + n - 1];
+// sensor_landmark.cpp:147-186 on the n points of one cluster
+template <typename PTS>
+__device__ __forceinline__ bool classify(const PTS& pts, const LaserParams& lp, int n) {
+    const float x1 = pts.x(0), y1 = pts.y(0), x2 = pts.x(n - 1), y2 = pts.y(n - 1);
     const float c = euler_distance(x1, y1, x2, y2);
     const float cc = __fmul_rn(c, c);
     float sum = 0.0f;
     for (int i = 1; i < n - 1; ++i) {
-        const float x = s.px[s0 + i], y = s.py[s0 + i];
+        const float x = pts.x(i), y = pts.y(i);
         const float a = euler_distance(x1, y1, x, y), b = euler_distance(x2, y2, x, y);
         const float num = __fsub_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), cc);
         const float den = __fmul_rn(__fmul_rn(2.0f, a), b);
@@ -109,7 +123,7 @@ __device__ __forceinline__ bool classify(const ScanSlot& s, const LaserParams& l
     const float mean = __fdiv_rn(sum, (float)(n - 2));
     float variance = 0.0f;
     for (int i = 1; i < n - 1; ++i) {  // the angles are recomputed instead of stored (same values)
-        const float x = s.px[s0 + i], y = s.py[s0 + i];
+        const float x = pts.x(i), y = pts.y(i);
         const float a = euler_distance(x1, y1, x, y), b = euler_distance(x2, y2, x, y);
         const float num = __fsub_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), cc);
         const float den = __fmul_rn(__fmul_rn(2.0f, a), b);
@@ -121,17 +135,18 @@ __device__ __forceinline__ bool classify(const ScanSlot& s, const LaserParams& l
     return sd < lp.std_max && mean > lp.min_mean && mean < lp.max_mean;
 }
 
-// sensor_landmark.cpp:192-298 (hyper-fit) + structures.h:126-133 on points [s0, s0 + n)
-__device__ __forceinline__ void fit(const ScanSlot& s, int s0, int n, float& out_range, float& out_bearing) {
+// sensor_landmark.cpp:192-298 (hyper-fit) + structures.h:126-133 on the n points of one cluster
+template <typename PTS>
+__device__ __forceinline__ void fit(const PTS& pts, int n, float& out_range, float& out_bearing) {
     float x_mean = 0.0f, y_mean = 0.0f, z_mean = 0.0f;
     for (int i = 0; i < n; ++i) {
-        x_mean = __fadd_rn(x_mean, s.px[s0 + i]);
-        y_mean = __fadd_rn(y_mean, s.py[s0 + i]);
+        x_mean = __fadd_rn(x_mean, pts.x(i));
+        y_mean = __fadd_rn(y_mean, pts.y(i));
     }
     x_mean = __fdiv_rn(x_mean, (float)n);
     y_mean = __fdiv_rn(y_mean, (float)n);
     for (int i = 0; i < n; ++i) {
-        const float x = __fsub_rn(s.px[s0 + i], x_mean), y = __fsub_rn(s.py[s0 + i], y_mean);
+        const float x = __fsub_rn(pts.x(i), x_mean), y = __fsub_rn(pts.y(i), y_mean);
         z_mean = __fadd_rn(z_mean, __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)));
     }
     z_mean = __fdiv_rn(z_mean, (float)n);
@@ -142,7 +157,7 @@ __device__ __forceinline__ void fit(const ScanSlot& s, int s0, int n, float& out
 #pragma unroll
         for (int b = 0; b < 4; ++b) G[a][b] = 0.0;
     for (int i = 0; i < n; ++i) {
-        const float x = __fsub_rn(s.px[s0 + i], x_mean), y = __fsub_rn(s.py[s0 + i], y_mean);
+        const float x = __fsub_rn(pts.x(i), x_mean), y = __fsub_rn(pts.y(i), y_mean);
         const float z = __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y));
         const double row[4] = {(double)z, (double)x, (double)y, 1.0};
 #pragma unroll
@@ -259,8 +274,8 @@ __device__ __forceinline__ void fit(const ScanSlot& s, int s0, int n, float& out
 __global__ void __launch_bounds__(LWPB * 32) laser_extract_kernel(const float* __restrict__ ranges, uint32_t nscan,
                                                                  const float* __restrict__ cos_map,
                                                                  const float* __restrict__ sin_map, LaserParams lp,
-                                                                 float* __restrict__ out_range,
-                                                                 float* __restrict__ out_bearing,
+                                                                 uint2* __restrict__ work,
+                                                                 uint32_t* __restrict__ work_count,
                                                                  int32_t* __restrict__ counts) {
     __shared__ ScanSlot slots[LWPB];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -306,26 +321,52 @@ __global__ void __launch_bounds__(LWPB * 32) laser_extract_kernel(const float* _
         if (lane == 0) s.ncand = nc < MAXC ? nc : MAXC;
     }
     __syncwarp();
+    // Classification: one lane per candidate. The accepted clusters keep their scan order (ballot + prefix count) and
+    // go, with the output slot they will fill, to a batch-wide dense work list; the fit runs in laser_fit_kernel.
     const int nc = s.ncand;
     int total = 0;
     for (int base = 0; base < nc; base += 32) {
         const int cnd = base + lane;
         bool ok = false;
-        float rg = 0.0f, bg = 0.0f;
+        int s0 = 0, n = 0;
         if (cnd < nc) {
-            const int s0 = s.cstart[cnd], n = s.clen[cnd];
-            ok = classify(s, lp, s0, n);
-            if (ok) fit(s, s0, n, rg, bg);
+            s0 = s.cstart[cnd];
+            n = s.clen[cnd];
+            ok = classify(SlotPoints{s.px + s0, s.py + s0}, lp, n);
         }
         const unsigned m = __ballot_sync(0xffffffffu, ok);
         const int slot = total + __popc(m & ((1u << lane) - 1u));
-        if (ok && slot < (int)ASLAM_LASER_MAX_LANDMARKS) {
-            out_range[(size_t)scan * ASLAM_LASER_MAX_LANDMARKS + slot] = rg;
-            out_bearing[(size_t)scan * ASLAM_LASER_MAX_LANDMARKS + slot] = bg;
+        const bool emit = ok && slot < (int)ASLAM_LASER_MAX_LANDMARKS;
+        const unsigned em = __ballot_sync(0xffffffffu, emit);
+        if (em) {
+            uint32_t wbase = 0;
+            if (lane == 0) wbase = atomicAdd(work_count, (uint32_t)__popc(em));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (emit)
+                work[wbase + __popc(em & ((1u << lane) - 1u))] =
+                    make_uint2(scan * ASLAM_LASER_MAX_LANDMARKS + (uint32_t)slot, (uint32_t)s0 | ((uint32_t)n << 16));
         }
         total += __popc(m);
     }
     if (lane == 0) counts[scan] = total;
+}
+
+// Circle fit of the accepted clusters, one thread per cluster of the whole batch (every lane busy; the order of the
+// work list does not matter: each entry names the output slot it fills).
+__global__ void __launch_bounds__(128) laser_fit_kernel(const float* __restrict__ ranges, const float* __restrict__ cos_map,
+                                                        const float* __restrict__ sin_map,
+                                                        const uint2* __restrict__ work,
+                                                        const uint32_t* __restrict__ work_count,
+                                                        float* __restrict__ out_range, float* __restrict__ out_bearing) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= *work_count) return;
+    const uint2 w = work[idx];
+    const uint32_t scan = w.x / ASLAM_LASER_MAX_LANDMARKS;
+    const int s0 = (int)(w.y & 0xffffu), n = (int)(w.y >> 16);
+    float rg, bg;
+    fit(RangePoints{ranges + (size_t)scan * RAYS + s0, cos_map + s0, sin_map + s0}, n, rg, bg);
+    out_range[w.x] = rg;
+    out_bearing[w.x] = bg;
 }
 
 // the Gazebo LDS model as arithmetic -- one thread per ray: ray k of a scan leaves the sensor at
@@ -374,6 +415,8 @@ struct aslam_laser {
     float* d_range_out = nullptr;
     float* d_bearing_out = nullptr;
     int32_t* d_counts = nullptr;
+    uint2* d_work = nullptr;          // accepted clusters of one batch: (output slot, start | length << 16)
+    uint32_t* d_work_count = nullptr;
     uint64_t launches = 0;
 };
 
@@ -427,6 +470,8 @@ aslam_status aslam_laser_create(const aslam_laser_config* cfg, uint32_t max_scan
     ok = ok && cuda_ok(cudaMalloc((void**)&h->d_range_out, ob), "cudaMalloc");
     ok = ok && cuda_ok(cudaMalloc((void**)&h->d_bearing_out, ob), "cudaMalloc");
     ok = ok && cuda_ok(cudaMalloc((void**)&h->d_counts, (size_t)max_scans * sizeof(int32_t)), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_work, (size_t)max_scans * ASLAM_LASER_MAX_LANDMARKS * sizeof(uint2)), "cudaMalloc");
+    ok = ok && cuda_ok(cudaMalloc((void**)&h->d_work_count, sizeof(uint32_t)), "cudaMalloc");
     ok = ok && cuda_ok(cudaMemcpy(h->d_cos, hc, sizeof(hc), cudaMemcpyHostToDevice), "tables");
     ok = ok && cuda_ok(cudaMemcpy(h->d_sin, hs, sizeof(hs), cudaMemcpyHostToDevice), "tables");
     if (!ok) {
@@ -441,7 +486,7 @@ aslam_status aslam_laser_destroy(aslam_laser* h) {
     if (!h) return ASLAM_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    void* ptrs[] = {h->d_cos, h->d_sin, h->d_ranges, h->d_range_out, h->d_bearing_out, h->d_counts};
+    void* ptrs[] = {h->d_cos, h->d_sin, h->d_ranges, h->d_range_out, h->d_bearing_out, h->d_counts, h->d_work, h->d_work_count};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -454,11 +499,20 @@ aslam_status aslam_laser_extract_device(aslam_laser* h, const float* d_ranges, u
     if (!h || !d_ranges || !d_range_out || !d_bearing_out || !d_counts) return ASLAM_ERR_ARG;
     if (nscan == 0) return ASLAM_OK;
     ASLAM_CUDA(cudaSetDevice(h->device));
-    const uint32_t grid = (nscan + LWPB - 1) / LWPB;
-    laser_extract_kernel<<<grid, LWPB * 32, 0, h->stream>>>(d_ranges, nscan, h->d_cos, h->d_sin, h->lp, d_range_out,
-                                                           d_bearing_out, d_counts);
-    ASLAM_CUDA(cudaGetLastError());
-    h->launches += 1;
+    // the work list holds the accepted clusters of at most max_scans scans: larger batches go in chunks
+    for (uint32_t first = 0; first < nscan; first += h->max_scans) {
+        const uint32_t cnt = nscan - first < h->max_scans ? nscan - first : h->max_scans;
+        const size_t o = (size_t)first * ASLAM_LASER_MAX_LANDMARKS;
+        ASLAM_CUDA(cudaMemsetAsync(h->d_work_count, 0, sizeof(uint32_t), h->stream));
+        laser_extract_kernel<<<(cnt + LWPB - 1) / LWPB, LWPB * 32, 0, h->stream>>>(
+            d_ranges + (size_t)first * RAYS, cnt, h->d_cos, h->d_sin, h->lp, h->d_work, h->d_work_count, d_counts + first);
+        // worst-case grid (every scan with a full list); CTAs beyond the work count return at once
+        const uint32_t fit_grid = (cnt * ASLAM_LASER_MAX_LANDMARKS + 127) / 128;
+        laser_fit_kernel<<<fit_grid, 128, 0, h->stream>>>(d_ranges + (size_t)first * RAYS, h->d_cos, h->d_sin, h->d_work,
+                                                         h->d_work_count, d_range_out + o, d_bearing_out + o);
+        ASLAM_CUDA(cudaGetLastError());
+        h->launches += 2;
+    }
     return ASLAM_OK;
 }
 
