@@ -252,13 +252,13 @@ __global__ void symmetrize_kernel(double* A, size_t ld, int n) {
 // of the trailing update keeps the other SMs busy on the caller's stream; the two meet again before L21 of k+1.
 aslam_status cholesky_lower(cudaStream_t st, double* A, size_t ld, int n, double* inv_blocks, int* d_fail,
                             uint64_t* launches) {
-    static thread_local cudaStream_t side = nullptr;
-    static thread_local cudaEvent_t ev_col = nullptr, ev_panel = nullptr;
-    if (!side) {
-        ASLAM_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-        ASLAM_CUDA(cudaEventCreateWithFlags(&ev_col, cudaEventDisableTiming));
-        ASLAM_CUDA(cudaEventCreateWithFlags(&ev_panel, cudaEventDisableTiming));
+    SideStream* ss = nullptr;  // per thread and device
+    {
+        const aslam_status rc = side_stream(0, &ss);
+        if (rc != ASLAM_OK) return rc;
     }
+    const cudaStream_t side = ss->s;
+    const cudaEvent_t ev_col = ss->fork, ev_panel = ss->join;
     chol_panel_kernel<<<1, 256, 0, st>>>(A, ld, n < BS ? n : BS, inv_blocks, d_fail, 0);
     ASLAM_CUDA(cudaGetLastError());
     if (launches) ++*launches;

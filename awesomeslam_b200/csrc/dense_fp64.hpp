@@ -50,6 +50,15 @@ aslam_status trsv_lower(cudaStream_t st, double* v, const double* L, size_t ldl,
 // A[j][i] <- A[i][j] for i > j.
 aslam_status symmetrize_from_lower(cudaStream_t st, double* A, size_t ld, int n, uint64_t* launches);
 
+// A side stream with a fork and a join event, owned by the calling thread, one per (slot, device): small kernels that
+// are independent of the caller's stream for a while (the Cholesky's lookahead panel, a GEMM's ragged-edge rows) run on
+// it. Created on first use for the CURRENT device. Slots: 0 the Cholesky, 1 dgemm_nt.
+struct SideStream {
+    cudaStream_t s = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+aslam_status side_stream(int slot, SideStream** out);
+
 // Measured throughput of the DMMA pipe of the current device, TFLOP/s (roofline denominator for the GEMMs).
 aslam_status probe_dmma_tflops(double* tflops);
 

@@ -296,6 +296,22 @@ __global__ void __launch_bounds__(256) dgemm_skinny_kernel(GemmParams p, const d
 
 }  // namespace
 
+aslam_status side_stream(int slot, SideStream** out) {
+    constexpr int MAXDEV = 64, SLOTS = 2;
+    static thread_local SideStream ctx[SLOTS][MAXDEV];
+    int dev = 0;
+    ASLAM_CUDA(cudaGetDevice(&dev));
+    if (slot < 0 || slot >= SLOTS || dev < 0 || dev >= MAXDEV) return ASLAM_ERR_ARG;
+    SideStream& c = ctx[slot][dev];
+    if (!c.s) {
+        ASLAM_CUDA(cudaStreamCreateWithFlags(&c.s, cudaStreamNonBlocking));
+        ASLAM_CUDA(cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming));
+        ASLAM_CUDA(cudaEventCreateWithFlags(&c.join, cudaEventDisableTiming));
+    }
+    *out = &c;
+    return ASLAM_OK;
+}
+
 aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, size_t lda, const double* B, size_t ldb,
                       double* C, size_t ldc, const Epilogue& e, uint64_t* launches) {
     if (M <= 0 || N <= 0 || K <= 0) return ASLAM_OK;
@@ -314,15 +330,15 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     if (!alias && M > 128 && M % 128 != 0 && M % 128 <= SKINNY_MAX) Mm = M - M % 128;
     if (!alias && N > 128 && N % 128 != 0 && N % 128 <= SKINNY_MAX) Nm = N - N % 128;
     if (e.lower_only && Nm > Mm) Nm = Mm;  // columns beyond the main rows only matter for the tail rows
-    if (Mm < M) {  // tail rows, all columns
-        dgemm_skinny_kernel<<<(N + 7) / 8, 256, 0, st>>>(p, A, lda, B, ldb, Mm, M, 0, N, 1);
-        ASLAM_CUDA(cudaGetLastError());
-        if (launches) ++*launches;
-    }
-    if (Nm < N && !e.lower_only) {  // tail columns, main rows
-        dgemm_skinny_kernel<<<(Mm + 7) / 8, 256, 0, st>>>(p, A, lda, B, ldb, 0, Mm, Nm, N, 0);
-        ASLAM_CUDA(cudaGetLastError());
-        if (launches) ++*launches;
+    // The ragged-edge kernels write rows / columns of C the tile kernel does not touch and are latency-bound (one warp
+    // walks all of K): they run on the side stream, under the tile kernel, and join before anything that follows.
+    const bool tail_rows = Mm < M, tail_cols = Nm < N && !e.lower_only;
+    SideStream* ss = nullptr;
+    if (tail_rows || tail_cols) {
+        const aslam_status rc = side_stream(1, &ss);
+        if (rc != ASLAM_OK) return rc;
+        ASLAM_CUDA(cudaEventRecord(ss->fork, st));
+        ASLAM_CUDA(cudaStreamWaitEvent(ss->s, ss->fork, 0));
     }
     p.M = Mm;
     p.N = Nm;
@@ -338,8 +354,25 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     }
     const long sms = 148;
     const double cost128 = 2.0 * (double)((t128 + sms - 1) / sms), cost64 = 1.08 * (double)((t64 + sms - 1) / sms);
-    if (Nm > 64 && cost128 <= cost64) return launch<128, 128, 4, 2>(st, A, lda, B, ldb, p);
-    return launch<128, 64, 4, 2>(st, A, lda, B, ldb, p);
+    const aslam_status rc = (Nm > 64 && cost128 <= cost64) ? launch<128, 128, 4, 2>(st, A, lda, B, ldb, p)
+                                                           : launch<128, 64, 4, 2>(st, A, lda, B, ldb, p);
+    if (rc != ASLAM_OK) return rc;
+    // the tile kernel goes to the GPU first (one CTA per SM); the ragged-edge CTAs then fit beside it
+    p.M = M;
+    p.N = N;
+    if (tail_rows) {  // tail rows, all columns
+        dgemm_skinny_kernel<<<(N + 7) / 8, 256, 0, ss->s>>>(p, A, lda, B, ldb, Mm, M, 0, N, 1);
+        ASLAM_CUDA(cudaGetLastError());
+        if (launches) ++*launches;
+    }
+    if (tail_cols) {  // tail columns, main rows
+        dgemm_skinny_kernel<<<(Mm + 7) / 8, 256, 0, ss->s>>>(p, A, lda, B, ldb, 0, Mm, Nm, N, 0);
+        ASLAM_CUDA(cudaGetLastError());
+        if (launches) ++*launches;
+    }
+    if (ss) ASLAM_CUDA(cudaEventRecord(ss->join, ss->s));
+    if (ss) ASLAM_CUDA(cudaStreamWaitEvent(st, ss->join, 0));
+    return ASLAM_OK;
 }
 
 // ---------------------------------------------------------------------------------- DMMA pipe probe
