@@ -25,6 +25,8 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <new>
 
 #include "dense_fp64.hpp"
@@ -468,6 +470,18 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     cudaStream_t st = h->stream;
     const int n = u->n;
     uint64_t& nl = h->launches;
+    // ASLAM_UKF_PHASES=1: CUDA-event time of every phase of the step, printed to stderr (diagnostic; synchronises)
+    static const bool phases = std::getenv("ASLAM_UKF_PHASES") != nullptr;
+    constexpr int MAXPH = 12;
+    cudaEvent_t pev[MAXPH];
+    const char* pname[MAXPH];
+    int nph = 0;
+    auto mark = [&](const char* name) {
+        if (!phases || nph >= MAXPH) return;
+        if (cudaEventCreate(&pev[nph]) != cudaSuccess) return;
+        cudaEventRecord(pev[nph], st);
+        pname[nph++] = name;
+    };
     // ---- updateZ
     UkfFrontArgs fa;
     fa.ox = x; fa.oy = y; fa.yaw = yaw; fa.m = m;
@@ -476,11 +490,13 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     ukf_front_kernel<<<1, 1024, 0, st>>>(fa, (uint32_t)n, h->X, u->Z, h->d_obs, h->ctx);
     ++nl;
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, st));
+    mark("start");
     // ---- L = Paug.llt().matrixL()
     ASLAM_CUDA(cudaMemsetAsync(u->fail, 0xff, 2 * sizeof(int), st));
     ASLAM_CUDA(cudaMemcpyAsync(u->Lb, h->P, (size_t)n * u->ld * sizeof(double), cudaMemcpyDeviceToDevice, st));
     aslam_status rc = dense::cholesky_lower(st, u->Lb, u->ld, n, u->invP, u->fail, &nl);
     if (rc != ASLAM_OK) return rc;
+    mark("chol(Paug)");
     // ---- sigma points, mean, differences
     SigmaArgs a;
     a.n = n; a.na = u->na; a.ns = u->ns; a.ld = u->ld; a.nsld = u->nsld;
@@ -497,6 +513,7 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     zdiff_kernel<<<n, 256, 0, st>>>(a, u->DZ, u->Z, u->zpred, u->dz0, u->dzv);
     ASLAM_CUDA(cudaGetLastError());
     nl += 5;
+    mark("sigma points");
     // ---- P = sum w d d' + Q;  S = sum w dz dz' + R;  Tc = sum w d dz'
     dense::Epilogue e;
     e.alpha = u->wc;
@@ -505,29 +522,35 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     e.u = u->d0; e.v = u->d0; e.diag = u->qdiag;
     rc = dense::dgemm_nt(st, n, n, u->ns, u->D, u->nsld, u->D, u->nsld, h->P, u->ld, e, &nl);
     if (rc != ASLAM_OK) return rc;
+    mark("P gemm");
     // M = wc DZ DZ' + R: the positive definite part of S (its rank-1 term c dz_0 dz_0' is applied analytically below)
     e.u = nullptr; e.v = nullptr; e.r1 = 0.0; e.diag = u->rdiag;
     rc = dense::dgemm_nt(st, n, n, u->ns, u->DZ, u->nsld, u->DZ, u->nsld, u->S, u->ld, e, &nl);
     if (rc != ASLAM_OK) return rc;
+    mark("M gemm");
     e.lower_only = false;
     e.r1 = u->w0 - u->wc;
     e.u = u->d0; e.v = u->dz0; e.diag = nullptr;
     rc = dense::dgemm_nt(st, n, n, u->ns, u->D, u->nsld, u->DZ, u->nsld, u->Tc, u->ld, e, &nl);
     if (rc != ASLAM_OK) return rc;
+    mark("Tc gemm");
     // ---- M = Lm Lm';  [W; a'; b'] = [Tc; dz_0'; dz'] Lm^-T  (a = Lm^-1 dz_0, b = Lm^-1 dz ride along as two extra rows)
     rc = dense::cholesky_lower(st, u->S, u->ld, n, u->invS, u->fail + 1, &nl);
     if (rc != ASLAM_OK) return rc;
+    mark("chol(M)");
     double* arow = u->Tc + (size_t)n * u->ld;
     double* brow = arow + u->ld;
     ASLAM_CUDA(cudaMemcpyAsync(arow, u->dz0, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     ASLAM_CUDA(cudaMemcpyAsync(brow, u->dzv, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     rc = dense::trsm_right_lower_t(st, u->Tc, u->ld, n + 2, u->S, u->ld, n, u->invS, &nl);
     if (rc != ASLAM_OK) return rc;
+    mark("trsm");
     sm_scalars_kernel<<<1, 256, 0, st>>>(n, arow, brow, u->w0 - u->wc, u->coef, u->status);
     state_update_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, u->ld, u->Tc, arow, brow, u->coef, u->mean, u->gvec, h->X,
                                                    u->status);
     ASLAM_CUDA(cudaGetLastError());
     nl += 2;
+    mark("state update");
     // ---- P = P_pred - W W' + (c/den) g g'
     dense::Epilogue d;
     d.alpha = -1.0;
@@ -542,6 +565,16 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     ASLAM_CUDA(cudaGetLastError());
     ++nl;
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, st));
+    mark("W W' + symmetrize");
+    if (nph > 1) {
+        cudaEventSynchronize(pev[nph - 1]);
+        for (int i = 1; i < nph; ++i) {
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, pev[i - 1], pev[i]);
+            std::fprintf(stderr, "ukf phase %-20s %8.3f ms\n", pname[i], ms);
+        }
+    }
+    for (int i = 0; i < nph; ++i) cudaEventDestroy(pev[i]);
     return ASLAM_OK;
 }
 
