@@ -36,6 +36,9 @@ struct Geo {
     static constexpr int FPB = (128 / TPF) > 0 ? (128 / TPF) : 1;
     static constexpr int THREADS = TPF * FPB;
     static constexpr int LMAX = (NP - 3) / 2;
+    // N <= max_state_dim - 1 <= NP - 1 (batched_padded_dim): row NP - 1 of every covariance is padding (zero), so the
+    // register tile holds NR = NP - 1 rows per column
+    static constexpr int NR = NP - 1;
     static_assert(NP % CPT == 0, "NP must be a multiple of CPT");
 };
 
@@ -57,6 +60,7 @@ template <int NP, int CPT>
 __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(const EkfParams kp) {
     using G = Geo<NP, CPT>;
     constexpr int TPF = G::TPF;
+    constexpr int NR = G::NR;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EkfSlot<NP>* slots = reinterpret_cast<EkfSlot<NP>*>(smem_raw);
     const int fs = threadIdx.x / TPF, ct = threadIdx.x % TPF;
@@ -66,11 +70,11 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
     const int j0 = ct * CPT;  // first owned column
     __shared__ int s_lcta;    // landmark blocks any filter of this CTA needs this step
 
-    double p[CPT][NP];
+    double p[CPT][NR];
     {
         const double* Pg = kp.st.P + (size_t)(live ? f : 0) * NP * NP;
 #pragma unroll
-        for (int i = 0; i < NP; ++i) {
+        for (int i = 0; i < NR; ++i) {
             if constexpr (CPT == 2) {
                 const double2 v = live ? *reinterpret_cast<const double2*>(Pg + i * NP + j0) : make_double2(0, 0);
                 p[0][i] = v.x;
@@ -168,7 +172,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                 const uint32_t j = j0 + c;
                 const double dj = (j >= g0 && j < N) ? kp.kp_lm : 0.0;
 #pragma unroll
-                for (int i = 0; i < NP; ++i) p[c][i] = fma((double)((uint32_t)i == j), dj, p[c][i]);
+                for (int i = 0; i < NR; ++i) p[c][i] = fma((double)((uint32_t)i == j), dj, p[c][i]);
             }
         }
         // ---- P = A P A' + Q (ekf.cpp:297); A = I except A(0,0), A(1,0)
@@ -182,7 +186,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
             }
             if (j0 == 0) {
 #pragma unroll
-                for (int i = 0; i < NP; ++i) s.V[0][i] = p[0][i];  // column 0 of A P
+                for (int i = 0; i < NR; ++i) s.V[0][i] = p[0][i];  // column 0 of A P
             }
         }
         __syncthreads();
@@ -193,10 +197,10 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                 const int j = j0 + c;
                 if (j == 0) {
 #pragma unroll
-                    for (int i = 0; i < NP; ++i) p[c][i] = p[c][i] * a00;
+                    for (int i = 0; i < NR; ++i) p[c][i] = p[c][i] * a00;
                 } else if (j == 1) {
 #pragma unroll
-                    for (int i = 0; i < NP; ++i) p[c][i] = s.V[0][i] * a10 + p[c][i];
+                    for (int i = 0; i < NR; ++i) p[c][i] = s.V[0][i] * a10 + p[c][i];
                 }
 #pragma unroll
                 for (int i = 0; i < 3; ++i)
@@ -269,7 +273,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                 dl[c] = fma(g[c][0], y0, fma(g[c][1], y1, g[c][2] * y2));
             }
 #pragma unroll
-            for (int i = 0; i < NP; ++i) {
+            for (int i = 0; i < NR; ++i) {
                 const double2 v01 = *reinterpret_cast<const double2*>(&s.V[0][i * 4]);
                 const double v2 = s.V[0][i * 4 + 2];
 #pragma unroll
@@ -335,7 +339,7 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
                     dl[c] = fma(g[c][0], y0, fma(g[c][1], y1, dl[c]));
                 }
 #pragma unroll
-                for (int i = 0; i < NP; ++i) {
+                for (int i = 0; i < NR; ++i) {
                     const double2 vi = *reinterpret_cast<const double2*>(&s.V[buf][i * 2]);
 #pragma unroll
                     for (int c = 0; c < CPT; ++c) p[c][i] = fma(-vi.x, g[c][0], fma(-vi.y, g[c][1], p[c][i]));
@@ -365,7 +369,9 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
         bool bad = false;
         double acc = 0.0;  // NaN/Inf anywhere in the owned columns makes the sum non-finite
 #pragma unroll
-        for (int i = 0; i < NP; ++i) {
+        for (int c = 0; c < CPT; ++c) Pg[(NP - 1) * NP + j0 + c] = 0.0;  // the padding row
+#pragma unroll
+        for (int i = 0; i < NR; ++i) {
 #pragma unroll
             for (int c = 0; c < CPT; ++c) acc += p[c][i];
             if constexpr (CPT == 2) {

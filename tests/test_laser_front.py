@@ -136,3 +136,30 @@ def test_synthetic_scan_kernel_matches_numpy_generator(aslam):
     rg, bg, cnt = lm.callback(got)
     assert np.all(cnt >= 3)
     lm.close()
+
+
+@pytest.mark.gpu
+def test_laser_device_path_batches_larger_than_the_work_list(aslam):
+    """aslam_laser_extract_device with more scans than the handle was created for (its dense work list of accepted
+    clusters holds max_scans scans: larger batches are processed in chunks) equals the host-buffer path of a handle
+    that is large enough."""
+    import torch
+    sc, _, _, _ = _scans(aslam, 200, 5, cfg3=True)
+    big = aslam.LandMarks(max_scans=200)
+    rg, bg, cnt = big.callback(sc)
+    big.close()
+    small = aslam.LandMarks(max_scans=48)
+    dev = torch.device("cuda", 0)
+    d_sc = torch.from_numpy(sc).to(dev)
+    d_rg = torch.zeros((200, 32), dtype=torch.float32, device=dev)
+    d_bg = torch.zeros((200, 32), dtype=torch.float32, device=dev)
+    d_cnt = torch.zeros(200, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    small.callback_device(d_sc.data_ptr(), 200, d_rg.data_ptr(), d_bg.data_ptr(), d_cnt.data_ptr())
+    small.sync()
+    assert small.launch_count == 2 * 5  # ceil(200 / 48) chunks, classification + fit each
+    assert np.array_equal(d_cnt.cpu().numpy(), cnt)
+    for i in range(200):
+        k = max(int(cnt[i]), 0)
+        assert np.array_equal(d_rg[i, :k].cpu().numpy(), rg[i, :k]) and np.array_equal(d_bg[i, :k].cpu().numpy(), bg[i, :k])
+    small.close()
