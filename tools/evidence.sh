@@ -25,6 +25,6 @@ if timeout 300 python tools/prof_target.py batched 65536 8 > /dev/null 2>&1; the
   timeout 900 $NCU -k regex:ekf_batched -s 1 -c 2 -o $O/${T}_batched -f python tools/prof_target.py batched 65536 8 > $O/${T}_ncu_b.log 2>&1; echo "batched rc=$?"
 fi
 if timeout 300 python tools/prof_target.py laser 65536 > /dev/null 2>&1; then
-  timeout 900 $NCU -k regex:laser_extract -s 1 -c 2 -o $O/${T}_laser -f python tools/prof_target.py laser 65536 > $O/${T}_ncu_laser.log 2>&1; echo "laser rc=$?"
+  timeout 900 $NCU -k 'regex:laser_(extract|fit)' -s 2 -c 4 -o $O/${T}_laser -f python tools/prof_target.py laser 65536 > $O/${T}_ncu_laser.log 2>&1; echo "laser rc=$?"
 fi
 ls -la $O | grep ${T}_
