@@ -280,7 +280,9 @@ aslam_status aslam_laser_destroy(aslam_laser* h);
  * assert(theta < 359) (:82) fires (first and last ray on the same object). Synchronous. */
 aslam_status aslam_laser_extract(aslam_laser* h, const float* ranges, uint32_t nscan, float* range_out,
                                  float* bearing_out, int32_t* counts);
-/* Same with device buffers, asynchronous on the handle's stream (aslam_laser_sync / aslam_laser_stream). */
+/* Same with device buffers, asynchronous on the handle's stream (aslam_laser_sync / aslam_laser_stream). nscan may
+ * exceed max_scans: the batch is then processed in chunks of max_scans (the size of the handle's work list). Two
+ * kernel launches per chunk (classification, then the circle fit of the accepted clusters). */
 aslam_status aslam_laser_extract_device(aslam_laser* h, const float* d_ranges, uint32_t nscan, float* d_range_out,
                                         float* d_bearing_out, int32_t* d_counts);
 /* Synthetic LaserScans, standing in for Gazebo's LDS plugin: 360 rays, one per degree from the
