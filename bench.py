@@ -392,6 +392,61 @@ def _ncu_traffic():
         return None
 
 
+def ukf_batched_leg(args, torch, dev, B=16384):
+    """Batched UKF-SLAM (K2, the reference's UKFSlam at its own size: the landmarks.yaml map, n = 19, 43 sigma points),
+    B filters with their own noise seeds, messages resident in HBM, FUSE messages per launch. The free-running reference
+    UKF turns indefinite (w0 < 0) and the kernel reproduces that, LLT failures included: the count of filters
+    that reported one is printed, the time per update does not depend on it. CPU: the oracle on a bounded sample."""
+    import awesomeslam_b200 as A
+    lmx, lmy = A.map_cfg1()
+    L = len(lmx)
+    K, W = min(args.steps, 10), max(args.warmup, 3)
+    total = WARM_MSGS + (W + K) * FUSE
+    rp = A.Replay(lmx, lmy, B, max(total, 240), seed0=0x0CF20000)
+    dev_t = [torch.from_numpy(a).to(dev) for a in (rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing)]
+
+    def run(f, msg0, nmsg):
+        p = [t.data_ptr() + msg0 * t[0].numel() * t.element_size() for t in dev_t]
+        f.run_device(nmsg, *p, L)
+
+    f = A.BatchedFilter("ukf", B, dev.index, max_state_dim=30)
+    stream = torch.cuda.ExternalStream(f.stream, device=dev)
+    run(f, 0, WARM_MSGS)
+    f.sync()
+    assert np.all(f.get_state(want_P=False, want_assoc=False)["N"] == 3 + 2 * L), "UKF warm-up did not map the 8 landmarks"
+    msg = WARM_MSGS
+    for _ in range(W):
+        run(f, msg, FUSE)
+        msg += FUSE
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    with torch.cuda.stream(stream):
+        e0.record()
+        for _ in range(K):
+            run(f, msg, FUSE)
+            msg += FUSE
+        e1.record()
+    f.sync()
+    ms = e0.elapsed_time(e1)
+    st = f.get_state(want_P=False, want_assoc=False)
+    failed = int(np.count_nonzero(st["status"] & A.capi.ST_LLT_FAILED))
+    f.close()
+    out = {"workload": "batched UKF-SLAM: %d filters x 8 landmarks (n=19, 43 sigma points), %d messages per launch" % (B, FUSE),
+           "updates_per_s": B * FUSE * K / (ms * 1e-3), "ms_per_launch": ms / K,
+           "filters_with_llt_failure": failed}
+    if not args.no_cpu:
+        from oracle import oracle as O
+        O.build()
+        sample, msgs = (1024 if (os.cpu_count() or 1) < 16 else 4096), 240
+        sec, X, P, N = O.run_batch("ukf", O.default_config(max_state_dim=30), sample, msgs, L, rp.x[:msgs, :sample].copy(),
+                                   rp.y[:msgs, :sample].copy(), rp.yaw[:msgs, :sample].copy(), rp.vx[:msgs, :sample].copy(),
+                                   rp.az[:msgs, :sample].copy(), rp.dt[:msgs, :sample].copy(),
+                                   rp.range[:msgs, :sample].copy(), rp.bearing[:msgs, :sample].copy(), 0, 30, want_P=False)
+        out["cpu_baseline"] = {"value": sample * msgs / sec, "unit": "updates/s", "cores": O.num_threads(), "kind": "port",
+                               "sample": "%d filters x %d messages from reset, OpenMP over filters, %.1f s" % (sample, msgs, sec)}
+    return out
+
+
 def large_cpu_leg(steps=10):
     """cfg4 on the host cores: the oracle's row-subset joint update (the same formula the kernels run), full size,
     OpenMP over the columns of P. Returns the cpu_baseline object of the large_map leg."""
@@ -591,8 +646,10 @@ def main():
             if large is not None and world == 1:
                 large["cpu_baseline"] = large_cpu_leg()
     laser = None
+    ukf_batched = None
     if rank == 0 and not args.no_large:
         laser = laser_leg(args, torch, dev)
+        ukf_batched = ukf_batched_leg(args, torch, dev)
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -632,6 +689,8 @@ def main():
         line["large_map_ukf"] = ukf_large
     if laser is not None:
         line["laser_front"] = laser
+    if ukf_batched is not None:
+        line["batched_ukf"] = ukf_batched
     if not args.no_cpu:
         cpu_filters, cpu_msgs = (1024 if (os.cpu_count() or 1) < 16 else 4096), 240
         ups, nthr, sec = cpu_leg(cpu_filters, cpu_msgs)
