@@ -415,6 +415,8 @@ struct aslam_laser {
     float* d_range_out = nullptr;
     float* d_bearing_out = nullptr;
     int32_t* d_counts = nullptr;
+    cudaStream_t copy_in = nullptr;   // host path: the scans of chunk k+1 cross PCIe while chunk k is processed
+    cudaEvent_t ev_in = nullptr;
     uint2* d_work = nullptr;          // accepted clusters of one batch: (output slot, start | length << 16)
     uint32_t* d_work_count = nullptr;
     uint64_t launches = 0;
@@ -463,6 +465,8 @@ aslam_status aslam_laser_create(const aslam_laser_config* cfg, uint32_t max_scan
         hc[th] = std::cos(c.deg2rad * static_cast<float>(th));
     }
     bool ok = cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    ok = ok && cuda_ok(cudaStreamCreateWithFlags(&h->copy_in, cudaStreamNonBlocking), "cudaStreamCreate");
+    ok = ok && cuda_ok(cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming), "cudaEventCreate");
     const size_t ob = (size_t)max_scans * ASLAM_LASER_MAX_LANDMARKS * sizeof(float);
     ok = ok && cuda_ok(cudaMalloc((void**)&h->d_cos, sizeof(hc)), "cudaMalloc");
     ok = ok && cuda_ok(cudaMalloc((void**)&h->d_sin, sizeof(hs)), "cudaMalloc");
@@ -489,6 +493,11 @@ aslam_status aslam_laser_destroy(aslam_laser* h) {
     void* ptrs[] = {h->d_cos, h->d_sin, h->d_ranges, h->d_range_out, h->d_bearing_out, h->d_counts, h->d_work, h->d_work_count};
     for (void* p : ptrs)
         if (p) cudaFree(p);
+    if (h->copy_in) {
+        cudaStreamSynchronize(h->copy_in);
+        cudaStreamDestroy(h->copy_in);
+    }
+    if (h->ev_in) cudaEventDestroy(h->ev_in);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ASLAM_OK;
@@ -521,13 +530,28 @@ aslam_status aslam_laser_extract(aslam_laser* h, const float* ranges, uint32_t n
     if (!h || !ranges || !range_out || !bearing_out || !counts || nscan > h->max_scans) return ASLAM_ERR_ARG;
     if (nscan == 0) return ASLAM_OK;
     ASLAM_CUDA(cudaSetDevice(h->device));
-    ASLAM_CUDA(cudaMemcpyAsync(h->d_ranges, ranges, (size_t)nscan * RAYS * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-    const aslam_status rc = aslam_laser_extract_device(h, h->d_ranges, nscan, h->d_range_out, h->d_bearing_out, h->d_counts);
-    if (rc != ASLAM_OK) return rc;
-    const size_t ob = (size_t)nscan * ASLAM_LASER_MAX_LANDMARKS * sizeof(float);
-    ASLAM_CUDA(cudaMemcpyAsync(range_out, h->d_range_out, ob, cudaMemcpyDeviceToHost, h->stream));
-    ASLAM_CUDA(cudaMemcpyAsync(bearing_out, h->d_bearing_out, ob, cudaMemcpyDeviceToHost, h->stream));
-    ASLAM_CUDA(cudaMemcpyAsync(counts, h->d_counts, (size_t)nscan * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    // Chunks of 8,192 scans: the host->device copy of a chunk runs on its own stream, the kernels and the (much smaller)
+    // result copies of the previous chunk on the handle's stream -- with pinned host buffers the call is bound by the
+    // input crossing PCIe once (11.8 MB per chunk), not by the sum of copy + kernels + copy.
+    constexpr uint32_t CHUNK = 8192;
+    // the staging area must not be overwritten while an earlier call's kernels still read it
+    ASLAM_CUDA(cudaEventRecord(h->ev_in, h->stream));
+    ASLAM_CUDA(cudaStreamWaitEvent(h->copy_in, h->ev_in, 0));
+    for (uint32_t first = 0; first < nscan; first += CHUNK) {
+        const uint32_t cnt = nscan - first < CHUNK ? nscan - first : CHUNK;
+        const size_t o = (size_t)first * ASLAM_LASER_MAX_LANDMARKS, ob = (size_t)cnt * ASLAM_LASER_MAX_LANDMARKS * sizeof(float);
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_ranges + (size_t)first * RAYS, ranges + (size_t)first * RAYS,
+                                   (size_t)cnt * RAYS * sizeof(float), cudaMemcpyHostToDevice, h->copy_in));
+        ASLAM_CUDA(cudaEventRecord(h->ev_in, h->copy_in));
+        ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_in, 0));
+        const aslam_status rc = aslam_laser_extract_device(h, h->d_ranges + (size_t)first * RAYS, cnt, h->d_range_out + o,
+                                                           h->d_bearing_out + o, h->d_counts + first);
+        if (rc != ASLAM_OK) return rc;
+        ASLAM_CUDA(cudaMemcpyAsync(range_out + o, h->d_range_out + o, ob, cudaMemcpyDeviceToHost, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(bearing_out + o, h->d_bearing_out + o, ob, cudaMemcpyDeviceToHost, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(counts + first, h->d_counts + first, (size_t)cnt * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                   h->stream));
+    }
     ASLAM_CUDA(cudaStreamSynchronize(h->stream));
     return ASLAM_OK;
 }

@@ -445,6 +445,17 @@ class LandMarks:
         capi.check(self._lib.aslam_laser_extract(self._h, capi.ptr(ranges), ns, capi.ptr(rg), capi.ptr(bg), capi.ptr(cnt)))
         return rg, bg, cnt
 
+    def callback_into(self, ranges, range_out, bearing_out, counts):
+        """`callback` into caller-owned host arrays (e.g. views of pinned memory: the copies then overlap the kernels):
+        ranges [nscan, 360] float32; range_out / bearing_out [nscan, 32] float32; counts [nscan] int32, all C-contiguous."""
+        ns = ranges.shape[0]
+        for a, dt, shape in ((ranges, np.float32, (ns, 360)), (range_out, np.float32, (ns, self.MAX_LANDMARKS)),
+                             (bearing_out, np.float32, (ns, self.MAX_LANDMARKS)), (counts, np.int32, (ns,))):
+            if a.dtype != dt or a.shape != shape or not a.flags["C_CONTIGUOUS"]:
+                raise ValueError("callback_into: wrong dtype / shape / layout")
+        capi.check(self._lib.aslam_laser_extract(self._h, capi.ptr(ranges), ns, capi.ptr(range_out), capi.ptr(bearing_out),
+                                                 capi.ptr(counts)))
+
     def synthesize(self, lmx, lmy, poses, noise=None, sigma=0.01, radius=0.25):
         """Synthetic LDS scans on the GPU (the Gazebo stand-in): poses [nscan, 3] (x, y, yaw), noise [nscan, 360]
         standard-normal float32 or None -> ranges [nscan, 360] float32 (+inf = no return)."""
