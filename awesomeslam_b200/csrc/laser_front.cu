@@ -33,6 +33,7 @@ struct LaserParams {
 
 struct __align__(16) ScanSlot {
     float px[RAYS], py[RAYS];
+    float ang[RAYS];  // inscribed angles of the cluster a ray belongs to (clusters are disjoint ray ranges)
     short cstart[MAXC], clen[MAXC];
     int ncand;
 };
@@ -106,7 +107,8 @@ __device__ __forceinline__ void jacobi4(double (&A)[4][4], double (&V)[4][4]) {
 
 // sensor_landmark.cpp:147-186 on the n points of one cluster
 template <typename PTS>
-__device__ __forceinline__ bool classify(const PTS& pts, const LaserParams& lp, int n) {
+__device__ __forceinline__ bool classify(const PTS& pts, const LaserParams& lp, int n, float* ang) {
+    // ang: n floats of scratch owned by this cluster (the reference keeps the angles in a vector, :152-171)
     const float x1 = pts.x(0), y1 = pts.y(0), x2 = pts.x(n - 1), y2 = pts.y(n - 1);
     const float c = euler_distance(x1, y1, x2, y2);
     const float cc = __fmul_rn(c, c);
@@ -118,17 +120,13 @@ __device__ __forceinline__ bool classify(const PTS& pts, const LaserParams& lp, 
         const float den = __fmul_rn(__fmul_rn(2.0f, a), b);
         // acosf of the reference's libm, taken as the correctly rounded value of the double routine
         const float angle = (float)acos((double)__fdiv_rn(num, den));
+        ang[i] = angle;
         sum = __fadd_rn(sum, angle);
     }
     const float mean = __fdiv_rn(sum, (float)(n - 2));
     float variance = 0.0f;
-    for (int i = 1; i < n - 1; ++i) {  // the angles are recomputed instead of stored (same values)
-        const float x = pts.x(i), y = pts.y(i);
-        const float a = euler_distance(x1, y1, x, y), b = euler_distance(x2, y2, x, y);
-        const float num = __fsub_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), cc);
-        const float den = __fmul_rn(__fmul_rn(2.0f, a), b);
-        const float angle = (float)acos((double)__fdiv_rn(num, den));
-        const double d = (double)__fsub_rn(angle, mean);
+    for (int i = 1; i < n - 1; ++i) {
+        const double d = (double)__fsub_rn(ang[i], mean);
         variance = (float)__dadd_rn((double)variance, __dmul_rn(d, d));  // pow(float, 2) is a double (:174)
     }
     const float sd = (float)sqrt(__ddiv_rn((double)variance, 5.0));  // (:177)
@@ -332,7 +330,7 @@ __global__ void __launch_bounds__(LWPB * 32) laser_extract_kernel(const float* _
         if (cnd < nc) {
             s0 = s.cstart[cnd];
             n = s.clen[cnd];
-            ok = classify(SlotPoints{s.px + s0, s.py + s0}, lp, n);
+            ok = classify(SlotPoints{s.px + s0, s.py + s0}, lp, n, s.ang + s0);
         }
         const unsigned m = __ballot_sync(0xffffffffu, ok);
         const int slot = total + __popc(m & ((1u << lane) - 1u));
