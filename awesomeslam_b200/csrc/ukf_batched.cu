@@ -29,15 +29,23 @@ constexpr int USP = 65;          // row pitch of the sigma-point matrices (odd: 
 constexpr int UTHREADS = 128;
 
 struct __align__(16) UkfSlot {
-    double XS[UNP][USP];   // XsigPred, later Xdiff       (row = state index, col = sigma point)
-    double ZS[UNP][USP];   // Zsig, later Zdiff
+    // The sigma-point matrices are dead once P, S and Tc have been formed; the LU factors of S, its inverse and K live
+    // in the same bytes from then on (a barrier separates the two uses): 3 instead of 2 CTAs per SM.
+    union {
+        struct {
+            double XS[UNP][USP];   // XsigPred, later Xdiff       (row = state index, col = sigma point)
+            double ZS[UNP][USP];   // Zsig, later Zdiff
+        };
+        struct {
+            double K[UNP][UNP];
+            double LU[UNP][UNP];   // PartialPivLU of S, then S^-1 in Si
+            double Si[UNP][UNP];
+        };
+    };
     double L[UNA][UNA];    // Paug -> L (ukf.cpp:263-280); later K S
     double P[UNP][UNP];
     double S[UNP][UNP];
     double Tc[UNP][UNP];
-    double K[UNP][UNP];
-    double LU[UNP][UNP];   // PartialPivLU of S, then S^-1 in Si
-    double Si[UNP][UNP];
     double X[UNP], Z[UNP], Zp[UNP], Zd[UNP], W[UNS];
     int piv[UNP];
     int fail_k;
@@ -252,9 +260,10 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
             else if (which == 1) {
                 const double v = acc + (a == b ? kp.kr : 0.0);
                 s.S[a][b] = v;
-                s.LU[a][b] = v;
             } else s.Tc[a][b] = acc;
         }
+        __syncthreads();  // last read of the sigma-point matrices: LU / Si / K take over their storage
+        for (int e = tid; e < N * N; e += UTHREADS) s.LU[e / N][e % N] = s.S[e / N][e % N];
         __syncthreads();
         // ---- S.inverse(): PartialPivLU (unblocked, first largest pivot) ...
         for (int k = 0; k < N; ++k) {
