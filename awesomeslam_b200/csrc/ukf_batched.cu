@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
                 const int i = k / N, j = k % N;
                 if (i >= g0 || j >= g0) s.P[i][j] = (i == j) ? kp.kp_lm : 0.0;
             }
+            __syncthreads();  // (uniform branch) the Paug loop below reads P with a different thread mapping
         }
         const float lambda = (float)(3.0 - (double)(N + 2));
         const float denom = __fadd_rn(__fadd_rn(lambda, (float)N), 2.0f);  // lambda + N + 2 in float
