@@ -59,10 +59,19 @@ def laser(B):
     lmx, lmy = A.map_cfg3()
     base = A.laser_scans(lmx, lmy, A.laser_poses(4096, seed=77, **A.replay.LASER_POSES_CFG3), seed=78)
     sc = np.tile(base, (max(B // 4096, 1), 1))
-    lm = A.LandMarks(max_scans=sc.shape[0])
-    for _ in range(3):
-        rg, bg, cnt = lm.callback(sc)
-    print("laser scans", sc.shape[0], "landmarks/scan", float(cnt.mean()))
+    import torch
+    n = sc.shape[0]
+    lm = A.LandMarks(max_scans=n)
+    dev = torch.device("cuda", 0)
+    d_sc = torch.from_numpy(sc).to(dev)
+    d_r = torch.empty((n, 32), dtype=torch.float32, device=dev)
+    d_b = torch.empty((n, 32), dtype=torch.float32, device=dev)
+    d_c = torch.empty((n,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize(dev)
+    for _ in range(3):  # the device-resident path: one classification + one fit launch for the whole batch
+        lm.callback_device(d_sc.data_ptr(), n, d_r.data_ptr(), d_b.data_ptr(), d_c.data_ptr())
+    lm.sync()
+    print("laser scans", n, "landmarks/scan", float(d_c.float().mean().item()))
 
 
 if __name__ == "__main__":
