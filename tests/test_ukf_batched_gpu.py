@@ -55,6 +55,28 @@ def test_ukf_batch_of_filters(aslam, orc):
     f.close()
 
 
+def test_ukf_batch_is_reproducible_through_growth(aslam):
+    """2,048 filters through promotion and growth (message 10) and on into the chaotic regime, twice, replayed in
+    different launch splits: bit-identical states and LLT reports. A free-running UKF amplifies a last-bit difference
+    within a few messages, so this is a sensitive detector of a shared-memory ordering bug (one was found this way
+    between the growth of P and the Paug loop)."""
+    lmx, lmy = aslam.map_cfg1()
+    B, T, L = 2048, 64, 8
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=0x0CF20000)
+    out = []
+    for split in (64, 8):
+        f = aslam.BatchedFilter("ukf", B, 0)
+        for t0 in range(0, T, split):
+            sl = slice(t0, t0 + split)
+            f.run_host(split, rp.x[sl], rp.y[sl], rp.yaw[sl], rp.vx[sl], rp.az[sl], rp.dt[sl], rp.range[sl], rp.bearing[sl], L)
+        st = f.get_state()
+        out.append((st["X"], st["P"], st["N"], st["status"], f.get_llt_fail()))
+        f.close()
+    for a, b in zip(out[0], out[1]):
+        assert np.array_equal(a, b, equal_nan=True)
+    assert np.mean(out[0][2] == 19) > 0.9  # (a free-running filter that has gone indefinite may map a spurious landmark)
+
+
 def test_ukf_cap_above_reference_is_refused(aslam):
     with pytest.raises(aslam.capi.AslamError) as e:
         aslam.BatchedFilter("ukf", 1, 0, max_state_dim=64)
