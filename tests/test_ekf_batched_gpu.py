@@ -196,6 +196,27 @@ def test_handles_on_two_devices_of_one_process(aslam, kind):
     assert np.array_equal(out[0]["N"], out[1]["N"]) and int(out[0]["N"].max()) == 19
 
 
+def test_kernel_instantiations_agree_bit_for_bit(aslam):
+    """The same replay through the <36,2>, <48,2> and <64,1> instantiations of the batched kernel (18, 24 and 64 threads
+    per filter; 7, 5 and 2 filters per CTA): X, P and N identical to the last bit, from reset through promotion and
+    growth. The arithmetic per element does not depend on the mapping, so any difference would be an ordering bug."""
+    lmx, lmy = aslam.map_cfg3()
+    B, T, L = 1024, 48, 16
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=0x5EED0000)
+    out = {}
+    for msd in (36, 48, 64):
+        f = aslam.BatchedFilter("ekf", B, 0, max_state_dim=msd)
+        assert f.ld == msd
+        f.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+        st = f.get_state()
+        out[msd] = (st["X"][:, :35].copy(), st["P"][:, :35, :35].copy(), st["N"].copy())
+        f.close()
+    assert np.all(out[36][2] == 35)
+    for msd in (48, 64):
+        for a, b in zip(out[36], out[msd]):
+            assert np.array_equal(a, b), msd
+
+
 def test_pipelined_host_path_equals_one_launch(aslam):
     """run_host without a sync in between (double-buffered staging, copy stream) plus the pipelined
     read_state_async / read_wait: every intermediate X equals the one a synchronous replay of the same
