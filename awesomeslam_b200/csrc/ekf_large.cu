@@ -1095,10 +1095,16 @@ aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
         const uint32_t full_rblocks = nrows / rows_per_cta ? nrows / rows_per_cta : 1;
         // column ranges: the full row blocks fill `waves` whole waves of the resident CTAs
         const uint32_t resident = (uint32_t)sms * (use_ldg ? 2u : 1u);
-        const uint32_t waves = waves_env ? (uint32_t)std::atoi(waves_env) : 4u;
-        uint32_t cx = (waves * resident + full_rblocks / 2) / full_rblocks;
-        if (cx < 1) cx = 1;
         const uint32_t cs = QT == 20 ? 8u : 16u;
+        // 12 waves where that still leaves a CTA at least 64 columns to stream (measured on the unsharded cfg4 matrix:
+        // 201 -> 196 us), else 4 (row-sharded handles: short column ranges would spend their time filling the ring)
+        auto ranges = [&](uint32_t w) {
+            const uint32_t c = (w * resident + full_rblocks / 2) / full_rblocks;
+            return c < 1 ? 1u : c;
+        };
+        uint32_t waves = (n + ranges(12u) - 1) / ranges(12u) >= 64u ? 12u : 4u;
+        if (waves_env) waves = (uint32_t)std::atoi(waves_env);
+        uint32_t cx = ranges(waves);
         uint32_t cols_per_cta = (n + cx - 1) / cx;
         cols_per_cta = ((cols_per_cta + cs - 1) / cs) * cs;
         cx = (n + cols_per_cta - 1) / cols_per_cta;
