@@ -74,6 +74,18 @@ def build_library(force=False, verbose=False):
     return LIB
 
 
+HOST_LIB = os.path.join(LIBDIR, "libaslam_host.so")
+
+
+def build_host_lib(force=False):
+    """csrc/replay.cpp alone (replay generator + quat2euler): host-only helpers without CUDA."""
+    os.makedirs(LIBDIR, exist_ok=True)
+    src = os.path.join(CSRC, "replay.cpp")
+    if force or _stale(HOST_LIB, [src, os.path.join(ROOT, "include", "aslam_c.h")]):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", src, "-o", HOST_LIB])
+    return HOST_LIB
+
+
 HARNESS = os.path.join(LIBDIR, "aslam_replay")
 
 
@@ -97,8 +109,26 @@ def build_oracle(force=False):
     return ORACLE_LIB
 
 
+REF_SRC = "/root/reference/awesome_slam"
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+
+def build_ref(force=False):
+    """TEST INFRASTRUCTURE: compiles the reference's own ekf.cpp / ukf.cpp / sensor_landmark.cpp, unmodified and from
+    where they lie under /root/reference, against the Eigen / ROS stand-ins of oracle/ref_shim into oracle/_ref/
+    (git-ignored, travels to the GPU box). Where /root/reference is absent (the GPU box) the prebuilt files are
+    used as they are. Returns the directory, or None when neither sources nor prebuilt libraries exist."""
+    if os.path.isdir(REF_SRC):
+        cmd = ["make", "-C", os.path.join(ROOT, "oracle", "ref_shim"), "REF=" + REF_SRC] + (["-B"] if force else [])
+        subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+        return REF_DIR
+    return REF_DIR if os.path.exists(os.path.join(REF_DIR, "libref_ekf.so")) else None
+
+
 if __name__ == "__main__":
     v = "-v" in sys.argv
     print(build_library(force="-f" in sys.argv, verbose=v))
+    print(build_host_lib(force="-f" in sys.argv))
     print(build_harness(force="-f" in sys.argv))
     print(build_oracle(force="-f" in sys.argv))
+    print(build_ref(force="-f" in sys.argv))

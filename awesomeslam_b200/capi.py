@@ -129,7 +129,28 @@ SIGNATURES = {
     "aslam_probe_dmma_tflops": (_i32, [_i32, C.POINTER(_f64)]),
     "aslam_replay_generate": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, _f64, _f64, C.c_uint64, _u32,
                                      _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "aslam_replay_generate_quat": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, _f64, _f64, C.c_uint64, _u32,
+                                          _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
+
+# The host-only helpers (no CUDA behind them): csrc/replay.cpp built alone into lib/libaslam_host.so, so that input
+# generation -- e.g. for bench.py's reference arm -- does not have to map the CUDA library.
+HOST_LIB_PATH = os.path.join(_HERE, "lib", "libaslam_host.so")
+HOST_SYMBOLS = ("aslam_quat2euler", "aslam_replay_generate", "aslam_replay_generate_quat")
+_host = None
+
+
+def host_lib():
+    global _host
+    if _host is None:
+        if not os.path.exists(HOST_LIB_PATH):
+            raise ImportError("%s is missing: build it with `python -m awesomeslam_b200.build`" % HOST_LIB_PATH)
+        l = C.CDLL(HOST_LIB_PATH)
+        for name in HOST_SYMBOLS:
+            fn = getattr(l, name)
+            fn.restype, fn.argtypes = SIGNATURES[name]
+        _host = l
+    return _host
 
 _lib = None
 

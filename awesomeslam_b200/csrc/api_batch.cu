@@ -351,14 +351,6 @@ aslam_status aslam_filter_read_wait(aslam_filter* h, uint64_t ticket) {
     return ASLAM_OK;
 }
 
-float aslam_quat2euler(double w, double x, double y, double z) {
-    const float fw = (float)w, fx = (float)x, fy = (float)y, fz = (float)z;
-    // tools.h:64: float arithmetic throughout, atan2f
-    const float num = 2 * (fw * fz + fx * fy);
-    const float den = 1 - 2 * (fz * fz + fy * fy);
-    return std::atan2(num, den);
-}
-
 aslam_status aslam_ekf_create(const aslam_config* cfg, uint32_t batch, int32_t device, aslam_filter** out) {
     return create_filter(ASLAM_KIND_EKF, cfg, batch, device, out);
 }

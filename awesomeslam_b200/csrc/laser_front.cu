@@ -29,6 +29,7 @@ constexpr int LWPB = 4;    // warps (scans) per CTA
 struct LaserParams {
     float thresh, std_max, min_mean, max_mean;
     int min_pts;
+    float c0, s0, c359, s359;  // table entries 0 and 359 as initialize() builds them: the wrap test (:63-64)
 };
 
 struct __align__(16) ScanSlot {
@@ -281,14 +282,18 @@ __global__ void __launch_bounds__(LWPB * 32) laser_extract_kernel(const float* _
     if (scan >= nscan) return;  // whole warp; no CTA barrier in this kernel
     ScanSlot& s = slots[warp];
     const float* r = ranges + (size_t)scan * RAYS;
-    for (int t = lane; t < RAYS; t += 32) {  // bearing2pose (:136-142)
+    // bearing2pose (:136-142). cos_map / sin_map are the POSE tables: entry t is what the reference multiplies ray t
+    // with inside its clustering loop, i.e. initialize()'s entry t + 1 (see aslam_laser_create).
+    for (int t = lane; t < RAYS; t += 32) {
         const float d = r[t];
         s.px[t] = __fmul_rn(d, cos_map[t]);
         s.py[t] = __fmul_rn(d, sin_map[t]);
     }
     __syncwarp();
-    // first and last ray on the same object: the reference's assert(theta < 359) fires (:82)
-    if (euler_distance(s.px[0], s.py[0], s.px[RAYS - 1], s.py[RAYS - 1]) < lp.thresh) {
+    // first and last ray on the same object: the reference's assert(theta < 359) fires (:82). This test (:63-64)
+    // projects rays 0 and 359 with their own table entries.
+    if (euler_distance(__fmul_rn(r[0], lp.c0), __fmul_rn(r[0], lp.s0), __fmul_rn(r[RAYS - 1], lp.c359),
+                       __fmul_rn(r[RAYS - 1], lp.s359)) < lp.thresh) {
         if (lane == 0) counts[scan] = -1;
         return;
     }
@@ -456,12 +461,21 @@ aslam_status aslam_laser_create(const aslam_laser_config* cfg, uint32_t max_scan
     h->lp.min_mean = c.min_mean;
     h->lp.max_mean = c.max_mean;
     h->lp.min_pts = c.min_cluster_points;
-    // LandMarks::initialize (sensor_landmark.cpp:50-57): float argument, float sin / cos of the host libm
+    // LandMarks::initialize (sensor_landmark.cpp:50-57): float argument, float sin / cos of the host libm.
+    // The clustering loop calls `bearing2pose(theta, msg->ranges[theta++])` (:87,98): the evaluation order of the two
+    // arguments is unspecified and GCC -- the compiler of every ROS build; oracle/_ref, the reference compiled here,
+    // pins it -- takes them right to left, so ray t is projected with table entry t + 1 (every cluster, and every
+    // published bearing, is rotated by +1 degree) and ray 359 with entry 360, one past the table, which reads 0.0f
+    // from the vector's spare capacity. The device tables hold that per-ray entry directly.
     float hc[RAYS], hs[RAYS];
     for (int th = 0; th < RAYS; ++th) {
-        hs[th] = std::sin(c.deg2rad * static_cast<float>(th));
-        hc[th] = std::cos(c.deg2rad * static_cast<float>(th));
+        hs[th] = th + 1 < RAYS ? std::sin(c.deg2rad * static_cast<float>(th + 1)) : 0.0f;
+        hc[th] = th + 1 < RAYS ? std::cos(c.deg2rad * static_cast<float>(th + 1)) : 0.0f;
     }
+    h->lp.c0 = std::cos(c.deg2rad * static_cast<float>(0));
+    h->lp.s0 = std::sin(c.deg2rad * static_cast<float>(0));
+    h->lp.c359 = std::cos(c.deg2rad * static_cast<float>(RAYS - 1));
+    h->lp.s359 = std::sin(c.deg2rad * static_cast<float>(RAYS - 1));
     bool ok = cuda_ok(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "cudaStreamCreate");
     ok = ok && cuda_ok(cudaStreamCreateWithFlags(&h->copy_in, cudaStreamNonBlocking), "cudaStreamCreate");
     ok = ok && cuda_ok(cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming), "cudaEventCreate");

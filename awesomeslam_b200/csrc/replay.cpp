@@ -44,7 +44,7 @@ double wrap_pi(double a) {
 
 void one_filter(const double* lm_x, const double* lm_y, uint32_t L, uint32_t batch, uint32_t steps, uint32_t warm,
                 double vx, double az, uint64_t seed, uint32_t b, double* ox, double* oy, float* yaw, double* ovx,
-                double* oaz, float* dt, float* range, float* bearing) {
+                double* oaz, float* dt, float* range, float* bearing, double* oqw, double* oqz) {
     Gauss g(seed);
     double x = 0.0, y = 0.0, th = 0.0;
     std::vector<std::pair<double, uint32_t>> order(L);
@@ -64,7 +64,10 @@ void one_filter(const double* lm_x, const double* lm_y, uint32_t L, uint32_t bat
         ox[i] = x + 0.01 * g();
         oy[i] = y + 0.01 * g();
         const double nyaw = th + 0.01 * g();
-        yaw[i] = aslam_quat2euler(std::cos(0.5 * nyaw), 0.0, 0.0, std::sin(0.5 * nyaw));
+        const double qw = std::cos(0.5 * nyaw), qz = std::sin(0.5 * nyaw);  // orientation (w, 0, 0, z) of the message
+        yaw[i] = aslam_quat2euler(qw, 0.0, 0.0, qz);
+        if (oqw) oqw[i] = qw;
+        if (oqz) oqz[i] = qz;
         ovx[i] = v;
         oaz[i] = w;
         dt[i] = 1.0f;
@@ -84,10 +87,19 @@ void one_filter(const double* lm_x, const double* lm_y, uint32_t L, uint32_t bat
 
 }  // namespace
 
-extern "C" aslam_status aslam_replay_generate(const double* lm_x, const double* lm_y, uint32_t L, uint32_t batch,
-                                              uint32_t steps, uint32_t warm, double vx, double az, uint64_t seed0,
-                                              uint32_t first_filter, double* ox, double* oy, float* yaw,
-                                              double* ovx, double* oaz, float* dt, float* range, float* bearing) {
+// tools.h:62-66 quat2euler: the four arguments are rounded to float first, float arithmetic, atan2f.
+extern "C" float aslam_quat2euler(double w, double x, double y, double z) {
+    const float fw = (float)w, fx = (float)x, fy = (float)y, fz = (float)z;
+    const float num = 2 * (fw * fz + fx * fy);
+    const float den = 1 - 2 * (fz * fz + fy * fy);
+    return std::atan2(num, den);
+}
+
+extern "C" aslam_status aslam_replay_generate_quat(const double* lm_x, const double* lm_y, uint32_t L, uint32_t batch,
+                                                   uint32_t steps, uint32_t warm, double vx, double az,
+                                                   uint64_t seed0, uint32_t first_filter, double* ox, double* oy,
+                                                   float* yaw, double* ovx, double* oaz, float* dt, float* range,
+                                                   float* bearing, double* qw, double* qz) {
     if (!ox || !oy || !yaw || !ovx || !oaz || !dt || (L && (!lm_x || !lm_y || !range || !bearing)))
         return ASLAM_ERR_ARG;
     unsigned nt = std::thread::hardware_concurrency();
@@ -98,8 +110,16 @@ extern "C" aslam_status aslam_replay_generate(const double* lm_x, const double* 
         pool.emplace_back([=]() {
             for (uint32_t b = t; b < batch; b += nt)
                 one_filter(lm_x, lm_y, L, batch, steps, warm, vx, az, seed0 + first_filter + b, b, ox, oy, yaw, ovx,
-                           oaz, dt, range, bearing);
+                           oaz, dt, range, bearing, qw, qz);
         });
     for (auto& th : pool) th.join();
     return ASLAM_OK;
+}
+
+extern "C" aslam_status aslam_replay_generate(const double* lm_x, const double* lm_y, uint32_t L, uint32_t batch,
+                                              uint32_t steps, uint32_t warm, double vx, double az, uint64_t seed0,
+                                              uint32_t first_filter, double* ox, double* oy, float* yaw,
+                                              double* ovx, double* oaz, float* dt, float* range, float* bearing) {
+    return aslam_replay_generate_quat(lm_x, lm_y, L, batch, steps, warm, vx, az, seed0, first_filter, ox, oy, yaw,
+                                      ovx, oaz, dt, range, bearing, nullptr, nullptr);
 }

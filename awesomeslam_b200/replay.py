@@ -55,10 +55,16 @@ class Replay:
         self.dt = np.zeros((steps, batch), np.float32)
         self.range = np.zeros((steps, batch, L), np.float32)
         self.bearing = np.zeros((steps, batch, L), np.float32)
+        # orientation quaternion (w, 0, 0, z) of each odometry message; yaw = quat2euler of it (tools.h:62-66)
+        self.qw = np.zeros((steps, batch), np.float64)
+        self.qz = np.zeros((steps, batch), np.float64)
         p = capi.ptr
-        capi.check(capi.lib().aslam_replay_generate(
+        st = capi.host_lib().aslam_replay_generate_quat(
             p(lm_x), p(lm_y), L, batch, steps, warm, vx, az, seed0, first_filter,
-            p(self.x), p(self.y), p(self.yaw), p(self.vx), p(self.az), p(self.dt), p(self.range), p(self.bearing)))
+            p(self.x), p(self.y), p(self.yaw), p(self.vx), p(self.az), p(self.dt), p(self.range), p(self.bearing),
+            p(self.qw), p(self.qz))
+        if st != capi.ASLAM_OK:
+            raise capi.AslamError(st, "aslam_replay_generate_quat: bad arguments")
 
     def odom_arrays(self):
         return self.x, self.y, self.yaw, self.vx, self.az, self.dt

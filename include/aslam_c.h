@@ -311,6 +311,15 @@ aslam_status aslam_replay_generate(const double* lm_x, const double* lm_y, uint3
                                    uint32_t steps, uint32_t warm, double vx, double az, uint64_t seed0,
                                    uint32_t first_filter, double* ox, double* oy, float* yaw, double* ovx,
                                    double* oaz, float* dt, float* range, float* bearing);
+/* The same replay, additionally returning the orientation quaternion (w, 0, 0, z) of every odometry message
+ * (qw, qz: double [steps][batch], may be null) -- what nav_msgs/Odometry carries and ekf.cpp:141 feeds to
+ * quat2euler; `yaw` is aslam_quat2euler(qw, 0, 0, qz). Both entry points are also built into the host-only
+ * library awesomeslam_b200/lib/libaslam_host.so (no CUDA), together with aslam_quat2euler. */
+aslam_status aslam_replay_generate_quat(const double* lm_x, const double* lm_y, uint32_t L, uint32_t batch,
+                                        uint32_t steps, uint32_t warm, double vx, double az, uint64_t seed0,
+                                        uint32_t first_filter, double* ox, double* oy, float* yaw, double* ovx,
+                                        double* oaz, float* dt, float* range, float* bearing, double* qw,
+                                        double* qz);
 
 #ifdef __cplusplus
 }

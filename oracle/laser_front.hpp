@@ -223,18 +223,26 @@ inline int laser_extract(const LaserConfig& cfg, const float* ranges, float* out
             sin_map.push_back(std::sin(cfg.deg2rad * static_cast<float>(th)));
             cos_map.push_back(std::cos(cfg.deg2rad * static_cast<float>(th)));
         }
-    auto pose = [&](int th) {  // bearing2pose (:136-142)
-        const float x = ranges[th] * cos_map[th];
-        const float y = ranges[th] * sin_map[th];
+    auto pose = [&](int th, int tab) {  // bearing2pose (:136-142) of ray th with table entry tab
+        const float c = tab < 360 ? cos_map[tab] : 0.0f, s = tab < 360 ? sin_map[tab] : 0.0f;
+        const float x = ranges[th] * c;
+        const float y = ranges[th] * s;
         return LPoint{x, y};
     };
-    LPoint p1 = pose(0), p2 = pose(359);
+    // (:87,98) `bearing2pose(theta, msg->ranges[theta++])`: the evaluation order of the two arguments is
+    // unspecified, and GCC -- the compiler of every ROS build and of oracle/_ref, which pins this -- takes them
+    // right to left: ray t is projected with table entry t + 1 (a +1 degree rotation of every cluster and of the
+    // published bearings), and ray 359 with entry 360, one past the table, read as 0.0f (fresh heap; oracle/_ref
+    // sets it). The wrap test (:63-64) has no side effect in its arguments and uses entries 0 and 359.
+    LPoint p1 = pose(0, 0), p2 = pose(359, 359);
     if (laser_distance(p1, p2) < cfg.min_dist_thresh) return -1;
     int theta = 0, count = 0;
-    p1 = pose(theta++);
+    p1 = pose(theta, theta + 1);
+    ++theta;
     std::vector<LPoint> cluster = {p1};
     while (theta < 360) {
-        p2 = pose(theta++);
+        p2 = pose(theta, theta + 1);
+        ++theta;
         if (laser_distance(p1, p2) < cfg.min_dist_thresh) {
             cluster.push_back(p2);
         } else if ((int)cluster.size() > cfg.min_cluster_points && circle_classification(cfg, cluster)) {

@@ -556,11 +556,19 @@ def laser_extract(ranges):
     the reference's assert(theta < 359) fires."""
     sin_map, cos_map = _laser_tables()
     with np.errstate(all="ignore"):
-        px = (ranges.astype(np.float32) * cos_map).astype(np.float32)
-        py = (ranges.astype(np.float32) * sin_map).astype(np.float32)
-        pts = list(zip(px, py))
-        if _ldist(pts[0], pts[359]) < _F(0.5):
+        r32 = ranges.astype(np.float32)
+        # wrap test (:63-64): rays 0 and 359 with their own table entries
+        w0 = (_F(r32[0] * cos_map[0]), _F(r32[0] * sin_map[0]))
+        w359 = (_F(r32[359] * cos_map[359]), _F(r32[359] * sin_map[359]))
+        if _ldist(w0, w359) < _F(0.5):
             return None
+        # (:87,98) bearing2pose(theta, ranges[theta++]) as GCC evaluates it (right to left): ray t uses table entry
+        # t + 1; entry 360 lies one past the table and reads 0.0f (see oracle/laser_front.hpp, pinned by oracle/_ref)
+        cs = np.concatenate([cos_map[1:], np.zeros(1, np.float32)]).astype(np.float32)
+        sn = np.concatenate([sin_map[1:], np.zeros(1, np.float32)]).astype(np.float32)
+        px = (r32 * cs).astype(np.float32)
+        py = (r32 * sn).astype(np.float32)
+        pts = list(zip(px, py))
         out, cluster, p1 = [], [pts[0]], pts[0]
         for th in range(1, 360):
             p2 = pts[th]

@@ -29,3 +29,12 @@ def aslam():
         build.build_library()
     awesomeslam_b200.capi.lib()
     return awesomeslam_b200
+
+
+@pytest.fixture(scope="session")
+def aslam_host():
+    """The package for HOST-side input generation only (maps, replay generator: lib/libaslam_host.so, no CUDA)."""
+    import awesomeslam_b200
+    from awesomeslam_b200 import build
+    build.build_host_lib()
+    return awesomeslam_b200

@@ -110,7 +110,8 @@ def test_laser_to_filter_pipeline(aslam, orc):
     Xo, Zo, Po = o.state()
     assert st["N"] == o.N == 3 + 2 * n and st["status"] == 0
     assert np.max(np.abs(st["X"] - Xo[:st["N"]])) <= 1e-5  # float-level differences of the observations, 14 updates
-    # the mapped cylinders sit where the world has them (robot pose known from odometry)
+    # the mapped cylinders sit where the world has them (robot pose known from odometry), up to the +1 degree rotation
+    # the reference's front end applies to every bearing (sensor_landmark.cpp:87,98 as GCC evaluates it: 0.035 m at 2 m)
     for l in range(n):
         d = np.hypot(np.array(lmx) - st["X"][3 + 2 * l], np.array(lmy) - st["X"][4 + 2 * l])
         assert d.min() < 0.08
