@@ -18,6 +18,7 @@ ASLAM_ERR_ARG = -1
 ASLAM_ERR_CUDA = -2
 ASLAM_ERR_UNSUPPORTED = -3
 ASLAM_ERR_NOT_READY = -4
+ASLAM_ERR_TIMEOUT = -5
 
 ST_CAP_REJECTED = 1 << 0
 ST_LLT_FAILED = 1 << 1
@@ -95,6 +96,7 @@ SIGNATURES = {
     "aslam_filter_get_llt_fail": (_i32, [_vp, _vp]),
     "aslam_filter_device_state": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "aslam_filter_load_state": (_i32, [_vp, _vp, _vp, _vp, _vp]),
+    "aslam_filter_load_aux": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "aslam_filter_launch_count": (C.c_uint64, [_vp]),
     "aslam_large_ekf_create": (_i32, [C.POINTER(Config), _u32, _u32, _u32, _i32, C.POINTER(_vp)]),
     "aslam_large_ukf_create": (_i32, [C.POINTER(Config), _u32, _i32, C.POINTER(_vp)]),
@@ -121,6 +123,8 @@ SIGNATURES = {
     "aslam_large_peer_attach": (_i32, [_vp, _u32, _u32, _vp, C.POINTER(_vp)]),
     "aslam_large_step_fused": (_i32, [_vp, _f64, _f64, _f32, _f64, _f64, _f32, _vp, _vp, _u32, _vp]),
     "aslam_large_launch_count": (C.c_uint64, [_vp]),
+    "aslam_large_set_timing": (_i32, [_vp, _i32]),
+    "aslam_large_trace": (_i32, [_vp, _vp]),
     "aslam_large_last_kernel_ms": (_i32, [_vp, C.POINTER(_f32)]),
     "aslam_large_status": (_i32, [_vp, C.POINTER(_u32), C.POINTER(_i32)]),
     "aslam_dense_gemm_nt": (_i32, [_vp, _i32, _i32, _i32, _vp, _sz, _vp, _sz, _vp, _sz, _f64, _f64, _i32]),
@@ -160,11 +164,12 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = os.environ.get("ASLAM_B200_LIB", LIB_PATH)  # experiments: another build of the same library
+    if not os.path.exists(path):
         raise ImportError(
             "%s is missing: build it with `python -m awesomeslam_b200.build` "
-            "(there is no CPU implementation behind this package)" % LIB_PATH)
-    l = C.CDLL(LIB_PATH)
+            "(there is no CPU implementation behind this package)" % path)
+    l = C.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(l, name)
         fn.restype = res

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -400,6 +401,11 @@ aslam_status aslam_filter_set_observations(aslam_filter* h, const float* range, 
     const uint32_t B = h->st.batch;
     const size_t total = offsets[B];
     if (total && (!range || !bearing)) return ASLAM_ERR_ARG;
+    for (uint32_t b = 0; b < B; ++b)  // the kernels take offsets[f+1] - offsets[f] as a count: it must not wrap
+        if (offsets[b] > offsets[b + 1]) {
+            set_error("set_observations: offsets must be non-decreasing");
+            return ASLAM_ERR_ARG;
+        }
     if (total > h->obs_capacity) {
         ASLAM_CUDA(cudaStreamSynchronize(h->stream));
         if (h->d_range) cudaFree(h->d_range);
@@ -509,9 +515,30 @@ aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const asla
     in.offsets = nullptr;
     in.obs_per_filter = obs_per_filter;
     in.assoc = h->d_assoc;
-    in.steps = steps;
-    rc = run_kernel(h, in);
-    if (rc != ASLAM_OK) return rc;
+    // The kernels index a message's observations with 32-bit offsets from `range` / `bearing`
+    // (step * batch * obs_per_filter + ...): a replay longer than 2^32 observations is cut into launches that each
+    // stay below it, with the pointers advanced on the host (same results: the state carries over in HBM).
+    const size_t max_steps = total ? (size_t)0xffffffffu / total : (size_t)steps;
+    if (max_steps == 0) {
+        set_error("run: batch * obs_per_filter exceeds 2^32 observations per message");
+        return ASLAM_ERR_UNSUPPORTED;
+    }
+    for (uint32_t s0 = 0; s0 < steps;) {
+        const uint32_t ns = (uint32_t)std::min<size_t>(steps - s0, max_steps);
+        const size_t mo = (size_t)s0 * h->st.batch;
+        in.ox = o->x + mo;
+        in.oy = o->y + mo;
+        in.yaw = o->yaw + mo;
+        in.vx = o->vx + mo;
+        in.az = o->az + mo;
+        in.dt = o->dt + mo;
+        in.range = d_range ? d_range + (size_t)s0 * total : nullptr;
+        in.bearing = d_bearing ? d_bearing + (size_t)s0 * total : nullptr;
+        in.steps = ns;
+        rc = run_kernel(h, in);
+        if (rc != ASLAM_OK) return rc;
+        s0 += ns;
+    }
     // the last message stays "current" (ekf.cpp:105: the list persists until replaced)
     h->cur_range = d_range + (size_t)(steps - 1) * total;
     h->cur_bearing = d_bearing + (size_t)(steps - 1) * total;
@@ -682,6 +709,55 @@ aslam_status aslam_filter_load_state(aslam_filter* h, const uint32_t* N, const d
     batch_transpose_kernel<<<(unsigned)B, 128, 0, h->stream>>>(h->d_scratch, h->st.P, (uint32_t)ld);
     ASLAM_CUDA(cudaGetLastError());
     ASLAM_CUDA(cudaMemsetAsync(h->st.flags, 0, B * sizeof(uint32_t), h->stream));
+    // everything else that outlives a message is put back to its initial value, so that nothing of a previous run
+    // leaks into the loaded state: empty wait-list, A = I (ekf.cpp:60), no status bits, no LLT failure
+    ASLAM_CUDA(cudaMemsetAsync(h->st.wcount, 0, B * sizeof(uint32_t), h->stream));
+    ASLAM_CUDA(cudaMemsetAsync(h->st.status, 0, B * sizeof(uint32_t), h->stream));
+    ASLAM_CUDA(cudaMemsetAsync(h->st.llt_fail, 0xff, B * sizeof(int32_t), h->stream));
+    if (h->st.A) {
+        std::vector<double> a(2 * B);
+        for (size_t b = 0; b < B; ++b) {
+            a[2 * b] = 1.0;
+            a[2 * b + 1] = 0.0;
+        }
+        ASLAM_CUDA(cudaMemcpyAsync(h->st.A, a.data(), 2 * B * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_filter_load_aux(aslam_filter* h, const double* a00, const double* a10, const uint32_t* wcount,
+                                   const float* wrange, const float* wbearing, const uint32_t* whits,
+                                   const uint32_t* status) {
+    if (!h) return ASLAM_ERR_ARG;
+    if ((a00 == nullptr) != (a10 == nullptr)) return ASLAM_ERR_ARG;
+    if (wcount && (!wrange || !wbearing || !whits)) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    const size_t B = h->st.batch;
+    if (a00 && h->st.A) {
+        std::vector<double> a(2 * B);
+        for (size_t b = 0; b < B; ++b) {
+            a[2 * b] = a00[b];
+            a[2 * b + 1] = a10[b];
+        }
+        ASLAM_CUDA(cudaMemcpyAsync(h->st.A, a.data(), 2 * B * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    if (wcount) {
+        for (size_t b = 0; b < B; ++b)
+            if (wcount[b] > ASLAM_MAX_WAIT) {
+                set_error("load_aux: wait-list longer than ASLAM_MAX_WAIT");
+                return ASLAM_ERR_ARG;
+            }
+        const size_t W = (size_t)ASLAM_MAX_WAIT;
+        ASLAM_CUDA(cudaMemcpyAsync(h->st.wcount, wcount, B * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(h->st.wrange, wrange, B * W * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(h->st.wbearing, wbearing, B * W * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(h->st.whits, whits, B * W * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    }
+    if (status)
+        ASLAM_CUDA(cudaMemcpyAsync(h->st.status, status, B * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     ASLAM_CUDA(cudaStreamSynchronize(h->stream));
     return ASLAM_OK;
 }

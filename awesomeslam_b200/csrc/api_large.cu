@@ -13,8 +13,8 @@
 
 namespace aslam {
 aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m,
-                              bool peer = false);
-aslam_status large_ekf_phase2(aslam_large* h, bool peer = false);
+                              int mode);
+aslam_status large_ekf_phase2(aslam_large* h);
 aslam_status large_ukf_create(aslam_large* h);
 void large_ukf_destroy(aslam_large* h);
 aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m);
@@ -65,6 +65,8 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
     A((void**)&h->P, (size_t)n * h->ldp * sizeof(double));
     A((void**)&h->X, (size_t)n * sizeof(double));
     A((void**)&h->A, 2 * sizeof(double));
+    A((void**)&h->predA, 2 * sizeof(double));
+    A((void**)&h->sync, 4 * sizeof(unsigned long long));
     A((void**)&h->ctx, sizeof(LargeCtx));
     A((void**)&h->d_obs, 2 * ASLAM_MAX_OBS * sizeof(float));
     if (kind == ASLAM_KIND_EKF) {
@@ -83,6 +85,7 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
         if (!cuda_ok(cudaMemsetAsync(h->P, 0, (size_t)n * h->ldp * sizeof(double), h->stream), "init P")) rc = ASLAM_ERR_CUDA;
         if (!cuda_ok(cudaMemsetAsync(h->X, 0, (size_t)n * sizeof(double), h->stream), "init X")) rc = ASLAM_ERR_CUDA;
         if (!cuda_ok(cudaMemsetAsync(h->ctx, 0, sizeof(LargeCtx), h->stream), "init ctx")) rc = ASLAM_ERR_CUDA;
+        if (!cuda_ok(cudaMemsetAsync(h->sync, 0, 4 * sizeof(unsigned long long), h->stream), "init sync")) rc = ASLAM_ERR_CUDA;
         if (!cuda_ok(cudaStreamSynchronize(h->stream), "init sync")) rc = ASLAM_ERR_CUDA;
     }
     if (rc == ASLAM_OK && kind == ASLAM_KIND_UKF) rc = large_ukf_create(h);
@@ -90,7 +93,12 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
         aslam_large_destroy(h);
         return rc;
     }
-    h->timed = std::getenv("ASLAM_LARGE_NO_TIMING") == nullptr;
+    h->timed = kind == ASLAM_KIND_UKF;  // EKF: opt-in (aslam_large_set_timing)
+    if (kind == ASLAM_KIND_EKF && std::getenv("ASLAM_LARGE_TRACE")) {
+        if (cudaMalloc((void**)&h->trace, 64 * 16 * sizeof(unsigned long long)) != cudaSuccess) h->trace = nullptr;
+        if (h->trace) cudaMemset(h->trace, 0, 64 * 16 * sizeof(unsigned long long));
+    }
+    h->pdl = std::getenv("ASLAM_LARGE_NO_PDL") == nullptr;  // diagnostic switch, same kernels either way
     *out = h;
     return ASLAM_OK;
 }
@@ -98,19 +106,20 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
 // EKF handles stage the observations on the side stream (the front kernel that reads them runs there), behind the
 // event that says the previous step no longer needs the context / observation buffers.
 aslam_status stage_obs(aslam_large* h, const float* range, const float* bearing, uint32_t m) {
-    cudaStream_t st = h->stream;
-    if (h->kind == ASLAM_KIND_EKF) {
-        st = h->side;
-        ASLAM_CUDA(cudaStreamWaitEvent(st, h->ev_ctx_free, 0));
-    }
     if (m > ASLAM_MAX_OBS) {
         set_error("large step: more than ASLAM_MAX_OBS observations in one message");
         return ASLAM_ERR_ARG;
     }
     if (m && (!range || !bearing)) return ASLAM_ERR_ARG;
-    if (m) {
-        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs, range, m * sizeof(float), cudaMemcpyHostToDevice, st));
-        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs + ASLAM_MAX_OBS, bearing, m * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (h->kind == ASLAM_KIND_EKF) {  // the EKF front kernel takes the observations in its arguments
+        for (uint32_t i = 0; i < m; ++i) {
+            h->obs_host[i] = range[i];
+            h->obs_host[ASLAM_MAX_OBS + i] = bearing[i];
+        }
+    } else if (m) {
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs, range, m * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        ASLAM_CUDA(cudaMemcpyAsync(h->d_obs + ASLAM_MAX_OBS, bearing, m * sizeof(float), cudaMemcpyHostToDevice,
+                                   h->stream));
     }
     h->m_last = m;
     return ASLAM_OK;
@@ -148,7 +157,7 @@ aslam_status aslam_large_destroy(aslam_large* h) {
     if (h->side) cudaStreamDestroy(h->side);
     for (int p = 0; p < LARGE_MAX_PEERS; ++p)
         if (h->peer_ipc[p] && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
-    void* ptrs[] = {h->P, h->X, h->A, h->ctx, h->d_obs, h->exch, h->hp, h->K, h->peer_block};
+    void* ptrs[] = {h->P, h->X, h->A, h->predA, h->sync, h->trace, h->ctx, h->d_obs, h->exch, h->hp, h->K, h->peer_block};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -206,11 +215,7 @@ aslam_status aslam_large_step(aslam_large* h, double x, double y, float yaw, dou
         if (rc != ASLAM_OK) return rc;
         return fetch_assoc(h, assoc_out);
     }
-    if (h->row_begin != 0 || h->row_end != h->n) {
-        set_error("large step: a sharded handle must use step_phase1 / exchange / step_phase2");
-        return ASLAM_ERR_UNSUPPORTED;
-    }
-    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m);
+    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m, LARGE_STEP_DIRECT);
     if (rc != ASLAM_OK) return rc;
     rc = large_ekf_phase2(h);
     if (rc != ASLAM_OK) return rc;
@@ -223,7 +228,7 @@ aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float y
     ASLAM_CUDA(cudaSetDevice(h->device));
     aslam_status rc = stage_obs(h, range, bearing, m);
     if (rc != ASLAM_OK) return rc;
-    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m);
+    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m, LARGE_STEP_EXCH);
     if (q_out) *q_out = h->q_host;
     return rc;
 }
@@ -231,7 +236,8 @@ aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float y
 aslam_status aslam_large_exchange_buffer(aslam_large* h, double** d_buf, size_t* count) {
     if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
     if (d_buf) *d_buf = h->exch;
-    if (count) *count = (size_t)2 * h->q_host * h->n;
+    // q <= 20: (P H_o') slices [q][n] + the q x q block (padded to 20 x 20); larger q: raw rows + slices (round 1)
+    if (count) *count = h->q_host <= 20 ? (size_t)h->q_host * h->n + 400 : (size_t)2 * h->q_host * h->n;
     return ASLAM_OK;
 }
 
@@ -295,6 +301,15 @@ aslam_status aslam_large_peer_attach(aslam_large* h, uint32_t world, uint32_t ra
             h->peer_base[p] = static_cast<unsigned char*>(ptr);
             h->peer_ipc[p] = true;
         }
+        // A peer shard on the SAME device (several handles of one test process on one GPU): its solve kernel must find
+        // room while this handle's kernels wait for it, so the streaming update is not made resident early (see
+        // large_ekf_phase2_fast).
+        if (p != rank) {
+            cudaPointerAttributes pa{};
+            if (cudaPointerGetAttributes(&pa, h->peer_base[p]) == cudaSuccess && pa.device == h->device)
+                h->peer_same_device = true;
+            cudaGetLastError();
+        }
     }
     h->peer_world = world;
     h->peer_rank = rank;
@@ -308,11 +323,28 @@ aslam_status aslam_large_step_fused(aslam_large* h, double x, double y, float ya
     ASLAM_CUDA(cudaSetDevice(h->device));
     aslam_status rc = stage_obs(h, range, bearing, m);
     if (rc != ASLAM_OK) return rc;
-    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m, true);
+    rc = large_ekf_phase1(h, x, y, yaw, vx, az, dt, m, LARGE_STEP_PEER);
     if (rc != ASLAM_OK) return rc;
-    rc = large_ekf_phase2(h, true);
+    rc = large_ekf_phase2(h);
     if (rc != ASLAM_OK) return rc;
     return fetch_assoc(h, assoc_out);
+}
+
+/* diagnostics: copies the [64][8] timeline of the last 64 steps (ASLAM_LARGE_TRACE=1), else ASLAM_ERR_UNSUPPORTED */
+aslam_status aslam_large_trace(aslam_large* h, unsigned long long* out1024) {
+    if (!h || !out1024) return ASLAM_ERR_ARG;
+    if (!h->trace) return ASLAM_ERR_UNSUPPORTED;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    ASLAM_CUDA(cudaStreamSynchronize(h->side));
+    ASLAM_CUDA(cudaStreamSynchronize(h->stream));
+    ASLAM_CUDA(cudaMemcpy(out1024, h->trace, 64 * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return ASLAM_OK;
+}
+
+aslam_status aslam_large_set_timing(aslam_large* h, int32_t on) {
+    if (!h) return ASLAM_ERR_ARG;
+    h->timed = on != 0;
+    return ASLAM_OK;
 }
 
 aslam_status aslam_large_last_kernel_ms(aslam_large* h, float* ms) {
@@ -326,12 +358,18 @@ aslam_status aslam_large_status(aslam_large* h, uint32_t* status, int32_t* llt_f
     if (!h) return ASLAM_ERR_ARG;
     ASLAM_CUDA(cudaSetDevice(h->device));
     if (h->kind == ASLAM_KIND_UKF) return large_ukf_status(h, status, llt_fail);
-    if (status) {
-        ASLAM_CUDA(cudaMemcpyAsync(status, (const char*)h->ctx + offsetof(LargeCtx, status), sizeof(uint32_t),
+    uint32_t st = 0;
+    {
+        ASLAM_CUDA(cudaMemcpyAsync(&st, (const char*)h->ctx + offsetof(LargeCtx, status), sizeof(uint32_t),
                                    cudaMemcpyDeviceToHost, h->stream));
         ASLAM_CUDA(cudaStreamSynchronize(h->stream));
     }
+    if (status) *status = st;
     if (llt_fail) *llt_fail = -1;
+    if (st & ASLAM_ST_PEER_TIMEOUT) {
+        set_error("large step: a peer's rows did not arrive within the spin bound; that step applied the predict only");
+        return ASLAM_ERR_TIMEOUT;
+    }
     return ASLAM_OK;
 }
 

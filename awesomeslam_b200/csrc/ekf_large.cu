@@ -7,16 +7,16 @@
 // A = I except A(0,0), A(1,0) (ekf.cpp:210-211) and H_o has <= 5 non-zeros per row, so everything
 // but the last product is O(q n); the last one streams P once: read + write 2*8*n^2 bytes.
 //
-// Kernels, in launch order
-//   large_front_kernel    1 CTA   association (float math, first-minimum ties), pose predict, A, H_o, y
-//   large_predict_kernel  n thr   P = A P A' + Q on rows/cols 0,1 (ekf.cpp:297)
-//   large_gather_kernel   n thr   raw rows rows[k] of P and the local slice of P H_o'  -> exchange buffer
-//   (sharded: the caller sums the exchange buffers of all ranks; every element has one owner)
-//   large_gain_kernel             S, S^-1 (per CTA, in smem), H_o P, K, X += K y
-//   large_update_kernel           P_local -= K_local (H_o P): the HBM-bound streaming kernel
+// Kernels of the path cfg4 takes (q <= 20), in launch order
+//   large_front_kernel      1 CTA, side stream, under the previous step's update: association (float math,
+//                           first-minimum ties), pose predict, A, H_o, y
+//   large_solve_kernel      gather of the q rows / columns of P (with the predict P = A P A' + Q applied on the fly),
+//                           exchange over peer memory when sharded, S, S^-1 (one warp, in registers), H_o P, K, X += K y
+//   large_update_ws_kernel  P_local -= K_local (H_o P): the HBM-bound streaming kernel, predict fused into the tiles,
+//                           launched with programmatic stream serialization behind the solve kernel
+// 20 < q <= 131 (more than 8 observed landmarks; no BASELINE config) keeps the round-1 chain
+//   large_predict_kernel -> large_gather[_fast]_kernel -> large_gain[_fast]_kernel -> large_update_{bulk,generic}_kernel
 #include <cuda_runtime.h>
-
-#include <cstdlib>
 
 #include "bulk_copy.cuh"
 #include "device_math.cuh"
@@ -41,10 +41,74 @@ struct FrontArgs {
     uint32_t q_ub;  // 3 + 2 m: rows the exchange / gain buffers are laid out for
     float pi, thresh;
     double kr_pose, kr_lm;
+    unsigned long long epoch;  // 1-based index of this step on the handle
+    // the message's observations travel in the kernel arguments: no staging copy in front of the launch
+    float range[ASLAM_MAX_OBS], bearing[ASLAM_MAX_OBS];
 };
 
-__global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t n, double* X, double* A,
-                                                          const float* obs, LargeCtx* ctx) {
+// Ordering between the kernels of consecutive steps that run on different streams (the front of step k+1 runs on the
+// side stream UNDER the streaming update of step k) is carried by two counters in device memory instead of CUDA
+// events: an event recorded between the solve kernel and the update would sit between the two launches and keep the
+// update from being launched programmatically behind the solve kernel.
+//   sync[SYNC_FRONT]  = k once the front of step k has written the context, A and the predicted pose
+//   sync[SYNC_SOLVE]  = k once the solve (or gain) kernel of step k has finished with the context and has written X
+//   sync[SYNC_COUNT]  : arrival counter of the solve CTAs of the step in flight
+// Every waiter was enqueued after the kernel it waits for, so the spin always terminates; it is bounded anyway.
+enum { SYNC_FRONT = 0, SYNC_SOLVE = 1, SYNC_COUNT = 2, SYNC_WORDS = 4 };
+
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// One thread: wait until *p >= target. Returns false when the bound expires.
+__device__ __forceinline__ bool spin_until(const unsigned long long* p, unsigned long long target) {
+    for (int it = 0; it < 8000000; ++it) {
+        if (ld_acquire_gpu(p) >= target) return true;
+        __nanosleep(64);
+    }
+    return false;
+}
+
+// Optional timeline (ASLAM_LARGE_TRACE=1, diagnostics only): %globaltimer stamps of the kernels of each step,
+// slot = (step % TRACE_STEPS) * 8 + {0 front begin, 1 front end, 2 solve first CTA in, 3 solve last CTA out,
+// 4 first update CTA past its wait, 5 last update CTA out, 6 first update CTA in}.
+constexpr int TRACE_STEPS = 64;
+__device__ __forceinline__ unsigned long long globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_min(unsigned long long* tr, unsigned long long epoch, int slot) {
+    if (tr) atomicMin(tr + (epoch % TRACE_STEPS) * 16 + slot, globaltimer());
+}
+// phase stamps of CTA 0 of the solve kernel: slots 8..15
+__device__ __forceinline__ void trace_mark(unsigned long long* tr, unsigned long long epoch, int slot) {
+    if (tr && blockIdx.x == 0 && threadIdx.x == 0) tr[(epoch % TRACE_STEPS) * 16 + slot] = globaltimer();
+}
+__device__ __forceinline__ void trace_max(unsigned long long* tr, unsigned long long epoch, int slot) {
+    if (tr) atomicMax(tr + (epoch % TRACE_STEPS) * 16 + slot, globaltimer());
+}
+
+constexpr int FRONT_THREADS = 256;  // small enough to be co-resident with the streaming update (158 regs x 288 threads)
+
+__global__ void __launch_bounds__(FRONT_THREADS) large_front_kernel(FrontArgs a, uint32_t n, double* X, double* A,
+                                                                   LargeCtx* ctx, unsigned long long* sync,
+                                                                   unsigned long long* trace) {
+    constexpr int NW = FRONT_THREADS / 32;
+    if (threadIdx.x == 0 && trace) {
+        unsigned long long* sl = trace + (a.epoch % TRACE_STEPS) * 16;
+        sl[0] = globaltimer();
+        sl[2] = ~0ull; sl[3] = 0; sl[4] = ~0ull; sl[5] = 0; sl[6] = ~0ull;
+    }
+    if (sync) {  // X of the previous step must be final and its context no longer in use
+        if (threadIdx.x == 0 && !spin_until(sync + SYNC_SOLVE, a.epoch - 1))
+            atomicOr(&ctx->status, (uint32_t)ASLAM_ST_STEP_TIMEOUT);
+        __syncthreads();
+    }
     __shared__ float s_nb[ASLAM_MAX_OBS];
     __shared__ int s_corr[ASLAM_MAX_OBS];
     __shared__ float s_mind[ASLAM_MAX_OBS];
@@ -58,20 +122,22 @@ __global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t
     // every thread keeps a few landmarks in registers and scans all observations against them: one pass over X,
     // one round of warp reductions, one CTA barrier, one final reduction per observation.
     __shared__ float2 s_pt[ASLAM_MAX_OBS];
-    __shared__ unsigned long long s_red[ASLAM_MAX_OBS][32];
+    __shared__ unsigned long long s_red[ASLAM_MAX_OBS][NW];
     if (tid < (int)a.m) {
-        const float b = normalize_angle(obs[ASLAM_MAX_OBS + tid], a.pi);  // ekf.cpp:150
+        const float b = normalize_angle(a.bearing[tid], a.pi);  // ekf.cpp:150
         s_nb[tid] = b;
-        s_pt[tid] = to_point(obs[tid], b, z0, z1, z2);
+        s_pt[tid] = to_point(a.range[tid], b, z0, z1, z2);
     }
     __syncthreads();
     constexpr int LPT = 4;  // landmarks per thread and pass
-    for (uint32_t o = 0; o < a.m; ++o) s_red[o][warp] = ~0ull;
-    for (uint32_t l0 = 0; l0 < L; l0 += 1024 * LPT) {
+    if (lane == 0)
+        for (uint32_t o = 0; o < a.m; ++o) s_red[o][warp] = ~0ull;
+    __syncwarp();
+    for (uint32_t l0 = 0; l0 < L; l0 += FRONT_THREADS * LPT) {
         float lx[LPT], ly[LPT];
 #pragma unroll
         for (int u = 0; u < LPT; ++u) {
-            const uint32_t l = l0 + u * 1024 + tid;
+            const uint32_t l = l0 + u * FRONT_THREADS + tid;
             lx[u] = l < L ? (float)X[3 + 2 * l] : 0.0f;
             ly[u] = l < L ? (float)X[4 + 2 * l] : 0.0f;
         }
@@ -80,7 +146,7 @@ __global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t
             unsigned long long best = ~0ull;
 #pragma unroll
             for (int u = 0; u < LPT; ++u) {
-                const uint32_t l = l0 + u * 1024 + tid;
+                const uint32_t l = l0 + u * FRONT_THREADS + tid;
                 if (l < L) {
                     const float d = euler_distance(pt.x, pt.y, lx[u], ly[u]);
                     // d >= 0: its bit pattern orders like the value; the low word breaks ties toward the
@@ -93,8 +159,8 @@ __global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t
         }
     }
     __syncthreads();
-    for (uint32_t o = warp; o < a.m; o += 32) {
-        unsigned long long best = s_red[o][lane];
+    for (uint32_t o = warp; o < a.m; o += NW) {
+        unsigned long long best = lane < NW ? s_red[o][lane] : ~0ull;
         for (int off = 16; off; off >>= 1) best = umin64(best, __shfl_xor_sync(0xffffffffu, best, off));
         if (lane == 0) {
             s_corr[o] = (int)(best & 0xffffffffu) * 2;  // corr_id counts state entries (ekf.cpp:170)
@@ -184,7 +250,7 @@ __global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t
         ctx->rdiag[kb] = a.kr_lm;
         double rg, br;
         measure_landmark(x, y, th, lx, ly, rg, br);
-        ctx->y[kr] = (double)obs[s_ob[c]] - rg;                                          // Z - h(X)
+        ctx->y[kr] = (double)a.range[s_ob[c]] - rg;                                      // Z - h(X)
         ctx->y[kb] = (double)normalize_angle((float)((double)s_nb[s_ob[c]] - br), a.pi);  // ekf.cpp:306
     } else if (tid < (int)a.q_ub + cnt) {  // unused rows q .. q_ub-1: harmless identity padding
         const int k = q + (tid - 3 - cnt);
@@ -195,6 +261,20 @@ __global__ void __launch_bounds__(1024) large_front_kernel(FrontArgs a, uint32_t
             ctx->rdiag[k] = 1.0;
         }
     }
+    if (sync) {  // publish: context, A and the predicted pose of step `epoch` are in place
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            if (trace) trace[(a.epoch % TRACE_STEPS) * 16 + 1] = globaltimer();
+            st_release_gpu(sync + SYNC_FRONT, a.epoch);
+        }
+    }
+}
+
+// Legacy chain (q > 20): marks the step's solve stage as done for the front of the next step.
+__global__ void large_mark_kernel(unsigned long long* sync, unsigned long long epoch) {
+    __threadfence();
+    st_release_gpu(sync + SYNC_SOLVE, epoch);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -640,89 +720,10 @@ __global__ void __launch_bounds__(256) large_gain_fast_kernel(uint32_t n, LargeC
 }
 
 // ------------------------------------------------------------------------------------------
-// K5: P_local -= K_local (H_o P). Thread owns R consecutive rows; its R x Q slice of -K sits in
-// registers for the whole tile. A CTA (256 threads, 256 R rows) walks a range of columns; the
-// Q-vector (H_o P)[:, j] of each column is staged in shared memory and read as a broadcast.
-// Per column and thread: one 16-byte load, R*Q DFMA, one 16-byte store -- P is read once and
-// written once: 16 n^2 bytes per step against 2 q n^2 flop (HBM-bound for q <~ 40).
+// K5: P_local -= K_local (H_o P), the HBM-bound streaming kernel: P is read once and written once, 16 n^2 bytes per
+// step against 2 q n^2 flop (HBM-bound for q <~ 40).
 // ------------------------------------------------------------------------------------------
-template <int R, int Q, int U>
-__global__ void __launch_bounds__(256) large_update_kernel(uint32_t n, uint32_t rb, uint32_t nrows, size_t ldp,
-                                                          double* __restrict__ P, const double* __restrict__ K,
-                                                          const double* __restrict__ hp, uint32_t cols_per_cta) {
-    constexpr int ROWS = 256 * R;
-    constexpr int CW = 64;  // columns staged per smem refill
-    __shared__ __align__(16) double s_hp[CW][Q];
-    const uint32_t rblk = blockIdx.y;
-    const uint32_t i0 = rblk * ROWS + threadIdx.x * R;  // local row
-    const uint32_t c_begin = blockIdx.x * cols_per_cta;
-    const uint32_t c_end = min(n, c_begin + cols_per_cta);
-    double nk[Q][R];
-#pragma unroll
-    for (int k = 0; k < Q; ++k)
-#pragma unroll
-        for (int r = 0; r < R; ++r) nk[k][r] = (i0 + r < nrows) ? -K[(size_t)k * n + rb + i0 + r] : 0.0;
-    const bool full = i0 + R <= nrows;
-    for (uint32_t c0 = c_begin; c0 < c_end; c0 += CW) {
-        const uint32_t cw = min((uint32_t)CW, c_end - c0);
-        __syncthreads();
-        {
-            const double* src = hp + (size_t)c0 * Q;
-            double* dst = &s_hp[0][0];
-            for (uint32_t i = threadIdx.x; i < cw * Q; i += 256) dst[i] = src[i];
-        }
-        __syncthreads();
-        if (i0 >= nrows) continue;
-        double* col = P + (size_t)c0 * ldp + i0;
-        uint32_t jj = 0;
-        if (full) {
-            for (; jj + U <= cw; jj += U) {
-                double v[U][R];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    if constexpr (R == 2) {
-                        const double2 t = __ldcs(reinterpret_cast<const double2*>(col + (size_t)(jj + u) * ldp));
-                        v[u][0] = t.x;
-                        v[u][1] = t.y;
-                    } else {
-#pragma unroll
-                        for (int r = 0; r < R; ++r) v[u][r] = __ldcs(col + (size_t)(jj + u) * ldp + r);
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-#pragma unroll
-                    for (int k = 0; k < Q; k += 2) {
-                        const double2 h = *reinterpret_cast<const double2*>(&s_hp[jj + u][k]);
-#pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            v[u][r] = fma(nk[k][r], h.x, v[u][r]);
-                            v[u][r] = fma(nk[k + 1][r], h.y, v[u][r]);
-                        }
-                    }
-                    if constexpr (R == 2) {
-                        __stcs(reinterpret_cast<double2*>(col + (size_t)(jj + u) * ldp), make_double2(v[u][0], v[u][1]));
-                    } else {
-#pragma unroll
-                        for (int r = 0; r < R; ++r) __stcs(col + (size_t)(jj + u) * ldp + r, v[u][r]);
-                    }
-                }
-            }
-        }
-        for (; jj < cw; ++jj) {  // column tail and the ragged last rows
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if (i0 + r >= nrows) continue;
-                double v = col[(size_t)jj * ldp + r];
-#pragma unroll
-                for (int k = 0; k < Q; ++k) v = fma(nk[k][r], s_hp[jj][k], v);
-                col[(size_t)jj * ldp + r] = v;
-            }
-        }
-    }
-}
-
-// K5, bulk-copy form (the one launched for q <= 40). The covariance tile never passes through
+// K5, bulk-copy form (launched for 20 < q <= 40; q <= 20 takes the warp-specialised kernel below). The covariance tile never passes through
 // registers on its way in or out: one elected thread drives the copy engine (cp.async.bulk, SASS
 // UBLKCP) to pull 256*R rows x CS columns of P -- CS contiguous column segments -- plus the matching
 // CS x Q block of H_o P into one of NST shared-memory stages, the CTA updates the stage in place
@@ -848,94 +849,184 @@ __global__ void __launch_bounds__(256, 1) large_update_bulk_kernel(uint32_t n, u
     if (tid == 0) bulk::wait_group<0>();
 }
 
-// K5, warp-specialised form (default). Same tiles and shared-memory ring as the kernel above, but the copy engine is
-// driven by a dedicated ninth warp, so the 8 consumer warps never meet in a CTA-wide barrier:
+// K5, persistent warp-specialised form (the kernel cfg4 runs). One CTA per SM for the whole launch; the row blocks x
+// column chunks of the local P are laid out as ONE sequence (row-block major) and every CTA takes a contiguous,
+// equally heavy piece of it, so its shared-memory ring never drains between tiles (the round-1 kernel gave each CTA
+// ~10 chunks and paid the ring fill / drain once per CTA: 84 % of the HBM peak).
 //   producer lane : wait done[st] -> bulk-store the stage -> (one chunk later, once that store has been read out of
-//                   shared memory) re-arm full[st] and bulk-load the chunk NST ahead
+//                   shared memory) re-arm full[st] and bulk-load the chunk NST-1 ahead (cp.async.bulk, SASS UBLKCP)
 //   consumer warp : wait full[st] -> update its 64 rows of the stage in place, 4 columns interleaved (8 independent
-//                   DFMA chains per thread instead of 2) -> fence.proxy.async -> arrive on done[st]
-// ncu on the kernel above (profiles/r01_summary.md): 26 % of the samples sat in __syncthreads behind thread 0's 17 bulk
-// instructions per chunk and 37 % in the 20-deep dependent DFMA chains; both are structural and are what this removes.
+//                   DFMA chains per thread) -> fence.proxy.async -> arrive on done[st]
+// Predict: P = A P A' + Q (ekf.cpp:297) has NOT been applied to P in memory on this path (see pred_entry below): the
+// consumer that owns rows 0, 1 / the chunk that holds columns 0, 1 applies it to the stage in shared memory before the
+// rank-q update -- the formulas of large_predict_kernel on the same operands.
+// The local rows are cut into equally high blocks of at most ROWS rows (StreamPlan), so every chunk moves about the
+// same number of bytes and the chunk sequence can simply be dealt out in equal counts.
+// Launched with programmatic stream serialization behind the solve kernel: barrier set-up and the first NST-1 tiles of
+// P (which the solve kernel does not write) are under way before griddepcontrol.wait; K, H_o P and predA are touched
+// only after it AND after the solve stage's completion counter has been seen (the counter makes correctness
+// independent of how the launch was serialized).
 __device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bulk::smem_u32(bar)) : "memory");
 }
 
-template <int R, int Q, int CS, int NST>
-__global__ void __launch_bounds__(288, 1) large_update_ws_kernel(uint32_t n, uint32_t rb, uint32_t nrows, size_t ldp,
-                                                                double* __restrict__ P, const double* __restrict__ K,
-                                                                const double* __restrict__ hp, uint32_t cols_per_cta) {
-    using G = BulkGeo<R, Q, CS, NST>;
+struct StreamPlan {
+    uint32_t n, rb, nrows;   // state dimension, first global row and number of rows of this shard
+    uint32_t nch;            // column chunks per row block: ceil(n / CS)
+    uint32_t nblk;           // row blocks
+    uint32_t blk_rows;       // rows per block (multiple of 16, <= ROWS): the local rows are cut into EQUAL blocks, so
+    uint32_t last_rows;      // that no short block is left over (its chunks would cost a full chunk's latency each)
+};
+
+// Tile geometry of the persistent kernel: CW consumer warps x 32 lanes x R rows per row block, CS columns per chunk.
+// CW = 7 (+ the producer warp = 8 warps, two per SM sub-partition) on purpose: the register file is split four ways, a
+// ninth warp would put three 168-register warps (16,128 of 16,384 registers) on one sub-partition and leave no room
+// there for a warp of any other kernel -- the front of the NEXT step, which is meant to run under this kernel, could
+// then only start when a CTA of this (persistent) grid retires, i.e. at the very end (measured: %globaltimer trace).
+template <int CW, int R, int Q, int CS, int NST>
+struct StreamGeo {
+    static constexpr int ROWS = CW * 32 * R;
+    static constexpr size_t P_BYTES = (size_t)CS * ROWS * sizeof(double);
+    static constexpr size_t H_BYTES = (size_t)CS * Q * sizeof(double);
+    static constexpr size_t STAGE = P_BYTES + H_BYTES;
+    static constexpr size_t SMEM = NST * STAGE + 2 * NST * sizeof(uint64_t) + 16;
+    static constexpr int THREADS = (CW + 1) * 32;
+};
+
+template <int CW, int R, int Q, int CS, int NST>
+__global__ void __launch_bounds__((CW + 1) * 32, 1) large_update_stream_kernel(
+    StreamPlan pl, size_t ldp, double* __restrict__ P, const double* __restrict__ K, const double* __restrict__ hp,
+    const double* __restrict__ predA, double kq, const unsigned long long* sync, unsigned long long epoch,
+    unsigned long long* trace) {
+    using G = StreamGeo<CW, R, Q, CS, NST>;
     static_assert(R == 2 && CS % 4 == 0, "the interleaved inner loop is written for 2 rows x 4 columns");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + NST * G::STAGE);
     uint64_t* done = full + NST;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const uint32_t r0 = blockIdx.y * G::ROWS;
-    const uint32_t rows_here = min((uint32_t)G::ROWS, (uint32_t)ldp - r0);
-    const uint32_t seg_bytes = rows_here * sizeof(double);
-    const uint32_t c_begin = blockIdx.x * cols_per_cta;
-    const uint32_t c_end = min(n, c_begin + cols_per_cta);
-    if (c_begin >= c_end) return;
-    const uint32_t nchunks = (c_end - c_begin + CS - 1) / CS;
+    const uint32_t n = pl.n, rb = pl.rb, nrows = pl.nrows;
+    if (tid == 0) trace_min(trace, epoch, 6);
+    const unsigned long long T = (unsigned long long)pl.nblk * pl.nch;  // chunks, row-block major
+    const uint32_t g_begin = (uint32_t)(T * blockIdx.x / gridDim.x);
+    const uint32_t g_end = (uint32_t)(T * (blockIdx.x + 1) / gridDim.x);
     auto stage_p = [&](int st) { return reinterpret_cast<double*>(smem_raw + st * G::STAGE); };
     auto stage_h = [&](int st) { return reinterpret_cast<double*>(smem_raw + st * G::STAGE + G::P_BYTES); };
+    auto rows_of = [&](uint32_t b) { return b + 1 < pl.nblk ? pl.blk_rows : pl.last_rows; };
 
     if (tid == 0) {
         for (int s = 0; s < NST; ++s) {
             bulk::mbar_init(&full[s], 1);
-            bulk::mbar_init(&done[s], 8);
+            bulk::mbar_init(&done[s], CW);
         }
         bulk::fence_barrier_init();
     }
     __syncthreads();
 
-    if (warp == 8) {  // ---------------- producer
+    if (warp == CW) {  // ---------------- producer
         if (lane != 0) return;
-        auto issue_load = [&](uint32_t chunk) {
-            const int st = chunk % NST;
-            const uint32_t c0 = c_begin + chunk * CS;
-            const uint32_t cw = min((uint32_t)CS, c_end - c0);
+        auto issue_p = [&](uint32_t g) {
+            const int st = (g - g_begin) % NST;
+            const uint32_t b = g / pl.nch, c0 = (g % pl.nch) * CS;
+            const uint32_t cw = min((uint32_t)CS, n - c0);
+            const uint32_t seg_bytes = rows_of(b) * (uint32_t)sizeof(double);
             bulk::mbar_expect_tx(&full[st], cw * seg_bytes + cw * Q * (uint32_t)sizeof(double));
             double* dp = stage_p(st);
             for (uint32_t c = 0; c < cw; ++c)
-                bulk::g2s(dp + c * G::ROWS, P + (size_t)(c0 + c) * ldp + r0, seg_bytes, &full[st]);
+                bulk::g2s(dp + c * G::ROWS, P + (size_t)(c0 + c) * ldp + (size_t)b * pl.blk_rows, seg_bytes, &full[st]);
+        };
+        auto issue_h = [&](uint32_t g) {
+            const int st = (g - g_begin) % NST;
+            const uint32_t c0 = (g % pl.nch) * CS;
+            const uint32_t cw = min((uint32_t)CS, n - c0);
             bulk::g2s(stage_h(st), hp + (size_t)c0 * Q, cw * Q * (uint32_t)sizeof(double), &full[st]);
         };
-        for (uint32_t c = 0; c < (uint32_t)(NST - 1) && c < nchunks; ++c) issue_load(c);
-        for (uint32_t chunk = 0; chunk < nchunks; ++chunk) {
-            const int st = chunk % NST;
-            const uint32_t c0 = c_begin + chunk * CS;
-            const uint32_t cw = min((uint32_t)CS, c_end - c0);
-            bulk::mbar_wait(&done[st], (chunk / NST) & 1u);
+        // P tiles first (independent of the solve kernel), H_o P blocks once it has completed
+        for (uint32_t g = g_begin; g < g_begin + (uint32_t)(NST - 1) && g < g_end; ++g) issue_p(g);
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        spin_until(sync + SYNC_SOLVE, epoch);
+        for (uint32_t g = g_begin; g < g_begin + (uint32_t)(NST - 1) && g < g_end; ++g) issue_h(g);
+        for (uint32_t g = g_begin; g < g_end; ++g) {
+            const uint32_t li = g - g_begin;
+            const int st = li % NST;
+            const uint32_t b = g / pl.nch, c0 = (g % pl.nch) * CS;
+            const uint32_t cw = min((uint32_t)CS, n - c0);
+            const uint32_t seg_bytes = rows_of(b) * (uint32_t)sizeof(double);
+            bulk::mbar_wait(&done[st], (li / NST) & 1u);
             const double* sp = stage_p(st);
-            for (uint32_t c = 0; c < cw; ++c) bulk::s2g(P + (size_t)(c0 + c) * ldp + r0, sp + c * G::ROWS, seg_bytes);
+            for (uint32_t c = 0; c < cw; ++c)
+                bulk::s2g(P + (size_t)(c0 + c) * ldp + (size_t)b * pl.blk_rows, sp + c * G::ROWS, seg_bytes);
             bulk::commit_group();
-            const uint32_t nxt = chunk + NST - 1;  // goes into the stage drained one chunk ago
-            if (nxt < nchunks) {
+            const uint32_t nxt = g + NST - 1;  // goes into the stage drained one chunk ago
+            if (nxt < g_end) {
                 bulk::wait_group_read<1>();
-                issue_load(nxt);
+                issue_p(nxt);
+                issue_h(nxt);
             }
         }
         bulk::wait_group<0>();
+        trace_max(trace, epoch, 5);
         return;
     }
 
     // ---------------- consumers
-    const uint32_t i0 = r0 + tid * R;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (lane == 0) spin_until(sync + SYNC_SOLVE, epoch);
+    __syncwarp();
+    if (tid == 0) trace_min(trace, epoch, 4);
+    double a00 = 1.0, a10 = 0.0;
+    if (predA) {
+        a00 = predA[0];
+        a10 = predA[1];
+    }
     double nk[Q][R];
+    uint32_t cur_b = 0xffffffffu;
+    for (uint32_t g = g_begin; g < g_end; ++g) {
+        const uint32_t li = g - g_begin;
+        const int st = li % NST;
+        const uint32_t b = g / pl.nch, c0 = (g % pl.nch) * CS;
+        const uint32_t cw = min((uint32_t)CS, n - c0);
+        const uint32_t i0 = b * pl.blk_rows + tid * R;  // local index of this thread's first row
+        if (b != cur_b) {                           // this thread's R x Q slice of -K
+            cur_b = b;
 #pragma unroll
-    for (int k = 0; k < Q; ++k)
+            for (int k = 0; k < Q; ++k)
 #pragma unroll
-        for (int r = 0; r < R; ++r) nk[k][r] = (i0 + r < nrows) ? -K[(size_t)k * n + rb + i0 + r] : 0.0;
-    const bool active = (uint32_t)(tid * R) < rows_here;
-
-    for (uint32_t chunk = 0; chunk < nchunks; ++chunk) {
-        const int st = chunk % NST;
-        const uint32_t cw = min((uint32_t)CS, c_end - (c_begin + chunk * CS));
-        bulk::mbar_wait(&full[st], (chunk / NST) & 1u);
+                for (int r = 0; r < R; ++r) nk[k][r] = (i0 + r < nrows) ? -K[(size_t)k * n + rb + i0 + r] : 0.0;
+        }
+        const bool active = (uint32_t)(tid * R) < rows_of(b);
+        const uint32_t g0 = rb + i0;  // global index of rows g0, g0 + 1
+        bulk::mbar_wait(&full[st], (li / NST) & 1u);
         if (active) {
             double* sp = stage_p(st) + tid * R;
             const double* sh = stage_h(st);
+            if (predA) {  // P = A P A' + Q on the part of this thread's two rows that lies in the stage
+                if (c0 == 0) {  // columns 0, 1 are the first two columns of this stage (n >= 5 > 2)
+                    if (g0 >= 2) {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            const double p0 = sp[r], p1 = sp[G::ROWS + r];
+                            sp[r] = p0 * a00;
+                            sp[G::ROWS + r] = p0 * a10 + p1;
+                        }
+                        if (g0 == 2) sp[2 * G::ROWS] += kq;  // P(2,2) += Q(2,2)
+                    } else {  // g0 == 0: the 2 x 2 corner, row pass then column pass
+                        const double p00 = sp[0], p10 = sp[1], p01 = sp[G::ROWS], p11 = sp[G::ROWS + 1];
+                        const double r00 = a00 * p00, r01 = a00 * p01;
+                        const double r10 = a10 * p00 + p10, r11 = a10 * p01 + p11;
+                        sp[0] = r00 * a00 + kq;
+                        sp[G::ROWS] = r00 * a10 + r01;
+                        sp[1] = r10 * a00;
+                        sp[G::ROWS + 1] = r10 * a10 + r11 + kq;
+                    }
+                }
+                if (g0 == 0) {  // rows 0, 1 of every other column
+                    for (uint32_t c = (c0 == 0 ? 2u : 0u); c < cw; ++c) {
+                        const double p0 = sp[c * G::ROWS], p1 = sp[c * G::ROWS + 1];
+                        sp[c * G::ROWS] = a00 * p0;
+                        sp[c * G::ROWS + 1] = a10 * p0 + p1;
+                    }
+                }
+            }
             if (cw == CS) {
 #pragma unroll
                 for (int cg = 0; cg < CS; cg += 4) {
@@ -990,6 +1081,568 @@ __global__ void __launch_bounds__(256) large_update_generic_kernel(uint32_t n, u
     }
 }
 
+// ==========================================================================================
+// Fast path, q_ub <= 20 (cfg4: 8 observed landmarks, q = 19): TWO kernels after the front --
+//   large_solve_kernel   gather + exchange + S + S^-1 + H_o P + K + X in one launch
+//   large_update_ws_kernel (above)   with the predict P = A P A' + Q applied to the tiles as they pass
+// P = A P A' + Q (ekf.cpp:297) touches rows / columns 0, 1 and P(2,2) only. Instead of a kernel that rewrites them
+// in place before the gather, every reader of P in the solve kernel goes through pred_entry(), which returns the
+// PREDICTED entry from the stored one(s), and the streaming update applies the same formulas to the tile rows /
+// columns 0, 1 in shared memory before its rank-q update. Same operations on the same operands as
+// large_predict_kernel, so the results are bit-identical to the unfused path.
+// ==========================================================================================
+__device__ __forceinline__ double pred_entry(const double* __restrict__ P, size_t ldp, uint32_t rb, uint32_t i,
+                                             uint32_t j, double a00, double a10, double kq) {
+    // (i, j) global indices; row i must be owned by this shard (rows 0, 1, 2 live together on the first shard)
+    if (i < 2 && j < 2) {  // the 2 x 2 corner: row pass, then column pass (large_predict_kernel, t == 0)
+        const double p00 = P[0], p10 = P[1], p01 = P[ldp], p11 = P[ldp + 1];
+        const double r00 = a00 * p00, r01 = a00 * p01;
+        const double r10 = a10 * p00 + p10, r11 = a10 * p01 + p11;
+        if (i == 0) return j == 0 ? r00 * a00 + kq : r00 * a10 + r01;
+        return j == 0 ? r10 * a00 : r10 * a10 + r11 + kq;
+    }
+    const double* c = P + (size_t)j * ldp;
+    if (i < 2) {  // j >= 2: rows 0, 1 of column j
+        const double p0 = c[0];
+        return i == 0 ? a00 * p0 : a10 * p0 + c[1];
+    }
+    if (j < 2) {  // i >= 2: row i of columns 0, 1
+        const double p0 = P[i - rb];
+        return j == 0 ? p0 * a00 : p0 * a10 + P[ldp + (i - rb)];
+    }
+    const double v = c[i - rb];
+    return (i == 2 && j == 2) ? v + kq : v;
+}
+
+// P H_o' of row t from the predicted column values colv[k] = P(t, rows[k]); entries of each H row left to right, as
+// the oracle sums them. H_o has the fixed structure pose rows = identity, then (range, bearing) pairs (ekf.cpp:124-132).
+template <int QT>
+__device__ __forceinline__ void pht_from_cols(const double (&colv)[QT], const double (*s_hval)[5], double (&pht)[QT]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        double sum = 0.0;
+        sum += colv[k] * s_hval[k][0];
+        pht[k] = sum;
+    }
+#pragma unroll
+    for (int c = 0; c < (QT - 3) / 2; ++c) {
+        const int kr = 3 + 2 * c, kb = kr + 1;
+        double sr = 0.0, sb = 0.0;
+        sr += colv[0] * s_hval[kr][0];
+        sr += colv[1] * s_hval[kr][1];
+        sr += colv[kr] * s_hval[kr][2];
+        sr += colv[kb] * s_hval[kr][3];
+        sb += colv[0] * s_hval[kb][0];
+        sb += colv[1] * s_hval[kb][1];
+        sb += colv[2] * s_hval[kb][2];
+        sb += colv[kr] * s_hval[kb][3];
+        sb += colv[kb] * s_hval[kb][4];
+        pht[kr] = sr;
+        pht[kb] = sb;
+    }
+    if ((QT - 3) % 2) pht[QT - 1] = 0.0;
+}
+
+// Predicted P(t, rows[k]) for the shard's own row t (column rows[k] of P: consecutive t are consecutive in memory).
+// Rows 0, 1 of the whole matrix are the only ones where the predict needs more than the stored entries of row t;
+// the two threads with t < 2 take the generic pred_entry(), everybody else the straight loads below.
+template <int QT>
+__device__ __forceinline__ void gather_cols(const double* __restrict__ P, size_t ldp, uint32_t rb, uint32_t t, bool mine,
+                                            int q, const int* s_rows, double a00, double a10, double kq,
+                                            double (&colv)[QT]) {
+    if (!mine) {
+#pragma unroll
+        for (int k = 0; k < QT; ++k) colv[k] = 0.0;
+    } else if (t >= 2) {
+        const double c0 = P[t - rb];
+        colv[0] = 0 < q ? c0 * a00 : 0.0;
+        colv[1] = 1 < q ? c0 * a10 + P[ldp + (t - rb)] : 0.0;
+        const double c2 = P[2 * ldp + (t - rb)];
+        colv[2] = 2 < q ? (t == 2 ? c2 + kq : c2) : 0.0;
+#pragma unroll
+        for (int k = 3; k < QT; ++k) colv[k] = k < q ? P[(size_t)s_rows[k] * ldp + (t - rb)] : 0.0;
+    } else {
+#pragma unroll 1
+        for (int k = 0; k < QT; ++k) {
+            const double cv = k < q ? pred_entry(P, ldp, rb, t, (uint32_t)s_rows[k], a00, a10, kq) : 0.0;
+#pragma unroll
+            for (int kk = 0; kk < QT; ++kk)
+                if (kk == k) colv[kk] = cv;
+        }
+    }
+}
+
+// What the shards exchange on the fast path: E[k][t] = (P H_o')(t, k) for every row t (its owner's value), k < q_ub,
+// followed by the q x q block Psub(k1, k2) = P(rows[k1], rows[k2]) (owner of row rows[k1]) at E + q_ub n.
+__device__ __forceinline__ size_t exch_psub_offset(uint32_t q_ub, uint32_t n) { return (size_t)q_ub * n; }
+
+// NCCL form, first half: this shard's part of the exchange buffer, zeros where it owns nothing (the caller sums the
+// buffers of all ranks; every element has exactly one owner, so the sum is exact).
+template <int QT>
+__global__ void __launch_bounds__(256) large_raw_gather_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp,
+                                                              const double* __restrict__ P,
+                                                              const double* __restrict__ A, double kq,
+                                                              const LargeCtx* __restrict__ ctx, uint32_t q_ub,
+                                                              double* __restrict__ E) {
+    __shared__ int s_rows[QT];
+    __shared__ double s_hval[QT][5];
+    const int q = ctx->q, tid = threadIdx.x;
+    if (tid < QT) {
+        s_rows[tid] = tid < q ? ctx->rows[tid] : 0;
+#pragma unroll
+        for (int e = 0; e < 5; ++e) s_hval[tid][e] = tid < q ? ctx->hval[tid][e] : 0.0;
+    }
+    __syncthreads();
+    const double a00 = A[0], a10 = A[1];
+    if (blockIdx.x == 0) {
+        for (int idx = tid; idx < QT * QT; idx += 256) {
+            const int k1 = idx / QT, k2 = idx % QT;
+            const uint32_t r1 = (uint32_t)s_rows[k1];
+            E[exch_psub_offset(q_ub, n) + idx] =
+                (k1 < q && k2 < q && r1 >= rb && r1 < re) ? pred_entry(P, ldp, rb, r1, (uint32_t)s_rows[k2], a00, a10, kq) : 0.0;
+        }
+    }
+    const uint32_t t = blockIdx.x * 256 + tid;
+    if (t >= n) return;
+    const bool mine = t >= rb && t < re;
+    double colv[QT], pht[QT];
+    gather_cols<QT>(P, ldp, rb, t, mine, q, s_rows, a00, a10, kq, colv);
+    pht_from_cols<QT>(colv, s_hval, pht);
+#pragma unroll
+    for (int k = 0; k < QT; ++k)
+        if (k < (int)q_ub) E[(size_t)k * n + t] = pht[k];
+}
+
+// Gauss-Jordan inverse with partial pivoting by ONE warp, lane i owns row i of the q x q matrix (q <= QT <= 32) held
+// in shared memory with a padded row stride (conflict-free column reads). Per pivot: first-maximum search of column k
+// (shuffle butterfly, ties to the lower row), then every lane eliminates its own row into the other buffer (no
+// read/write hazard), one __syncwarp per pivot -- no CTA barrier and no 170-cycle barrier round trip per pivot as in
+// the CTA-wide version of large_gain_fast_kernel, whose arithmetic this repeats element for element
+// (`(j == k ? 1 : p_kj) * d`, `-f * p_kk`, `fma(-f, p_kj, s_ij)`), so the result is bit-identical to it. The row
+// swaps are undone as one column permutation when the rows are written to Sinv (QT x QT, zero padded by the caller).
+template <int QT>
+__device__ __forceinline__ void warp_gauss_jordan(double* bufA, double* bufB, int ld, int q, int lane, int* s_piv,
+                                                  int* s_perm, double* Sinv) {
+    double* cur = bufA;
+    double* nxt = bufB;
+    for (int k = 0; k < q; ++k) {
+        double best = -1.0;
+        if (lane >= k && lane < q) {
+            const double v = fabs(cur[lane * ld + k]);
+            best = v >= 0.0 ? v : -0.5;  // a NaN never wins against a number, as in `v > best`
+        }
+        int p = lane;
+#pragma unroll
+        for (int off = 16; off; off >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best, off);
+            const int op = __shfl_xor_sync(0xffffffffu, p, off);
+            if (ob > best || (ob == best && op < p)) {
+                best = ob;
+                p = op;
+            }
+        }
+        if (lane == 0) s_piv[k] = p;
+        // both rows into registers first (static indices: the loop is fully unrolled), so that the 2 q loads are in
+        // flight together instead of one dependent load -> multiply -> store chain per element
+        const int r = lane == p ? k : lane;  // row p holds the old row k after the swap
+        const int rr = lane < q ? r : 0;
+        double prow[QT], srow[QT];
+#pragma unroll
+        for (int jj = 0; jj < QT; ++jj) {
+            prow[jj] = cur[p * ld + jj];
+            srow[jj] = cur[rr * ld + jj];
+        }
+        const double d = 1.0 / cur[p * ld + k];
+        const double f = cur[rr * ld + k];
+        const bool is_k = lane == k;
+        if (lane < q) {
+#pragma unroll
+            for (int jj = 0; jj < QT; ++jj) {
+                if (jj < q) {
+                    const double pkj = (jj == k ? 1.0 : prow[jj]) * d;  // row k after the swap and the scaling
+                    double out;
+                    if (is_k)
+                        out = pkj;
+                    else
+                        out = jj == k ? -f * pkj : fma(-f, pkj, srow[jj]);
+                    nxt[lane * ld + jj] = out;
+                }
+            }
+        }
+        __syncwarp();
+        double* sw = cur;
+        cur = nxt;
+        nxt = sw;
+    }
+    // undo the row swaps on the columns (k = q-1 .. 0), composed into one permutation: Sinv(i, c) = cur(i, perm[c])
+    if (lane == 0) {
+        for (int c = 0; c < q; ++c) s_perm[c] = c;
+        for (int k = q - 1; k >= 0; --k) {
+            const int pv = s_piv[k], a = s_perm[k];
+            s_perm[k] = s_perm[pv];
+            s_perm[pv] = a;
+        }
+    }
+    __syncwarp();
+    if (lane < q) {
+        double o[QT];
+#pragma unroll
+        for (int c = 0; c < QT; ++c) o[c] = c < q ? cur[lane * ld + s_perm[c]] : 0.0;
+#pragma unroll
+        for (int c = 0; c < QT; ++c)
+            if (c < q) Sinv[lane * QT + c] = o[c];
+    }
+}
+
+// Cholesky factor of the (symmetric positive definite) innovation covariance by ONE warp, lane i holding row i of the
+// lower triangle in registers: S = H_o P H_o' + R with R = 0.2 I, so S >= R > 0 whenever P is positive semi-definite.
+// Right-looking, fully unrolled (static register indices): per column one rsqrt, one shuffle of the pivot and one
+// shuffle per remaining row. 19 short steps instead of the 19 long ones of a pivoted Gauss-Jordan sweep (measured:
+// the sweep kept warp 0 busy for ~27 us while the other seven warps sat in the barrier behind it). K then comes from
+// two triangular solves per column instead of a product with an explicit S^-1 -- the same 2 q^2 flop.
+// The reference takes `S.inverse()` (PartialPivLU, ekf.cpp:301); for an SPD S both are backward stable and differ in
+// the last bits only (tests: <= 1e-9, measured ~1e-16). Returns false -- and the caller falls back to the pivoted sweep
+// -- when a pivot is not positive.
+template <int QT>
+__device__ __forceinline__ bool warp_cholesky(double* S, int ld, int q, int lane, double* invd) {
+    // lane i holds row i of the lower triangle in registers (static indices: fully unrolled); right-looking: per column
+    // one shuffle of the pivot, one rsqrt, one shuffle + fma per remaining column. The factor is written back over
+    // the lower triangle of S (row stride ld), the reciprocal diagonal to invd.
+    double s[QT];
+#pragma unroll
+    for (int j = 0; j < QT; ++j) s[j] = (lane < q && j <= lane && j < q) ? S[lane * ld + j] : 0.0;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < QT; ++k) {
+        const double akk = __shfl_sync(0xffffffffu, s[k], k);
+        const bool live = k < q;  // warp-uniform
+        if (live && !(akk > 0.0)) ok = false;
+        const double inv = live ? rsqrt(akk) : 1.0;
+        const double lik = lane == k ? akk * inv : s[k] * inv;  // column k of L (rows >= k; zero above)
+        s[k] = live ? lik : s[k];
+        if (lane == k) invd[k] = inv;
+#pragma unroll
+        for (int j = k + 1; j < QT; ++j) {
+            const double ljk = __shfl_sync(0xffffffffu, lik, j);
+            if (live && j < q && lane >= j) s[j] = fma(-lik, ljk, s[j]);
+        }
+    }
+    if (lane < q) {
+#pragma unroll
+        for (int j = 0; j < QT; ++j)
+            if (j <= lane) S[lane * ld + j] = s[j];
+    }
+    return ok;
+}
+
+// W = L^-1 (lower triangular), lane c computing column c by forward substitution in registers:
+// W(i, c) = -(sum_{c <= j < i} L(i, j) W(j, c)) / L(i, i), W(c, c) = 1 / L(c, c). Every lane runs the full (unrolled)
+// triangle with zeros above its own diagonal, so the loads of L are warp-wide broadcasts and the code has no
+// lane-dependent control flow; two partial sums per row halve the dependent chain.
+template <int QT>
+__device__ __forceinline__ void warp_lower_inverse(const double* L, int ld, int q, int lane, const double* invd,
+                                                   double* W) {
+    double w[QT];
+#pragma unroll
+    for (int j = 0; j < QT; ++j) w[j] = (j == lane && lane < q) ? invd[j] : 0.0;
+#pragma unroll
+    for (int i = 1; i < QT; ++i) {
+        double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+        for (int jx = 0; jx < i; jx += 2) {
+            acc0 = fma(L[i * ld + jx], w[jx], acc0);
+            if (jx + 1 < i) acc1 = fma(L[i * ld + jx + 1], w[jx + 1], acc1);
+        }
+        if (i < q && i > lane) w[i] = -(acc0 + acc1) * invd[i];
+    }
+    if (lane < q) {
+#pragma unroll
+        for (int i = 0; i < QT; ++i)
+            if (i < q) W[i * ld + lane] = w[i];
+    }
+}
+
+enum { SOLVE_DIRECT = 0, SOLVE_EXCH = 1, SOLVE_PEER = 2 };
+
+// Everything between the front and the streaming update, one launch, 256 columns t of P per CTA.
+//   DIRECT  one GPU: raw rows and the q x q block of P are read straight from P (no exchange buffer at all)
+//   EXCH    NCCL form, second half: the raw rows come from the summed local exchange buffer E
+//   PEER    fused exchange: every owned raw-row value is stored into the exchange buffer of EVERY rank over NVLink peer
+//           memory, the CTA publishes its stores (system-scope fence) and bumps its rank's arrival counter on every
+//           destination, works on the part that needs no remote data (P H_o' of its own rows), and only then waits
+//           (bounded) for the counters of all sources. On a timeout the step is ABANDONED cleanly: K = 0, X keeps its
+//           predicted value, H_o P = 0 -- the update then applies the predict only -- and ASLAM_ST_PEER_TIMEOUT is
+//           raised (aslam_large_status returns ASLAM_ERR_TIMEOUT).
+// Everything between the front and the streaming update, one launch, 256 columns t of P per CTA.
+//   DIRECT  one GPU: raw rows and the q x q block of P are read straight from P (no exchange buffer at all)
+//   EXCH    NCCL form, second half: the raw rows come from the summed local exchange buffer E
+//   PEER    fused exchange: every owned raw-row value is stored into the exchange buffer of EVERY rank over NVLink peer
+//           memory, the CTA publishes its stores (system-scope fence) and bumps its rank's arrival counter on every
+//           destination, works on the part that needs no remote data (P H_o' of its own rows), and only then waits
+//           (bounded) for the counters of all sources. On a timeout the step is ABANDONED cleanly: K = 0, X keeps its
+//           predicted value, H_o P = 0 -- the update then applies the predict only -- and ASLAM_ST_PEER_TIMEOUT is
+//           raised (aslam_large_status returns ASLAM_ERR_TIMEOUT).
+// Predicted P(rows[k], tc) for the rows this shard owns (raw) and predicted P(t, rows[k]) for its own row t (colv).
+// Columns / rows 0, 1 of the whole grid are the only places where the predict needs more than the stored entry; the
+// two threads with t < 2 take the generic pred_entry(), everybody else the straight loads below.
+template <int QT>
+__device__ __forceinline__ void gather_rows_cols(const double* __restrict__ P, size_t ldp, uint32_t rb, uint32_t re,
+                                                 uint32_t t, bool mine, int q, const int* s_rows, double a00,
+                                                 double a10, double kq, double (&raw)[QT], double (&colv)[QT]) {
+    if (t >= 2) {
+        const double* col = P + (size_t)t * ldp - rb;  // column t, indexed by global row
+        const bool own01 = rb == 0;                    // rows 0, 1, 2 live on the first shard
+        const double p0 = own01 ? col[0] : 0.0;
+        raw[0] = (0 < q && own01) ? a00 * p0 : 0.0;
+        raw[1] = (1 < q && own01) ? a10 * p0 + col[1] : 0.0;
+        raw[2] = (2 < q && own01) ? (t == 2 ? col[2] + kq : col[2]) : 0.0;
+#pragma unroll
+        for (int k = 3; k < QT; ++k) {
+            const uint32_t r = (uint32_t)s_rows[k];
+            raw[k] = (k < q && r >= rb && r < re) ? col[r] : 0.0;
+        }
+        if (mine) {
+            const double c0 = P[t - rb];
+            colv[0] = 0 < q ? c0 * a00 : 0.0;
+            colv[1] = 1 < q ? c0 * a10 + P[ldp + (t - rb)] : 0.0;
+            const double c2 = P[2 * ldp + (t - rb)];
+            colv[2] = 2 < q ? (t == 2 ? c2 + kq : c2) : 0.0;
+#pragma unroll
+            for (int k = 3; k < QT; ++k)
+                colv[k] = k < q ? P[(size_t)s_rows[k] * ldp + (t - rb)] : 0.0;
+        } else {
+#pragma unroll
+            for (int k = 0; k < QT; ++k) colv[k] = 0.0;
+        }
+    } else {
+#pragma unroll 1
+        for (int k = 0; k < QT; ++k) {
+            const uint32_t r = (uint32_t)s_rows[k];
+            const bool in = k < q;
+            // dynamic k only on this cold path: the arrays are written through a switch-free helper below
+            const double rv = (in && r >= rb && r < re) ? pred_entry(P, ldp, rb, r, t, a00, a10, kq) : 0.0;
+            const double cv = (in && mine) ? pred_entry(P, ldp, rb, t, r, a00, a10, kq) : 0.0;
+#pragma unroll
+            for (int kk = 0; kk < QT; ++kk)
+                if (kk == k) {
+                    raw[kk] = rv;
+                    colv[kk] = cv;
+                }
+        }
+    }
+}
+
+// Everything between the front and the streaming update, one launch, 256 columns t of P per CTA.
+//   DIRECT  one GPU: raw rows and the q x q block of P are read straight from P (no exchange buffer at all)
+//   EXCH    NCCL form, second half: raw rows and P H_o' come from the summed local exchange buffer E
+//   PEER    fused exchange: every value this rank owns is stored into the exchange buffer of EVERY rank over NVLink peer
+//           memory, the CTA publishes its stores (system-scope fence) and bumps its rank's arrival counter on every
+//           destination, and only then waits (bounded) for the counters of all sources. On a timeout the step is
+//           ABANDONED cleanly: K = 0, X keeps its predicted value, H_o P = 0 -- the update then applies the predict
+//           only -- and ASLAM_ST_PEER_TIMEOUT is raised (aslam_large_status returns ASLAM_ERR_TIMEOUT).
+template <int QT, int MODE>
+__global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp,
+                                                         const double* __restrict__ P, const double* __restrict__ A,
+                                                         double kq, LargeCtx* __restrict__ ctx, uint32_t q_ub,
+                                                         const double* __restrict__ E, double* __restrict__ hp,
+                                                         double* __restrict__ K, double* __restrict__ X,
+                                                         double* __restrict__ predA, const PeerSet ps,
+                                                         unsigned long long target, unsigned long long* sync,
+                                                         unsigned long long epoch, unsigned long long* trace) {
+    // let the streaming update become resident and prefetch its first P tiles while this kernel works
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    static_assert(QT <= 32 && QT + 1 <= 32, "one lane per row");
+    constexpr int LD = QT + 1;
+    __shared__ double S[QT * LD];
+    __shared__ double T[QT * LD];
+    __shared__ double Sinv[QT * QT];
+    __shared__ double s_hval[QT][5];
+    __shared__ int s_hk[QT][5], s_hnnz[QT], s_rows[QT], s_piv[QT], s_perm[QT];
+    __shared__ double s_y[QT], s_rdiag[QT], s_invd[QT];
+    __shared__ int s_abort, s_chol_ok;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        s_abort = 0;
+        // the front of this step runs on the side stream: wait for its context, A and pose
+        if (!spin_until(sync + SYNC_FRONT, epoch)) atomicOr(&ctx->status, (uint32_t)ASLAM_ST_STEP_TIMEOUT);
+        trace_min(trace, epoch, 2);
+    }
+    for (int idx = tid; idx < QT * QT; idx += 256) Sinv[idx] = 0.0;  // padding must not contribute
+    __syncthreads();
+    const int q = ctx->q;
+    const double a00 = A[0], a10 = A[1];
+    if (tid < QT) {
+        const bool in = tid < q;
+        s_rows[tid] = in ? ctx->rows[tid] : 0;
+        s_hnnz[tid] = in ? ctx->hnnz[tid] : 0;
+        s_y[tid] = in ? ctx->y[tid] : 0.0;
+        s_rdiag[tid] = in ? ctx->rdiag[tid] : 1.0;
+#pragma unroll
+        for (int e = 0; e < 5; ++e) {
+            s_hval[tid][e] = in ? ctx->hval[tid][e] : 0.0;
+            s_hk[tid][e] = in ? ctx->hk[tid][e] : 0;
+        }
+    }
+    if (blockIdx.x == 0 && tid == 0) {  // the streaming update applies the predict with these two entries of A
+        predA[0] = a00;
+        predA[1] = a10;
+    }
+    __syncthreads();
+    const uint32_t t = blockIdx.x * 256 + tid;
+    const bool valid = t < n;
+    const uint32_t tc = valid ? t : n - 1;
+    const bool mine = valid && t >= rb && t < re;
+    // ---- (P H_o')(t, :) of the shard's own row t. By the symmetry of P this is also column t of H_o P, which is how
+    // the update uses it below: P -= K (P H_o')' instead of P -= K (H_o P) (ekf.cpp:310 read with P = P'). The two
+    // differ by the rounding-level asymmetry of P only (1.7e-16 between the covariance forms) and it
+    // replaces 19 strided row reads of a column-major matrix per step (155 k scattered sectors, 20 us behind the
+    // streaming kernel's prefetch) by 19 contiguous column reads.
+    double pht[QT];
+    {
+        double colv[QT];
+        gather_cols<QT>(P, ldp, rb, tc, mine, q, s_rows, a00, a10, kq, colv);
+        pht_from_cols<QT>(colv, s_hval, pht);
+    }
+    trace_mark(trace, epoch, 8);  // own columns gathered
+    if constexpr (MODE == SOLVE_PEER) {
+        if (mine) {
+#pragma unroll
+            for (int k = 0; k < QT; ++k)
+                if (k < q)
+                    for (int p = 0; p < ps.world; ++p) ps.E[p][(size_t)k * n + t] = pht[k];
+        }
+        if (blockIdx.x == 0) {  // the rows of the q x q block this shard owns
+            for (int idx = tid; idx < QT * QT; idx += 256) {
+                const int k1 = idx / QT, k2 = idx % QT;
+                const uint32_t r1 = (uint32_t)s_rows[k1];
+                if (k1 < q && k2 < q && r1 >= rb && r1 < re) {
+                    const double v = pred_entry(P, ldp, rb, r1, (uint32_t)s_rows[k2], a00, a10, kq);
+                    for (int p = 0; p < ps.world; ++p) ps.E[p][exch_psub_offset(q_ub, n) + idx] = v;
+                }
+            }
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence_system();
+            for (int p = 0; p < ps.world; ++p) atomicAdd_system(ps.flag[p] + ps.rank, 1ULL);
+        }
+        if (tid < ps.world) {  // wait for the other ranks' values
+            const unsigned long long* flags = ps.flag[ps.rank];
+            unsigned long long v = 0;
+            for (int it = 0; it < 4000000; ++it) {
+                asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + tid) : "memory");
+                if (v >= target) break;
+                __nanosleep(128);
+            }
+            if (v < target) {
+                s_abort = 1;
+                atomicOr(&ctx->status, (uint32_t)ASLAM_ST_PEER_TIMEOUT);
+            }
+        }
+        __syncthreads();
+    }
+    const bool abort_step = MODE == SOLVE_PEER && s_abort != 0;
+    // ---- (P H_o')(t, :) of every row t and the q x q block P(rows, rows)
+    if constexpr (MODE != SOLVE_DIRECT) {
+#pragma unroll
+        for (int k = 0; k < QT; ++k)
+            pht[k] = (k < q && !abort_step) ? ld_exch<MODE == SOLVE_PEER>(E + (size_t)k * n + tc) : 0.0;
+    }
+    for (int idx = tid; idx < QT * QT; idx += 256) {
+        const int k1 = idx / QT, k2 = idx % QT;
+        double v = 0.0;
+        if (k1 < q && k2 < q && !abort_step) {
+            if constexpr (MODE == SOLVE_DIRECT)
+                v = pred_entry(P, ldp, rb, (uint32_t)s_rows[k1], (uint32_t)s_rows[k2], a00, a10, kq);
+            else
+                v = ld_exch<MODE == SOLVE_PEER>(E + exch_psub_offset(q_ub, n) + idx);
+        }
+        S[k1 * LD + k2] = v;  // Psub, staged in S
+    }
+    __syncthreads();
+    trace_mark(trace, epoch, 9);  // exchange waited for, q x q block in shared memory
+    // S = H_s Psub H_s' + R (H_s: the q x q sparse form of H_o), zero-padded to QT x QT with the identity on the padding
+    for (int idx = tid; idx < QT * QT; idx += 256) {
+        const int a = idx / QT, jx = idx % QT;
+        double hpaj = 0.0;
+        for (int f = 0; f < s_hnnz[a]; ++f) hpaj += s_hval[a][f] * S[s_hk[a][f] * LD + jx];
+        T[a * LD + jx] = hpaj;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < QT * QT; idx += 256) {
+        const int a = idx / QT, b = idx % QT;
+        double sum = 0.0;
+        for (int e = 0; e < s_hnnz[b]; ++e) sum += T[a * LD + s_hk[b][e]] * s_hval[b][e];
+        S[a * LD + b] = sum + (a == b ? s_rdiag[a] : 0.0);
+    }
+    __syncthreads();
+    trace_mark(trace, epoch, 10);  // S built
+    // warp 0: S = L L' in place on a copy (T), then W = L^-1 (into S); every thread then adds up its entries of
+    // S^-1 = W' W. If S is not positive definite: S^-1 by the pivoted sweep -- what `S.inverse()` of ekf.cpp:301 does
+    // through PartialPivLU -- straight into Sinv.
+    if (tid < 32) {
+        for (int idx = tid; idx < QT * LD; idx += 32) T[idx] = S[idx];
+        __syncwarp();
+        const bool ok = warp_cholesky<QT>(T, LD, q, tid, s_invd);
+        const bool all_ok = __all_sync(0xffffffffu, ok);
+        if (tid == 0) s_chol_ok = all_ok ? 1 : 0;
+        if (all_ok) {
+            warp_lower_inverse<QT>(T, LD, q, tid, s_invd, S);
+        } else {
+            for (int idx = tid; idx < QT * QT; idx += 32) Sinv[idx] = 0.0;
+            __syncwarp();
+            warp_gauss_jordan<QT>(S, T, LD, q, tid, s_piv, s_perm, Sinv);
+        }
+    }
+    // ---- column t of H_o P (= row t of P H_o', see above): independent of S^-1, stored while warp 0 factorises
+    if (valid) {
+        double* hpo = hp + (size_t)t * QT;
+#pragma unroll
+        for (int k = 0; k < QT; k += 2)
+            *reinterpret_cast<double2*>(hpo + k) = abort_step ? make_double2(0.0, 0.0) : make_double2(pht[k], pht[k + 1]);
+    }
+    __syncthreads();
+    trace_mark(trace, epoch, 11);  // factorised, H_o P stored
+    if (s_chol_ok) {  // S^-1(a, b) = sum_{k >= max(a, b)} W(k, a) W(k, b); the padding of Sinv stays zero
+        for (int idx = tid; idx < QT * QT; idx += 256) {
+            const int a = idx / QT, b = idx % QT;
+            if (a < q && b < q) {
+                double sum = 0.0;
+                for (int k = a > b ? a : b; k < q; ++k) sum = fma(S[k * LD + a], S[k * LD + b], sum);
+                Sinv[idx] = sum;
+            }
+        }
+        __syncthreads();
+    }
+    if (valid) {
+        double dx = 0.0;
+#pragma unroll
+        for (int k = 0; k < QT; ++k) {  // K row t = (P H_o')(t, :) S^-1
+            double sum = 0.0;
+#pragma unroll
+            for (int e = 0; e < QT; ++e) sum += pht[e] * Sinv[e * QT + k];
+            if (abort_step) sum = 0.0;
+            dx += sum * s_y[k];
+            K[(size_t)k * n + t] = sum;
+        }
+        X[t] += dx;  // ekf.cpp:309
+    }
+    trace_mark(trace, epoch, 12);  // K and X written
+    // ---- the last CTA to get here publishes "X is final, the context is free" for the front of the next step
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        trace_max(trace, epoch, 3);
+        const unsigned long long arrived = atomicAdd(sync + SYNC_COUNT, 1ULL) + 1;
+        if (arrived == gridDim.x) {
+            sync[SYNC_COUNT] = 0;
+            __threadfence();
+            st_release_gpu(sync + SYNC_SOLVE, epoch);
+        }
+    }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------- host side
@@ -1008,8 +1661,8 @@ static PeerSet peer_set(const aslam_large* h, uint64_t epoch) {
     return ps;
 }
 
-aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
-                              uint32_t m, bool peer) {
+static FrontArgs front_args(const aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                            uint32_t m) {
     FrontArgs a;
     a.ox = x; a.oy = y; a.vx = vx; a.az = az; a.yaw = yaw; a.dt = dt;
     a.m = m;
@@ -1018,44 +1671,184 @@ aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, dou
     a.thresh = h->cfg.min_dist_thresh;
     a.kr_pose = (double)h->cfg.ekf_kr;
     a.kr_lm = (double)h->cfg.ukf_kr;  // ekf.cpp:278 (UKF constant, as written)
+    a.epoch = h->step_epoch + 1;
+    for (uint32_t i = 0; i < ASLAM_MAX_OBS; ++i) {
+        a.range[i] = i < m ? h->obs_host[i] : 0.0f;
+        a.bearing[i] = i < m ? h->obs_host[ASLAM_MAX_OBS + i] : 0.0f;
+    }
+    return a;
+}
+
+// mode: LARGE_STEP_DIRECT (unsharded handle, no exchange buffer), LARGE_STEP_EXCH (the caller sums h->exch between
+// phase1 and phase2), LARGE_STEP_PEER (fused exchange over peer memory).
+aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
+                              uint32_t m, int mode) {
+    const FrontArgs a = front_args(h, x, y, yaw, vx, az, dt, m);
     const uint32_t n = h->n, nb = (n + 255) / 256;
-    // front on the side stream (stage_obs already made it wait for ev_ctx_free): it overlaps the previous step's
-    // streaming update; predict / gather need both the front's context and the updated P
-    ASLAM_CUDA(cudaStreamWaitEvent(h->side, h->ev_ctx_free, 0));
-    large_front_kernel<<<1, 1024, 0, h->side>>>(a, n, h->X, h->A, h->d_obs, h->ctx);
+    // every argument / attachment check comes BEFORE the first launch: an error return leaves the handle untouched
+    if (mode == LARGE_STEP_PEER && (a.q_ub > 40 || !h->peer_world)) {
+        set_error("fused large step: needs peer_attach and at most 18 observations per message");
+        return ASLAM_ERR_UNSUPPORTED;
+    }
+    if (mode == LARGE_STEP_DIRECT && (h->row_begin != 0 || h->row_end != n)) {
+        set_error("large step: a sharded handle must use step_phase1 / exchange / step_phase2 or step_fused");
+        return ASLAM_ERR_UNSUPPORTED;
+    }
+    // The front runs on the side stream, so that it overlaps the previous step's streaming update. Ordering against
+    // the main stream is carried by the counters in h->sync (see SYNC_*), not by events: the front waits for the
+    // previous step's solve stage, this step's solve kernel waits for the front.
+    h->step_epoch += 1;
+    {
+        // The front usually becomes resident BEFORE the update CTA that will share its SM. An SM keeps the shared-memory
+        // carve-out of the first kernel that arrives until it is empty again, and the update needs ~180 KB: without
+        // this the SM the front sits on cannot take its update CTA, the persistent grid runs that CTA after another one
+        // has finished, and the update takes twice as long (measured: 190 -> 461 us).
+        static PerDeviceOnce once_;
+        int dev_ = -1;
+        if (once_.pending(&dev_)) {
+            ASLAM_CUDA(cudaFuncSetAttribute(large_front_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            (int)cudaSharedmemCarveoutMaxShared));
+            ASLAM_CUDA(cudaFuncSetAttribute(large_solve_kernel<20, SOLVE_DIRECT>,
+                                            cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            (int)cudaSharedmemCarveoutMaxShared));
+            ASLAM_CUDA(cudaFuncSetAttribute(large_solve_kernel<20, SOLVE_EXCH>,
+                                            cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            (int)cudaSharedmemCarveoutMaxShared));
+            ASLAM_CUDA(cudaFuncSetAttribute(large_solve_kernel<20, SOLVE_PEER>,
+                                            cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            (int)cudaSharedmemCarveoutMaxShared));
+            once_.mark(dev_);
+        }
+    }
+    large_front_kernel<<<1, FRONT_THREADS, 0, h->side>>>(a, n, h->X, h->A, h->ctx, h->sync, h->trace);
+    h->launches += 1;
+    h->q_host = a.q_ub;
+    h->step_mode = mode;
+    const double kq = (double)h->cfg.ekf_kq;
+    if (a.q_ub <= 20) {  // fast path: no in-place predict, no separate gather (see large_solve_kernel)
+        if (mode == LARGE_STEP_PEER) {
+            h->peer_epoch += 1;  // the step's epoch (1-based) picks the buffer parity and the arrival target
+        } else if (mode == LARGE_STEP_EXCH) {
+            ASLAM_CUDA(cudaEventRecord(h->ev_front, h->side));
+            ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_front, 0));
+            large_raw_gather_kernel<20><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A, kq,
+                                                                   h->ctx, a.q_ub, h->exch);
+            h->launches += 1;
+        }
+        ASLAM_CUDA(cudaGetLastError());
+        return ASLAM_OK;
+    }
+    // round-1 chain for q > 20: stream-ordered behind the front through an event
     ASLAM_CUDA(cudaEventRecord(h->ev_front, h->side));
     ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_front, 0));
-    large_predict_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A,
-                                                    (double)h->cfg.ekf_kq);
-    if (peer) {
-        // the step's epoch (1-based) picks the buffer parity; phase2 waits for epoch * nb arrivals per source
-        if (a.q_ub > 40 || !h->peer_world) {
-            set_error("fused large step: needs peer_attach and at most 18 observations per message");
-            return ASLAM_ERR_UNSUPPORTED;
-        }
+    large_predict_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A, kq);
+    if (mode == LARGE_STEP_PEER) {
         h->peer_epoch += 1;
         const PeerSet ps = peer_set(h, h->peer_epoch);
-        if (a.q_ub <= 20)
-            large_gather_fast_kernel<20, true><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P,
-                                                                          h->ctx, a.q_ub, nullptr, ps);
-        else
-            large_gather_fast_kernel<40, true><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P,
-                                                                          h->ctx, a.q_ub, nullptr, ps);
-    } else if (a.q_ub <= 20)
-        large_gather_fast_kernel<20, false><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx,
-                                                                       a.q_ub, h->exch, PeerSet{});
-    else if (a.q_ub <= 40)
+        large_gather_fast_kernel<40, true><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P,
+                                                                      h->ctx, a.q_ub, nullptr, ps);
+    } else if (a.q_ub <= 40)
         large_gather_fast_kernel<40, false><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx,
                                                                        a.q_ub, h->exch, PeerSet{});
     else
         large_gather_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->ctx, a.q_ub, h->exch);
     ASLAM_CUDA(cudaGetLastError());
-    h->launches += 3;
-    h->q_host = a.q_ub;
+    h->launches += 2;
     return ASLAM_OK;
 }
 
-aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
+// Grid of the streaming update: column ranges x row blocks. The full row blocks fill `waves` whole waves of the
+// resident CTAs (one per SM): 12 waves where that still leaves a CTA at least 64 columns to stream (measured on the
+// unsharded cfg4 matrix), else 4 (row-sharded handles: short column ranges would spend their time filling the ring).
+static dim3 update_grid(const aslam_large* h, uint32_t nrows, uint32_t rows_per_cta, uint32_t cs,
+                        uint32_t* cols_per_cta_out) {
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    const uint32_t n = h->n;
+    const uint32_t rblocks = (nrows + rows_per_cta - 1) / rows_per_cta;
+    const uint32_t full_rblocks = nrows / rows_per_cta ? nrows / rows_per_cta : 1;
+    auto ranges = [&](uint32_t w) {
+        const uint32_t c = (w * (uint32_t)sms + full_rblocks / 2) / full_rblocks;
+        return c < 1 ? 1u : c;
+    };
+    const uint32_t waves = (n + ranges(12u) - 1) / ranges(12u) >= 64u ? 12u : 4u;
+    uint32_t cx = ranges(waves);
+    uint32_t cols_per_cta = (n + cx - 1) / cx;
+    cols_per_cta = ((cols_per_cta + cs - 1) / cs) * cs;
+    cx = (n + cols_per_cta - 1) / cols_per_cta;
+    *cols_per_cta_out = cols_per_cta;
+    return dim3(cx, rblocks);
+}
+
+static aslam_status large_ekf_phase2_fast(aslam_large* h) {
+    const uint32_t n = h->n, nb = (n + 255) / 256, q_ub = h->q_host;
+    const uint32_t nrows = h->row_end - h->row_begin;
+    const double kq = (double)h->cfg.ekf_kq;
+    const unsigned long long epoch = h->step_epoch;
+    if (h->step_mode == LARGE_STEP_PEER) {
+        const PeerSet ps = peer_set(h, h->peer_epoch);
+        const unsigned long long target = (unsigned long long)h->peer_epoch * nb;  // nb solve CTAs per rank and step
+        large_solve_kernel<20, SOLVE_PEER><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A, kq,
+                                                                      h->ctx, q_ub, ps.E[h->peer_rank], h->hp, h->K, h->X,
+                                                                      h->predA, ps, target, h->sync, epoch, h->trace);
+    } else if (h->step_mode == LARGE_STEP_EXCH) {
+        large_solve_kernel<20, SOLVE_EXCH><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A, kq,
+                                                                      h->ctx, q_ub, h->exch, h->hp, h->K, h->X, h->predA,
+                                                                      PeerSet{}, 0ull, h->sync, epoch, h->trace);
+    } else {
+        large_solve_kernel<20, SOLVE_DIRECT><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A,
+                                                                        kq, h->ctx, q_ub, nullptr, h->hp, h->K, h->X,
+                                                                        h->predA, PeerSet{}, 0ull, h->sync, epoch,
+                                                                        h->trace);
+    }
+    if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
+#ifndef ASLAM_STREAM_NST
+#define ASLAM_STREAM_NST 4
+#endif
+#ifndef ASLAM_STREAM_CS
+#define ASLAM_STREAM_CS 12
+#endif
+    constexpr int NST = ASLAM_STREAM_NST, CW = 7, CS = ASLAM_STREAM_CS;
+    using G = StreamGeo<CW, 2, 20, CS, NST>;
+    constexpr size_t WS_SMEM = G::SMEM;
+    ASLAM_DYN_SMEM((large_update_stream_kernel<CW, 2, 20, CS, NST>), WS_SMEM);
+    StreamPlan pl{};
+    pl.n = n;
+    pl.rb = h->row_begin;
+    pl.nrows = nrows;
+    pl.nch = (n + CS - 1) / CS;
+    pl.nblk = (nrows + (uint32_t)G::ROWS - 1) / (uint32_t)G::ROWS;
+    pl.blk_rows = (((nrows + pl.nblk - 1) / pl.nblk + 15) / 16) * 16;
+    while ((pl.nblk - 1) * pl.blk_rows >= (uint32_t)h->ldp) pl.nblk -= 1;  // (padding can make the last block empty)
+    pl.last_rows = (uint32_t)h->ldp - (pl.nblk - 1) * pl.blk_rows;           // padded to 16 rows, like ldp
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3((unsigned)sms);  // persistent: one CTA per SM
+    lc.blockDim = dim3(G::THREADS);
+    lc.dynamicSmemBytes = WS_SMEM;
+    lc.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at;
+    // Early launch needs the two launches to be adjacent in the stream (no timing event between them). With a peer
+    // shard on the same GPU the 148 early-resident update CTAs would leave no SM with registers for that peer's solve
+    // kernel, which this handle's solve kernel is waiting for: plain stream order there.
+    const bool early = h->pdl && !h->timed && !(h->step_mode == LARGE_STEP_PEER && h->peer_same_device);
+    lc.numAttrs = early ? 1 : 0;
+    ASLAM_CUDA(cudaLaunchKernelEx(&lc, large_update_stream_kernel<CW, 2, 20, CS, NST>, pl, h->ldp, h->P, (const double*)h->K,
+                                  (const double*)h->hp, (const double*)h->predA, kq,
+                                  (const unsigned long long*)h->sync, epoch, h->trace));
+    if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, h->stream));
+    ASLAM_CUDA(cudaGetLastError());
+    h->launches += 2;
+    return ASLAM_OK;
+}
+
+aslam_status large_ekf_phase2(aslam_large* h) {
+    if (h->q_host <= 20) return large_ekf_phase2_fast(h);
+    const bool peer = h->step_mode == LARGE_STEP_PEER;
     const uint32_t n = h->n, nb = (n + 255) / 256, q_ub = h->q_host;
     const uint32_t QT = large_ekf_qt(q_ub);
     const size_t smem = (size_t)q_ub * q_ub * sizeof(double);
@@ -1066,78 +1859,29 @@ aslam_status large_ekf_phase2(aslam_large* h, bool peer) {
         const double* E = ps.E[h->peer_rank];
         const unsigned long long* flags = ps.flag[h->peer_rank];
         const unsigned long long target = (unsigned long long)h->peer_epoch * nb;  // nb gather CTAs per rank and step
-        if (QT == 20)
-            large_gain_fast_kernel<20, true><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, E, h->hp, h->K, h->X, flags, target,
-                                                                        (int)h->peer_world);
-        else
-            large_gain_fast_kernel<40, true><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, E, h->hp, h->K, h->X, flags, target,
-                                                                        (int)h->peer_world);
-    } else if (QT == 20)
-        large_gain_fast_kernel<20, false><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X, nullptr, 0,
-                                                                     0);
-    else if (QT == 40)
+        large_gain_fast_kernel<40, true><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, E, h->hp, h->K, h->X, flags, target,
+                                                                    (int)h->peer_world);
+    } else if (QT == 40)
         large_gain_fast_kernel<40, false><<<nb, 256, 0, h->stream>>>(n, h->ctx, q_ub, h->exch, h->hp, h->K, h->X, nullptr, 0,
                                                                      0);
     else
         large_gain_kernel<<<nb, 256, smem, h->stream>>>(n, h->ctx, q_ub, h->exch, QT, h->hp, h->K, h->X);
     const uint32_t nrows = h->row_end - h->row_begin;
-    // X and the context are final for this step once the gain kernel is done (the fast update kernels read neither)
-    if (QT == 20 || QT == 40) ASLAM_CUDA(cudaEventRecord(h->ev_ctx_free, h->stream));
+    // X and the context are final for this step once the gain kernel is done (the bulk update kernel reads neither)
+    if (QT == 40) large_mark_kernel<<<1, 1, 0, h->stream>>>(h->sync, h->step_epoch);
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
-    if (QT == 20 || QT == 40) {
-        int sms = 148;
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
-        static const char* variant = std::getenv("ASLAM_LARGE_UPDATE");  // "ldg": register-path kernel
-        static const char* waves_env = std::getenv("ASLAM_LARGE_WAVES");
-        const bool use_ldg = variant && variant[0] == 'l';
-        const uint32_t rows_per_cta = QT == 20 ? 512u : 256u;
-        const uint32_t rblocks = (nrows + rows_per_cta - 1) / rows_per_cta;
-        const uint32_t full_rblocks = nrows / rows_per_cta ? nrows / rows_per_cta : 1;
-        // column ranges: the full row blocks fill `waves` whole waves of the resident CTAs
-        const uint32_t resident = (uint32_t)sms * (use_ldg ? 2u : 1u);
-        const uint32_t cs = QT == 20 ? 8u : 16u;
-        // 12 waves where that still leaves a CTA at least 64 columns to stream (measured on the unsharded cfg4 matrix:
-        // 201 -> 196 us), else 4 (row-sharded handles: short column ranges would spend their time filling the ring)
-        auto ranges = [&](uint32_t w) {
-            const uint32_t c = (w * resident + full_rblocks / 2) / full_rblocks;
-            return c < 1 ? 1u : c;
-        };
-        uint32_t waves = (n + ranges(12u) - 1) / ranges(12u) >= 64u ? 12u : 4u;
-        if (waves_env) waves = (uint32_t)std::atoi(waves_env);
-        uint32_t cx = ranges(waves);
-        uint32_t cols_per_cta = (n + cx - 1) / cx;
-        cols_per_cta = ((cols_per_cta + cs - 1) / cs) * cs;
-        cx = (n + cols_per_cta - 1) / cols_per_cta;
-        dim3 grid(cx, rblocks);
-        if (use_ldg) {
-            if (QT == 20)
-                large_update_kernel<2, 20, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K,
-                                                                          h->hp, cols_per_cta);
-            else
-                large_update_kernel<1, 40, 4><<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K,
-                                                                          h->hp, cols_per_cta);
-        } else if (QT == 20 && !(variant && variant[0] == 'b')) {  // default; ASLAM_LARGE_UPDATE=bulk: the one-barrier kernel
-            using G = BulkGeo<2, 20, 8, 5>;
-            constexpr size_t WS_SMEM = G::SMEM + 5 * sizeof(uint64_t);
-            ASLAM_DYN_SMEM((large_update_ws_kernel<2, 20, 8, 5>), WS_SMEM);
-            large_update_ws_kernel<2, 20, 8, 5><<<grid, 288, WS_SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
-                                                                                  h->K, h->hp, cols_per_cta);
-        } else if (QT == 20) {
-            using G = BulkGeo<2, 20, 8, 5>;
-            ASLAM_DYN_SMEM((large_update_bulk_kernel<2, 20, 8, 5>), G::SMEM);
-            large_update_bulk_kernel<2, 20, 8, 5><<<grid, 256, G::SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
-                                                                                    h->K, h->hp, cols_per_cta);
-        } else {
-            using G = BulkGeo<1, 40, 16, 5>;
-            ASLAM_DYN_SMEM((large_update_bulk_kernel<1, 40, 16, 5>), G::SMEM);
-            large_update_bulk_kernel<1, 40, 16, 5><<<grid, 256, G::SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
-                                                                                     h->K, h->hp, cols_per_cta);
-        }
+    if (QT == 40) {
+        using G = BulkGeo<1, 40, 16, 5>;
+        ASLAM_DYN_SMEM((large_update_bulk_kernel<1, 40, 16, 5>), G::SMEM);
+        uint32_t cols_per_cta = 0;
+        const dim3 grid = update_grid(h, nrows, 256u, 16u, &cols_per_cta);
+        large_update_bulk_kernel<1, 40, 16, 5><<<grid, 256, G::SMEM, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P,
+                                                                                 h->K, h->hp, cols_per_cta);
     } else {
         dim3 grid((nrows + 255) / 256, (n + 31) / 32);
         large_update_generic_kernel<<<grid, 256, 0, h->stream>>>(n, h->row_begin, nrows, h->ldp, h->P, h->K, h->hp, QT,
                                                                h->ctx);
-        ASLAM_CUDA(cudaEventRecord(h->ev_ctx_free, h->stream));  // this kernel reads the context
+        large_mark_kernel<<<1, 1, 0, h->stream>>>(h->sync, h->step_epoch);  // this kernel reads the context
     }
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, h->stream));
     ASLAM_CUDA(cudaGetLastError());

@@ -28,6 +28,7 @@ struct LargeCtx {
 // other rank (CUDA IPC over NVLink, or plain pointers inside one process) and the gather kernel stores each
 // value it owns straight into all of them; one arrival counter per (destination, source) pair orders the step.
 constexpr int LARGE_MAX_PEERS = 8;
+enum { LARGE_STEP_DIRECT = 0, LARGE_STEP_EXCH = 1, LARGE_STEP_PEER = 2 };
 struct PeerSet {
     double* E[LARGE_MAX_PEERS];                 // this step's (parity-selected) exchange buffer of rank p
     unsigned long long* flag[LARGE_MAX_PEERS];  // rank p's arrival counters, indexed by source rank
@@ -47,8 +48,13 @@ struct aslam_large {
     double* P = nullptr;             // [n][ldp]: column j at P + j*ldp holds rows row_begin..row_end-1
     double* X = nullptr;             // [n]
     double* A = nullptr;             // [2]: A(0,0), A(1,0) (ekf.cpp:210-211)
+    double* predA = nullptr;         // [2]: the A entries of the step in flight, for the predict fused into the update
     aslam::LargeCtx* ctx = nullptr;
-    float* d_obs = nullptr;          // [2][ASLAM_MAX_OBS] range, bearing
+    float* d_obs = nullptr;          // [2][ASLAM_MAX_OBS] range, bearing (UKF; the EKF front takes them as arguments)
+    float obs_host[2 * ASLAM_MAX_OBS] = {};   // EKF: the observations of the message in flight
+    unsigned long long* sync = nullptr;       // EKF: step-ordering counters in device memory (ekf_large.cu SYNC_*)
+    uint64_t step_epoch = 0;                  // EKF: steps enqueued so far
+    unsigned long long* trace = nullptr;      // EKF diagnostics (ASLAM_LARGE_TRACE=1): [64][8] %globaltimer stamps
     double* exch = nullptr;          // [2*LARGE_QMAX][n] raw rows of P, then P H^T slices
     double* hp = nullptr;            // [n][QP]   H P, k contiguous per column
     double* K = nullptr;             // [QP][n]   gain, row k contiguous
@@ -57,15 +63,18 @@ struct aslam_large {
     uint64_t launches = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the streaming update kernel of the last step
     // EKF: the front kernel of step k+1 (association, pose predict, H rows; it needs X and the context, not P) runs
-    // on `side` behind ev_ctx_free, so it overlaps the streaming update of step k; the main stream joins at ev_front
+    // on `side`, so it overlaps the streaming update of step k; ordering through `sync` (fast path) / ev_front (q > 20)
     cudaStream_t side = nullptr;
     cudaEvent_t ev_ctx_free = nullptr, ev_front = nullptr;
-    bool timed = false;
+    bool timed = false;              // CUDA events around the streaming update (aslam_large_set_timing)
+    bool pdl = true;                 // launch the streaming update with programmatic stream serialization
+    int step_mode = 0;               // LARGE_STEP_* of the step in flight (phase1 -> phase2)
     // fused peer exchange: block = [E parity 0][E parity 1][LARGE_MAX_PEERS arrival counters]
     unsigned char* peer_block = nullptr;        // own block (cudaMalloc)
     unsigned char* peer_base[aslam::LARGE_MAX_PEERS] = {};  // every rank's block as mapped here
     bool peer_ipc[aslam::LARGE_MAX_PEERS] = {};  // mapped with cudaIpcOpenMemHandle (to be closed)
     uint32_t peer_world = 0, peer_rank = 0;
+    bool peer_same_device = false;              // some peer shard lives on this handle's own GPU
     uint64_t peer_epoch = 0;                    // fused steps taken so far (all ranks step in lockstep)
     // UKF large-map state lives in ukf_large.cu's own struct, reached through `ukf`
     void* ukf = nullptr;

@@ -200,6 +200,20 @@ class BatchedFilter:
             Pp[b, :n, :n] = np.asarray(P[b])[:n, :n].T  # column-major on the wire
         capi.check(self._lib.aslam_filter_load_state(self._h, capi.ptr(N), capi.ptr(Xp), capi.ptr(Zp), capi.ptr(Pp)))
 
+    def load_aux(self, a00=None, a10=None, wait=None, status=None):
+        """The rest of a checkpoint (after load_state): A entries from get_aux, wait = get_wait()'s dict, status."""
+        a00 = None if a00 is None else capi.as_np(a00, np.float64)
+        a10 = None if a10 is None else capi.as_np(a10, np.float64)
+        wc = wr = wb = wh = None
+        if wait is not None:
+            wc = capi.as_np(wait["count"], np.uint32)
+            wr = capi.as_np(wait["range"], np.float32)
+            wb = capi.as_np(wait["bearing"], np.float32)
+            wh = capi.as_np(wait["hits"], np.uint32)
+        st = None if status is None else capi.as_np(status, np.uint32)
+        capi.check(self._lib.aslam_filter_load_aux(self._h, capi.ptr(a00), capi.ptr(a10), capi.ptr(wc), capi.ptr(wr),
+                                                   capi.ptr(wb), capi.ptr(wh), capi.ptr(st)))
+
     @property
     def launch_count(self):
         return int(self._lib.aslam_filter_launch_count(self._h))
@@ -382,6 +396,11 @@ class LargeFilter:
                                                     capi.ptr(rng), capi.ptr(brg), rng.size, capi.ptr(assoc)))
         return None if assoc is None else assoc[:self._m]
 
+    def set_timing(self, on=True):
+        """EKF: record CUDA events around the streaming update of every later step (off by default: the event keeps
+        the update from being launched early behind the solve kernel)."""
+        capi.check(self._lib.aslam_large_set_timing(self._h, 1 if on else 0))
+
     def last_kernel_ms(self):
         ms = C.c_float()
         capi.check(self._lib.aslam_large_last_kernel_ms(self._h, C.byref(ms)))
@@ -390,7 +409,9 @@ class LargeFilter:
     def status(self):
         st = C.c_uint32()
         fk = C.c_int32()
-        capi.check(self._lib.aslam_large_status(self._h, C.byref(st), C.byref(fk)))
+        rc = self._lib.aslam_large_status(self._h, C.byref(st), C.byref(fk))
+        if rc != capi.ASLAM_ERR_TIMEOUT:  # a peer timeout is reported through the status bit as well
+            capi.check(rc)
         return int(st.value), int(fk.value)
 
     @property

@@ -347,6 +347,7 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
 
     def timed(step):
         with torch.cuda.stream(stream):
+            f.set_timing(False)
             for _ in range(max(W, 3)):
                 step()
             f.sync()
@@ -363,23 +364,27 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
             torch.cuda.synchronize(dev)
             ms = e0.elapsed_time(e1) / K
             launches = f.launch_count - l0
+            # the streaming kernel alone: CUDA events around it on the handle's stream (a separate pass: the event
+            # between the solve kernel and the update disables the update's early launch, so those steps are slower)
+            f.set_timing(True)
             kms = []
             for _ in range(K):
                 step()
                 kms.append(f.last_kernel_ms())
             f.sync()
+            f.set_timing(False)
         if world > 1:
             dist.barrier()
         return ms, launches, kms
 
-    exchange, nccl_ms = "none (one GPU)", None
+    exchange, nccl_ms, parity = "none (one GPU)", None, None
     if world == 1:
         ms, launches, kms = timed(step_single)
     else:
         # comparison point: phase1 -> NCCL all-reduce of the exchange buffer -> phase2
         nccl_ms, launches, kms = timed(step_nccl)
         ms, exchange = nccl_ms, "NCCL all-reduce of the [2q][n] exchange buffer"
-        try:  # the fused exchange: CUDA IPC peer mappings, stores + arrival counters inside the kernels
+        try:  # the fused exchange: CUDA IPC peer mappings, stores + arrival counters inside the solve kernel
             hd, _ = f.peer_export()
             handles = [None] * world
             dist.all_gather_object(handles, hd)
@@ -387,7 +392,12 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
             dist.barrier()
             ms, launches, kms = timed(step_fused)
             assert f.status()[0] == 0, "fused exchange timed out"
-            exchange = "fused: peer stores over NVLink + arrival counters in the gather/gain kernels (no collective call)"
+            exchange = ("fused: peer stores over NVLink + arrival counters inside the solve kernel "
+                        "(no collective call, 3 launches per step)")
+            parity = large_parity(f, step_nccl, step_fused, torch, dist, rank, world, dev, rb, re, X0, G, d,
+                                  rng, brg, ODOM)
+        except AssertionError:
+            raise
         except Exception as e:  # noqa: BLE001  (reported, and the NCCL numbers stand)
             sys.stderr.write("fused exchange unavailable: %r\n" % (e,))
     t = torch.tensor([ms, float(np.mean(kms))], dtype=torch.float64, device=dev)
@@ -406,13 +416,83 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
     return {
         "workload": "cfg4: large-map EKF n=8195 (4096 landmarks), q=19 rows of H per step, FP64 P%s"
                     % ("" if world == 1 else ", rows sharded over %d GPUs, one exchange per step" % world),
-        "exchange": exchange, "ms_per_step_nccl_exchange": nccl_ms,
+        "exchange": exchange, "ms_per_step_nccl_exchange": nccl_ms, "parity": parity,
         "steps_per_s": 1e3 / ms, "ms_per_step": ms, "launches_per_step": launches / K,
-        "roofline": {"bound": "hbm", "kernel": "large_update_ws_kernel<2,20,8,5>", "achieved": achieved,
+        "roofline": {"bound": "hbm", "kernel": "large_update_stream_kernel<7,2,20,12,4> (persistent, 1 CTA/SM)", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                      "traffic": _ncu_traffic() if world == 1 else None,
                      "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": kernel_ms, "peak_source": peak_src},
     }
+
+
+def large_parity(f, step_nccl, step_fused, torch, dist, rank, world, dev, rb, re, X0, G, d, rng, brg, ODOM, steps=3):
+    """Driver-visible parity of the multi-process exchange (bit-identical by design, asserted here on hardware):
+    from the same loaded state, `steps` steps through the NCCL all-reduce form and through the fused peer-store form
+    must leave EQUAL X and EQUAL local rows of P on every rank; and rank 0 runs the same steps on an UNSHARDED handle
+    of its own GPU and compares X and, row block by row block (gathered over the ranks), the whole P."""
+    import awesomeslam_b200 as A
+    n = X0.size
+    P0 = A.dense_P(G, d)
+    out = {}
+    res = {}
+    for name, step in (("nccl", step_nccl), ("fused", step_fused)):
+        f.load_state_colmajor(X0, P0)
+        if world > 1:
+            dist.barrier()
+        for _ in range(steps):
+            step()
+        f.sync()
+        res[name] = f.get_state()
+        if world > 1:
+            dist.barrier()
+    eq = bool(np.array_equal(res["nccl"][0], res["fused"][0]) and np.array_equal(res["nccl"][1], res["fused"][1]))
+    flag = torch.tensor([1 if eq else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    out["fused_eq_nccl"] = bool(flag.item())
+    # against the unsharded handle on rank 0 (1 GB more on that GPU, freed at once)
+    digest = torch.zeros(2, dtype=torch.float64, device=dev)
+    Pl = res["fused"][1]  # [rows, n]
+    if rank == 0:
+        u = A.LargeFilter("ekf", n, dev.index)
+        u.load_state_colmajor(X0, P0)
+        for _ in range(steps):
+            u.step(*ODOM, rng, brg, want_assoc=False)
+        Xu, Pu = u.get_state()
+        u.close()
+        bounds = [None] * world
+    else:
+        Xu = Pu = None
+        bounds = None
+    del P0
+    # every rank sends its rows to rank 0 in turn (gather_object of 67 MB blocks at N = 8: bounded, once per run)
+    ok = True
+    for src in range(world):
+        if src == 0:
+            blk = Pl if rank == 0 else None
+            lo, hi = (rb, re) if rank == 0 else (0, 0)
+        else:
+            if rank == src:
+                t = torch.from_numpy(np.ascontiguousarray(Pl)).to(dev)
+                meta = torch.tensor([rb, re], dtype=torch.int64, device=dev)
+                dist.send(meta, 0)
+                dist.send(t, 0)
+            if rank == 0:
+                meta = torch.zeros(2, dtype=torch.int64, device=dev)
+                dist.recv(meta, src)
+                lo, hi = int(meta[0].item()), int(meta[1].item())
+                t = torch.empty((hi - lo, n), dtype=torch.float64, device=dev)
+                dist.recv(t, src)
+                blk = t.cpu().numpy()
+        if rank == 0:
+            ok = ok and bool(np.array_equal(blk, Pu[lo:hi]))
+    if rank == 0:
+        ok = ok and bool(np.array_equal(res["fused"][0], Xu))
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+    dist.broadcast(flag, 0)
+    out["eq_unsharded"] = bool(flag.item())
+    out["steps"] = steps
+    assert out["fused_eq_nccl"] and out["eq_unsharded"], "sharded large-map EKF differs from the unsharded one: %r" % out
+    return out
 
 
 def _ncu_traffic():
@@ -684,8 +764,15 @@ def main():
     large = None
     if not args.no_large:
         large = large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src)
+    # everything that involves more than one rank is done: the other ranks leave now instead of spinning in a barrier
+    # while rank 0 runs its single-GPU legs and the CPU baselines
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
     ukf_large = None
-    if rank == 0 and not args.no_large:
+    if not args.no_large:
         ukf_large = ukf_large_leg(args, torch, dev)
         if not args.no_cpu:
             ukf_large["cpu_baseline"] = ukf_large_cpu_leg()
@@ -693,15 +780,9 @@ def main():
                 large["cpu_baseline"] = large_cpu_leg()
     laser = None
     ukf_batched = None
-    if rank == 0 and not args.no_large:
+    if not args.no_large:
         laser = laser_leg(args, torch, dev)
         ukf_batched = ukf_batched_leg(args, torch, dev)
-    if world > 1:
-        dist.barrier()
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
 
     per_gpu_ups = value / world
     line = {
@@ -742,8 +823,6 @@ def main():
         line["cpu_baseline"] = cpu_leg(cpu_filters, cpu_msgs)
         line["speedup_e2e_vs_cpu"] = e2e / line["cpu_baseline"]["value"]
     _emit(line)
-    if world > 1:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -43,7 +43,8 @@ enum {
     ASLAM_ERR_ARG = -1,         /* null pointer / size out of range */
     ASLAM_ERR_CUDA = -2,        /* CUDA runtime error: see aslam_last_error() */
     ASLAM_ERR_UNSUPPORTED = -3, /* e.g. max_state_dim too large for the batched kernels */
-    ASLAM_ERR_NOT_READY = -4    /* step before the first set_observations (ekf.cpp:76) */
+    ASLAM_ERR_NOT_READY = -4,   /* step before the first set_observations (ekf.cpp:76) */
+    ASLAM_ERR_TIMEOUT = -5      /* aslam_large_status: a fused-exchange step gave up waiting for a peer */
 };
 
 /* Per-filter status bits (reference failure modes that are silent there) */
@@ -53,7 +54,8 @@ enum {
     ASLAM_ST_NONFINITE = 1u << 2,     /* X or P holds a NaN/Inf */
     ASLAM_ST_WAIT_OVERFLOW = 1u << 3, /* wait-list exceeded ASLAM_MAX_WAIT (reference: unbounded) */
     ASLAM_ST_OBS_OVERFLOW = 1u << 4,  /* more than ASLAM_MAX_OBS observations in one message */
-    ASLAM_ST_PEER_TIMEOUT = 1u << 5   /* fused exchange: a peer's rows did not arrive within the spin bound */
+    ASLAM_ST_PEER_TIMEOUT = 1u << 5,  /* fused exchange: a peer's rows did not arrive within the spin bound */
+    ASLAM_ST_STEP_TIMEOUT = 1u << 6   /* large-map EKF: a kernel gave up waiting for the previous kernel of the step chain */
 };
 
 #define ASLAM_MAX_WAIT 256u /* capacity of the per-filter new-landmark wait-list */
@@ -175,9 +177,19 @@ aslam_status aslam_filter_get_landmarks(aslam_filter* h, double* x, double* y, u
 aslam_status aslam_filter_device_state(aslam_filter* h, const double** d_X, const uint32_t** d_N);
 
 /* Checkpoint / start from a supplied state (the reference has none).
- * Sets N, X, Z, P for every filter; marks it initialised (init_x = init_z = false). */
+ * load_state sets N, X, Z, P for every filter, marks it initialised (init_x = init_z = false) and RESETS everything
+ * else that outlives a message: empty wait-list, A = I, status 0, no LLT failure -- nothing of an earlier run on the
+ * same handle leaks into the loaded state.
+ * load_aux restores the rest of a checkpoint taken with get_aux / get_wait / get_state (call it after load_state):
+ * the two persistent entries of A (ekf.cpp:206-211 keeps them when vx or az is 0; EKF handles only), the wait-list
+ * with its hit counts (ekf.h:104; arrays laid out as get_wait returns them) and the status bits. Groups passed as
+ * NULL keep their reset value. A run resumed from load_state + load_aux continues bit-identically to the
+ * uninterrupted one. */
 aslam_status aslam_filter_load_state(aslam_filter* h, const uint32_t* N, const double* X, const double* Z,
                                      const double* P);
+aslam_status aslam_filter_load_aux(aslam_filter* h, const double* a00, const double* a10, const uint32_t* wcount,
+                                   const float* wrange, const float* wbearing, const uint32_t* whits,
+                                   const uint32_t* status);
 
 /* ---------------------------------------------------------------- large-map filter ------- */
 /* One filter with n = 3 + 2 * landmarks state entries; P is n x n FP64 in HBM.
@@ -211,10 +223,13 @@ aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float y
                                      uint32_t* q_out);
 aslam_status aslam_large_exchange_buffer(aslam_large* h, double** d_buf, size_t* count);
 aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out);
-/* Fused form of the same exchange (no NCCL call, no host round trip between the phases): every rank's
- * gather kernel stores the values it owns straight into the exchange block of EVERY rank over NVLink
- * peer memory and bumps an arrival counter there; the gain kernel of each rank spins (bounded;
- * ASLAM_ST_PEER_TIMEOUT on expiry) until all sources have arrived. Set-up, once per handle:
+/* Fused form of the same exchange (no NCCL call, no host round trip, ONE kernel between the front and the
+ * streaming update): every rank's solve kernel stores the values it owns straight into the exchange block of EVERY
+ * rank over NVLink peer memory and bumps an arrival counter there, then spins (bounded) until all sources have
+ * arrived. When the bound expires the step is abandoned cleanly -- K = 0: the filter applies the predict only, the
+ * state stays valid -- ASLAM_ST_PEER_TIMEOUT is raised and aslam_large_status returns ASLAM_ERR_TIMEOUT.
+ * All argument and attachment checks are made before the first launch: an error return leaves the handle untouched.
+ * Set-up, once per handle:
  *   peer_export: allocates this handle's exchange block, returns its CUDA IPC handle (64 bytes) and,
  *                for ranks living in the same process, the raw device pointer (either may be NULL);
  *   peer_attach: `ipc_handles` = world x 64 bytes gathered from all ranks (other processes), or
@@ -229,9 +244,16 @@ aslam_status aslam_large_step_fused(aslam_large* h, double x, double y, float ya
 /* Kernels this handle has launched so far. */
 uint64_t aslam_large_launch_count(aslam_large* h);
 /* Device time (CUDA events on the handle's stream) of the dominant kernel of the LAST step: the
- * streaming covariance update (EKF) / the whole step's GEMM chain (UKF). Waits for that kernel. */
+ * streaming covariance update (EKF) / the whole step's GEMM chain (UKF). Waits for that kernel.
+ * EKF handles record the events only after aslam_large_set_timing(h, 1): an event between the solve kernel and the
+ * update keeps the update from being launched early (programmatic dependent launch), so a timed step is slower. */
+aslam_status aslam_large_set_timing(aslam_large* h, int32_t on);
+/* Diagnostics (handles created with ASLAM_LARGE_TRACE=1 in the environment, else ASLAM_ERR_UNSUPPORTED): the
+ * %globaltimer stamps [64 steps][16] the EKF kernels left for the last 64 steps (csrc/ekf_large.cu, TRACE_STEPS). */
+aslam_status aslam_large_trace(aslam_large* h, unsigned long long* out1024);
 aslam_status aslam_large_last_kernel_ms(aslam_large* h, float* ms);
-/* status bits of the filter (ASLAM_ST_*), and for the UKF the first failing LLT pivot or -1. */
+/* status bits of the filter (ASLAM_ST_*), and for the UKF the first failing LLT pivot or -1.
+ * Returns ASLAM_ERR_TIMEOUT (status still written) when ASLAM_ST_PEER_TIMEOUT is set. */
 aslam_status aslam_large_status(aslam_large* h, uint32_t* status, int32_t* llt_fail);
 
 /* ---------------------------------------------------------------- FP64 dense blocks ------- */

@@ -38,7 +38,18 @@ def _run_single(aslam, orc, kind, steps, cfg_over=None, lm=None, check_every=1, 
             # which injects a 6e-8 relative step. Counted, reported, and the CUDA filter is re-seeded
             # from the oracle's state so that every later step is still checked to 1e-9.
             worst["resyncs"].append((t, ex, ep))
+            st_before = s["status"].copy()
             f.load_state([n], [X], [Z], [P])
+            # the rest of the checkpoint comes from the oracle as well: wait-list with its hit counts, A (EKF)
+            wr, wb, wc = o.wait()
+            W = aslam.capi.MAX_WAIT
+            wait = {"count": np.array([wr.size], np.uint32), "range": np.zeros((1, W), np.float32),
+                    "bearing": np.zeros((1, W), np.float32), "hits": np.zeros((1, W), np.uint32)}
+            wait["range"][0, :wr.size] = wr
+            wait["bearing"][0, :wr.size] = wb
+            wait["hits"][0, :wr.size] = wc
+            a = o.a_entries() if kind == "ekf" else (None, None)
+            f.load_aux(None if a[0] is None else [a[0]], None if a[1] is None else [a[1]], wait=wait, status=st_before)
             continue
         worst["X"] = max(worst["X"], ex)
         worst["P"] = max(worst["P"], ep)
@@ -266,3 +277,53 @@ def test_single_filter_class_mirror(aslam, orc):
     assert lx.size == (o.N - 3) // 2 == 8
     assert relerr(lx, X[3::2]) <= TOL_F64 and relerr(ly, X[4::2]) <= TOL_F64
     e.close()
+
+
+@pytest.mark.parametrize("kind", ["ekf", "ukf"])
+def test_checkpoint_restore_continues_bit_identically(aslam, kind):
+    """Checkpoint in the middle of the promotion phase (wait-list half counted, for the EKF a non-trivial A kept over a
+    zero-twist message), restore into a FRESH handle with load_state + load_aux, continue: bit-identical to the
+    uninterrupted run. And load_state alone on a USED handle resets the wait-list, A and the status."""
+    lmx, lmy = aslam.map_cfg1()
+    B, T, L, cut = 8, 40, 8, 6
+    rp = aslam.Replay(lmx, lmy, B, T, warm=4, vx=0.02, seed0=991)   # moving from message 4 on: A != I at the cut
+    rp.vx[cut + 1] = 0.0                                   # a message that keeps the previous A (ekf.cpp:206)
+
+    def run(f, t0, t1):
+        for t in range(t0, t1):
+            f.set_observations([rp.range[t, b] for b in range(B)], [rp.bearing[t, b] for b in range(B)])
+            f.step(rp.x[t], rp.y[t], rp.yaw[t], rp.vx[t], rp.az[t], rp.dt[t])
+
+    a = aslam.BatchedFilter(kind, B, 0)
+    run(a, 0, cut)
+    s, aux, w = a.get_state(), a.get_aux(), a.get_wait()
+    assert int(w["count"].max()) > 0 and int(w["hits"].max()) < 10  # nothing promoted yet: the counts matter
+    b = aslam.BatchedFilter(kind, B, 0)
+    b.load_state(s["N"], s["X"], aux["Z"], s["P"])
+    b.load_aux(aux["a00"] if kind == "ekf" else None, aux["a10"] if kind == "ekf" else None, wait=w,
+               status=s["status"])
+    run(a, cut, T)
+    run(b, cut, T)
+    sa, sb = a.get_state(), b.get_state()
+    assert np.array_equal(sa["N"], sb["N"]) and int(sa["N"].min()) > 3
+    assert np.array_equal(sa["X"], sb["X"]) and np.array_equal(sa["P"], sb["P"])
+    wa, wb = a.get_wait(), b.get_wait()
+    assert all(np.array_equal(wa[k], wb[k]) for k in wa)
+    # a used handle: load_state puts the wait-list, A and the status back to their initial values
+    a.load_state(s["N"], s["X"], aux["Z"], s["P"])
+    w0, x0 = a.get_wait(), a.get_aux()
+    assert not w0["count"].any() and not a.get_state(want_P=False, want_assoc=False)["status"].any()
+    if kind == "ekf":
+        assert np.all(x0["a00"] == 1.0) and np.all(x0["a10"] == 0.0)
+    a.close()
+    b.close()
+
+
+def test_set_observations_rejects_decreasing_offsets(aslam):
+    f = aslam.BatchedFilter("ekf", 2, 0)
+    import ctypes as C
+    off = np.array([0, 3, 2], np.uint32)
+    r = np.zeros(4, np.float32)
+    rc = f._lib.aslam_filter_set_observations(f._h, aslam.capi.ptr(r), aslam.capi.ptr(r), aslam.capi.ptr(off))
+    assert rc == aslam.capi.ASLAM_ERR_ARG
+    f.close()

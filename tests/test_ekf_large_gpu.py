@@ -203,3 +203,39 @@ def test_cfg4_full_size_one_step(aslam, orc):
     the oracle (O(q n^2) on the host cores), plus the symmetry property of the updated P."""
     worst = _run_large(aslam, orc, 64, 8, 2)
     print("cfg4 worst relerr", worst)
+
+
+def test_large_ekf_fused_step_without_peer_gives_up_cleanly(aslam):
+    """A fused step whose peer never arrives: the spin bound expires, the step is ABANDONED (K = 0: predict only,
+    the state stays finite), ASLAM_ST_PEER_TIMEOUT is raised and aslam_large_status returns ASLAM_ERR_TIMEOUT.
+    And the argument checks come before any launch: a fused step on a handle that was never attached is refused
+    and leaves the state untouched."""
+    import ctypes as C
+    tx, ty, X0, G, d = aslam.large_map_state(9, seed=6)
+    P0 = aslam.dense_P(G, d)
+    n = X0.size
+    k = 70
+    lo = aslam.LargeFilter("ekf", n, row_begin=0, row_end=k)
+    hi = aslam.LargeFilter("ekf", n, row_begin=k, row_end=n)
+    for f in (lo, hi):
+        f.load_state_colmajor(X0, P0)
+    rng, brg, idx = aslam.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8, seed=50)
+    with pytest.raises(aslam.capi.AslamError) as e:  # not attached: refused before the first launch
+        lo.step_fused(0.0, 0.0, np.float32(0.0), 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
+    assert e.value.status == aslam.capi.ASLAM_ERR_UNSUPPORTED
+    X, P = lo.get_state()
+    assert np.array_equal(X, X0) and np.array_equal(P, P0[:k])
+    blocks = [f.peer_export()[1] for f in (lo, hi)]
+    for r, f in enumerate((lo, hi)):
+        f.peer_attach(2, r, blocks=blocks)
+    lo.step_fused(0.0, 0.0, np.float32(0.0), 0.05, 0.1, 1.0, rng, brg, want_assoc=False)  # `hi` never steps
+    st = C.c_uint32()
+    rc = lo._lib.aslam_large_status(lo._h, C.byref(st), None)
+    assert rc == aslam.capi.ASLAM_ERR_TIMEOUT and st.value & (1 << 5)
+    X, P = lo.get_state()
+    assert np.all(np.isfinite(X)) and np.all(np.isfinite(P))
+    assert np.array_equal(X[3:], X0[3:])  # no correction was applied; only the pose moved (predict)
+    # P = A P A' + Q: rows / columns 0, 1 and P(2,2) changed, everything else is the loaded matrix
+    assert np.array_equal(P[3:, 3:], P0[3:k, 3:])
+    for f in (lo, hi):
+        f.close()

@@ -22,6 +22,7 @@ for _ in range(steps):
 f.sync()
 dt = (time.perf_counter() - t0) / steps
 ks = []
+f.set_timing(True)
 for _ in range(steps):
     f.step(0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
     ks.append(f.last_kernel_ms())
