@@ -27,8 +27,9 @@ uint32_t batched_padded_dim(int32_t max_state_dim, int kind) {
     const int nmax = max_state_dim - 1;
     if (nmax < 3) return 0;
     if (kind == ASLAM_KIND_UKF) {
-        if (nmax <= 29) return 30;  // the reference's cap; larger UKF maps: aslam_large_ukf_*
-        return 0;
+        if (nmax <= 29) return 30;  // the reference's cap (config.h:45)
+        if (nmax <= 35) return 36;  // the cfg3 shape: 16 landmarks, N = 35, 75 sigma points
+        return 0;                   // larger UKF maps: aslam_large_ukf_*
     }
     if (nmax <= 29) return 30;
     if (nmax <= 35) return 36;

@@ -22,8 +22,6 @@
 // SURVEY.md section 6.2.) One __syncthreads per block; V and dx are double-buffered.
 #include <cuda_runtime.h>
 
-#include <cstdlib>
-
 #include "ekf_batched_common.cuh"
 
 namespace aslam {
@@ -430,12 +428,7 @@ aslam_status launch_ekf_batched(const aslam_config& cfg, const BatchState& st, c
     kp.kp_lm = (double)cfg.ukf_kp_landmark_pose;  // ekf.cpp:277
     switch (st.ld) {
         case 30: return launch_t<30, 2>(kp, stream);
-        case 36: {
-            // cfg3 size: ASLAM_EKF_KERNEL=mma selects the warp-per-filter DMMA kernel (ekf_batched_mma.cu)
-            const char* variant = std::getenv("ASLAM_EKF_KERNEL");  // read per launch: tests switch it
-            if (variant && variant[0] == 'm') return launch_ekf_batched_mma36(kp, stream);
-            return launch_t<36, 2>(kp, stream);
-        }
+        case 36: return launch_t<36, 2>(kp, stream);
         case 48: return launch_t<48, 2>(kp, stream);
         case 64: return launch_t<64, 1>(kp, stream);
         default: set_error("ekf_batched: unsupported padded dim"); return ASLAM_ERR_UNSUPPORTED;

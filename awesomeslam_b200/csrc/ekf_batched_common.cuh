@@ -1,5 +1,5 @@
 // Pieces shared by the two batched EKF kernels (ekf_batched.cu: thread-owns-columns DFMA kernel for any padded
-// dimension; ekf_batched_mma.cu: warp-per-filter DMMA kernel for the cfg3 size): kernel parameters, the
+// dimension; tools/probes/ekf_batched_mma.cu: the measured-and-rejected warp-per-filter DMMA variant, not built): kernel parameters, the
 // shared-memory message buffer and its cp.async prefetch.
 #pragma once
 #include <cuda_runtime.h>
@@ -67,6 +67,5 @@ __device__ __forceinline__ void prefetch_message(MsgBuf& m, const BatchInput& in
     }
 }
 
-aslam_status launch_ekf_batched_mma36(const EkfParams& kp, cudaStream_t stream);
 
 }  // namespace aslam

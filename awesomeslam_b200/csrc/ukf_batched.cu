@@ -4,7 +4,13 @@
 //
 // Mapping: one CTA (128 threads) per filter; the whole working set of a step -- Paug/L, the
 // 2N+5 propagated sigma points, their measurement images, P, S, Tc, K -- lives in shared memory
-// (about 75 KB, three filters per SM) and P stays there across the `steps` messages of a launch.
+// and P stays there across the `steps` messages of a launch. The kernel is instantiated for the padded state
+// dimensions 30 (N <= 29: the reference's own cap, config.h:45; 66 KB, three filters per SM) and 36 (N <= 35: the
+// cfg3 shape of 16 landmarks, 75 sigma points; 92 KB, two per SM).
+// Barriers: the factorisations are the latency chains of the step. LLT takes ONE barrier per column (the diagonal
+// goes to a side array, so nobody waits for thread 0 to patch it in; round 1 took 3), and the pivot search of
+// PartialPivLU is a shuffle reduction of warp 0 instead of a serial scan by one thread. (An out-of-place LU pass with
+// one barrier per pivot was measured too: it touches N^2 instead of (N-k)^2 entries per pivot and was 15 % slower.)
 //
 // Numerics: the reference UKF is numerically fragile (w0 = (1-N)/3 < 0: P - K S K' goes indefinite
 // and Eigen's LLT silently returns a half-factored L), so every reduction here
@@ -22,13 +28,13 @@ namespace aslam {
 
 namespace {
 
-constexpr int UNP = 30;          // padded state dim (N <= 29: the reference's cap, config.h:45)
-constexpr int UNA = UNP + 2;     // augmented
-constexpr int UNS = 2 * UNP + 5; // sigma points (<= 63 used)
-constexpr int USP = 65;          // row pitch of the sigma-point matrices (odd: conflict-free row walks)
 constexpr int UTHREADS = 128;
 
+template <int UNP>
 struct __align__(16) UkfSlot {
+    static constexpr int UNA = UNP + 2;      // augmented
+    static constexpr int UNS = 2 * UNP + 5;  // sigma points
+    static constexpr int USP = UNS | 1;      // row pitch of the sigma-point matrices (odd: conflict-free row walks)
     // The sigma-point matrices are dead once P, S and Tc have been formed; the LU factors of S, its inverse and K live
     // in the same bytes from then on (a barrier separates the two uses): 3 instead of 2 CTAs per SM.
     union {
@@ -46,7 +52,7 @@ struct __align__(16) UkfSlot {
     double P[UNP][UNP];
     double S[UNP][UNP];
     double Tc[UNP][UNP];
-    double X[UNP], Z[UNP], Zp[UNP], Zd[UNP], W[UNS];
+    double X[UNP], Z[UNP], Zp[UNP], Zd[UNP], Ld[UNA];
     int piv[UNP];
     int fail_k;
     FrontSlot fr;
@@ -60,9 +66,10 @@ struct UkfParams {
     float std_a, std_yaw;
 };
 
+template <int UNP>
 __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams kp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    UkfSlot& s = *reinterpret_cast<UkfSlot*>(smem_raw);
+    UkfSlot<UNP>& s = *reinterpret_cast<UkfSlot<UNP>*>(smem_raw);
     const int tid = threadIdx.x;
     const uint32_t f = blockIdx.x;
     const float pi = kp.fp.pi;
@@ -138,8 +145,8 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         }
         const float lambda = (float)(3.0 - (double)(N + 2));
         const float denom = __fadd_rn(__fadd_rn(lambda, (float)N), 2.0f);  // lambda + N + 2 in float
-        for (int i = tid; i < NS; i += UTHREADS)
-            s.W[i] = i == 0 ? (double)__fdiv_rn(lambda, denom) : (double)(float)(0.5 / (double)denom);
+        // weights(0) = lambda / (lambda + N + 2) and the common weight 0.5 / (..), both rounded to float (ukf.h:75-80)
+        const double w0 = (double)__fdiv_rn(lambda, denom), wc = (double)(float)(0.5 / (double)denom);
         // ---- Paug (ukf.cpp:262-277) into L
         for (int k = tid; k < NA * NA; k += UTHREADS) {
             const int i = k / NA, j = k % NA;
@@ -150,7 +157,10 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         }
         if (tid == 0) s.fail_k = -1;
         __syncthreads();
-        // ---- L = Paug.llt().matrixL(): Eigen's unblocked left-looking LLT with its failure rule
+        // ---- L = Paug.llt().matrixL(): Eigen's unblocked left-looking LLT with its failure rule. One barrier per
+        // column: every thread forms the pivot x itself (same operands, same order: the same value), the new diagonal
+        // goes to Ld (L[k][k] still holds the Paug entry that the other threads may not have read yet) and is
+        // patched in with the upper triangle below.
         for (int k = 0; k < NA; ++k) {
             if (s.fail_k >= 0) break;
             double x = s.L[k][k];
@@ -171,13 +181,16 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
                 for (int j = 0; j < k; ++j) sum += s.L[i][j] * s.L[k][j];
                 s.L[i][k] = (s.L[i][k] - sum) / x;
             }
-            __syncthreads();
-            if (tid == 0) s.L[k][k] = x;
+            if (tid == 0) s.Ld[k] = x;
             __syncthreads();
         }
-        for (int k = tid; k < NA * NA; k += UTHREADS) {
-            const int i = k / NA, j = k % NA;
-            if (j > i) s.L[i][j] = 0.0;
+        {
+            const int done = s.fail_k >= 0 ? s.fail_k : NA;  // columns that were factorised
+            for (int k = tid; k < NA * NA; k += UTHREADS) {
+                const int i = k / NA, j = k % NA;
+                if (j > i) s.L[i][j] = 0.0;
+                else if (i == j && i < done) s.L[i][i] = s.Ld[i];
+            }
         }
         __syncthreads();
         // ---- sigma points (ukf.cpp:283-289) propagated through f (ukf.cpp:292-297)
@@ -208,7 +221,7 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         // ---- predicted mean (ukf.cpp:300-304) and Zsig (ukf.cpp:322-326)
         for (int k = tid; k < N; k += UTHREADS) {
             double acc = 0.0;
-            for (int i = 0; i < NS; ++i) acc += s.W[i] * s.XS[k][i];
+            for (int i = 0; i < NS; ++i) acc += (i == 0 ? w0 : wc) * s.XS[k][i];
             s.X[k] = acc;
         }
         {
@@ -231,7 +244,7 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         // ---- Zpred (ukf.cpp:329-339); Xdiff in place (ukf.cpp:312-313)
         for (int k = tid; k < N; k += UTHREADS) {
             double acc = 0.0;
-            for (int i = 0; i < NS; ++i) acc += s.W[i] * s.ZS[k][i];
+            for (int i = 0; i < NS; ++i) acc += (i == 0 ? w0 : wc) * s.ZS[k][i];
             if (k >= 2 && (k & 1) == 0) acc = (double)normalize_angle((float)acc, pi);
             s.Zp[k] = acc;
         }
@@ -255,8 +268,8 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
             const int which = e / (N * N), r = e % (N * N), a = r / N, b = r % N;
             const double* da = which == 1 ? s.ZS[a] : s.XS[a];
             const double* db = which == 0 ? s.XS[b] : s.ZS[b];
-            double acc = 0.0;
-            for (int i = 0; i < NS; ++i) acc = acc + (s.W[i] * da[i]) * db[i];
+            double acc = 0.0 + (w0 * da[0]) * db[0];
+            for (int i = 1; i < NS; ++i) acc = acc + (wc * da[i]) * db[i];
             if (which == 0) s.P[a][b] = acc + ((a == b && a < 3) ? kp.kq : 0.0);
             else if (which == 1) {
                 const double v = acc + (a == b ? kp.kr : 0.0);
@@ -266,64 +279,79 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         __syncthreads();  // last read of the sigma-point matrices: LU / Si / K take over their storage
         for (int e = tid; e < N * N; e += UTHREADS) s.LU[e / N][e % N] = s.S[e / N][e % N];
         __syncthreads();
-        // ---- S.inverse(): PartialPivLU (unblocked, first largest pivot) ...
+        // ---- S.inverse(): PartialPivLU (unblocked, first largest pivot). Per pivot: warp 0 finds the pivot row with a
+        // shuffle reduction (largest |a(i,k)|, i >= k, ties to the lowest row: Eigen's first maximum); the row swap
+        // (and its barrier) only happens when the pivot is not on the diagonal.
         for (int k = 0; k < N; ++k) {
-            if (tid == 0) {
+            if (tid < 32) {
+                double best = -1.0;
                 int p = k;
-                double best = fabs(s.LU[k][k]);
-                for (int i = k + 1; i < N; ++i) {
+                for (int i = k + tid; i < N; i += 32) {  // (N <= 35: at most two rows per lane, ascending)
                     const double v = fabs(s.LU[i][k]);
                     if (v > best) {
                         best = v;
                         p = i;
                     }
                 }
-                s.piv[k] = best != 0.0 ? p : -1 - p;  // zero pivot: recorded, no swap/scale
+#pragma unroll
+                for (int off = 16; off; off >>= 1) {
+                    const double ob = __shfl_xor_sync(0xffffffffu, best, off);
+                    const int op = __shfl_xor_sync(0xffffffffu, p, off);
+                    if (ob > best || (ob == best && op < p)) {
+                        best = ob;
+                        p = op;
+                    }
+                }
+                if (tid == 0) s.piv[k] = best != 0.0 ? p : -1 - p;  // zero pivot: recorded, no swap/scale
             }
             __syncthreads();
             const int pr = s.piv[k];
             const bool nz = pr >= 0;
             const int p = nz ? pr : -1 - pr;
-            if (nz && p != k)
+            if (nz && p != k) {
                 for (int j = tid; j < N; j += UTHREADS) {
                     const double t = s.LU[k][j];
                     s.LU[k][j] = s.LU[p][j];
                     s.LU[p][j] = t;
                 }
-            __syncthreads();
+                __syncthreads();  // (uniform branch)
+            }
             if (nz) {
                 const double pv = s.LU[k][k];
                 for (int i = k + 1 + tid; i < N; i += UTHREADS) s.LU[i][k] /= pv;
+                __syncthreads();
             }
-            __syncthreads();
-            for (int e = tid; e < (N - k - 1) * (N - k - 1); e += UTHREADS) {
-                const int i = k + 1 + e / (N - k - 1), j = k + 1 + e % (N - k - 1);
+            const int m = N - k - 1;
+            for (int e = tid; e < m * m; e += UTHREADS) {
+                const int i = k + 1 + e / m, j = k + 1 + e % m;
                 s.LU[i][j] -= s.LU[i][k] * s.LU[k][j];
             }
             __syncthreads();
         }
+        double* F = &s.LU[0][0];  // the LU factors
+        double* I = &s.Si[0][0];  // S^-1 is built here
         // ... then solve against the permuted identity, one column per thread
-        for (int e = tid; e < N * N; e += UTHREADS) s.Si[e / N][e % N] = (e / N == e % N) ? 1.0 : 0.0;
+        for (int e = tid; e < N * N; e += UTHREADS) I[(e / N) * UNP + e % N] = (e / N == e % N) ? 1.0 : 0.0;
         __syncthreads();
         for (int j = tid; j < N; j += UTHREADS) {
             for (int k = 0; k < N; ++k) {
                 const int pr = s.piv[k];
                 const int p = pr >= 0 ? pr : -1 - pr;
                 if (p != k) {
-                    const double t = s.Si[k][j];
-                    s.Si[k][j] = s.Si[p][j];
-                    s.Si[p][j] = t;
+                    const double t = I[k * UNP + j];
+                    I[k * UNP + j] = I[p * UNP + j];
+                    I[p * UNP + j] = t;
                 }
             }
             for (int i = 0; i < N; ++i) {
-                double v = s.Si[i][j];
-                for (int k = 0; k < i; ++k) v -= s.LU[i][k] * s.Si[k][j];
-                s.Si[i][j] = v;
+                double v = I[i * UNP + j];
+                for (int k = 0; k < i; ++k) v -= F[i * UNP + k] * I[k * UNP + j];
+                I[i * UNP + j] = v;
             }
             for (int i = N - 1; i >= 0; --i) {
-                double v = s.Si[i][j];
-                for (int k = i + 1; k < N; ++k) v -= s.LU[i][k] * s.Si[k][j];
-                s.Si[i][j] = v / s.LU[i][i];
+                double v = I[i * UNP + j];
+                for (int k = i + 1; k < N; ++k) v -= F[i * UNP + k] * I[k * UNP + j];
+                I[i * UNP + j] = v / F[i * UNP + i];
             }
         }
         __syncthreads();
@@ -331,7 +359,7 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         for (int e = tid; e < N * N; e += UTHREADS) {
             const int i = e / N, j = e % N;
             double acc = 0.0;
-            for (int k = 0; k < N; ++k) acc += s.Tc[i][k] * s.Si[k][j];
+            for (int k = 0; k < N; ++k) acc += s.Tc[i][k] * I[k * UNP + j];
             s.K[i][j] = acc;
         }
         for (int k = tid; k < N; k += UTHREADS) {
@@ -389,12 +417,20 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
 
 }  // namespace
 
+template <int UNP>
+static aslam_status launch_ukf_t(const UkfParams& kp, cudaStream_t stream) {
+    // Resident CTAs per SM are what sets this kernel's throughput (measured by padding the allocation: 3 per SM
+    // 5.86 M updates/s at n = 19, 2 per SM 4.14 M, 1 per SM 2.18 M -- every phase is a latency chain), and the
+    // footprint is set by the cap the handle was created with, not by the filters' current N.
+    const size_t smem = sizeof(UkfSlot<UNP>);
+    ASLAM_DYN_SMEM(ukf_batched_kernel<UNP>, smem);
+    ukf_batched_kernel<UNP><<<kp.st.batch, UTHREADS, smem, stream>>>(kp);
+    ASLAM_CUDA(cudaGetLastError());
+    return ASLAM_OK;
+}
+
 aslam_status launch_ukf_batched(const aslam_config& cfg, const BatchState& st, const BatchInput& in,
                                 cudaStream_t stream) {
-    if (st.ld != UNP) {
-        set_error("ukf_batched: only the reference's cap (max_state_dim <= 30) is built; use aslam_large_ukf_*");
-        return ASLAM_ERR_UNSUPPORTED;
-    }
     UkfParams kp;
     kp.st = st;
     kp.in = in;
@@ -410,11 +446,13 @@ aslam_status launch_ukf_batched(const aslam_config& cfg, const BatchState& st, c
     kp.kp_lm = (double)cfg.ukf_kp_landmark_pose;
     kp.std_a = cfg.ukf_std_a;
     kp.std_yaw = cfg.ukf_std_yaw;
-    const size_t smem = sizeof(UkfSlot);
-    ASLAM_DYN_SMEM(ukf_batched_kernel, smem);
-    ukf_batched_kernel<<<st.batch, UTHREADS, smem, stream>>>(kp);
-    ASLAM_CUDA(cudaGetLastError());
-    return ASLAM_OK;
+    switch (st.ld) {
+        case 30: return launch_ukf_t<30>(kp, stream);
+        case 36: return launch_ukf_t<36>(kp, stream);
+        default:
+            set_error("ukf_batched: built for max_state_dim <= 36 (padded dimensions 30 and 36); larger maps: aslam_large_ukf_*");
+            return ASLAM_ERR_UNSUPPORTED;
+    }
 }
 
 }  // namespace aslam

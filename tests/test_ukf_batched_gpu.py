@@ -77,7 +77,60 @@ def test_ukf_batch_is_reproducible_through_growth(aslam):
     assert np.mean(out[0][2] == 19) > 0.9  # (a free-running filter that has gone indefinite may map a spurious landmark)
 
 
-def test_ukf_cap_above_reference_is_refused(aslam):
+def test_ukf_cap_beyond_the_batched_kernels_is_refused(aslam):
+    """The batched UKF is built for max_state_dim <= 36 (the reference's cap 30, and the cfg3 shape); beyond that the
+    create call refuses (larger UKF maps go through aslam_large_ukf_*)."""
     with pytest.raises(aslam.capi.AslamError) as e:
         aslam.BatchedFilter("ukf", 1, 0, max_state_dim=64)
     assert e.value.status == aslam.capi.ASLAM_ERR_UNSUPPORTED
+    f = aslam.BatchedFilter("ukf", 1, 0, max_state_dim=36)
+    assert f.ld == 36
+    f.close()
+
+
+def test_cfg3_shape_batched_ukf(aslam, orc):
+    """SURVEY 2.2 K2 at the cfg3 shape: 16 landmarks, N = 35, n_aug = 37, 75 sigma points, max_state_dim = 36 (the
+    only constant lifted, as for the EKF). 64 filters with their own seeds, 28 messages (all 16 landmarks are
+    promoted on the 10th; a reference UKF with that many landmarks turns indefinite within a few more messages,
+    SURVEY 3.2 -- the LLT failures are part of the comparison, fail column equal), every message of every filter
+    checked against the oracle (Eigen's unblocked LLT above size 32 as well: the oracle's stated rule,
+    oracle/dense.hpp). Once a filter has gone chaotic a last-bit difference can flip a float cast (see
+    test_cfg2_*): the comparison stops at the first such blip, which must come late and stay below 1e-5."""
+    lmx, lmy = aslam.map_cfg3()
+    B, T, L = 64, 28, 16
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=aslam.replay.SEED_CFG3)
+    f = aslam.BatchedFilter("ukf", B, 0, max_state_dim=36)
+    os_ = [orc.Filter("ukf", max_state_dim=36) for _ in range(B)]
+    worst, fails, checked = [0.0, 0.0], 0, 0
+    dead = np.zeros(B, bool)      # filters that have had a float-cast blip: free-running, no longer comparable
+    first_blip = T
+    for t in range(T):
+        f.set_observations(rp.range[t].ravel(), rp.bearing[t].ravel())
+        f.step(rp.x[t], rp.y[t], rp.yaw[t], rp.vx[t], rp.az[t], rp.dt[t])
+        s = f.get_state()
+        fk = f.get_llt_fail()
+        for b in range(B):
+            o = os_[b]
+            o.set_observations(rp.range[t, b], rp.bearing[t, b])
+            o.step(rp.x[t, b], rp.y[t, b], rp.yaw[t, b], rp.vx[t, b], rp.az[t, b], rp.dt[t, b])
+            if dead[b]:
+                continue
+            X, Z, P = o.state()
+            n = o.N
+            assert int(s["N"][b]) == n, (t, b)
+            assert int(fk[b]) == o.llt_fail(), (t, b)
+            fails += o.llt_fail() >= 0
+            ex, ep = relerr(s["X"][b, :n], X), relerr(s["P"][b, :n, :n], P)
+            if max(ex, ep) > TOL_F64:
+                assert max(ex, ep) <= 1e-5, (t, b, ex, ep)
+                dead[b] = True
+                first_blip = min(first_blip, t)
+            else:
+                checked += 1
+                worst = [max(worst[0], ex), max(worst[1], ep)]
+    print("cfg3-shape UKF: %d filter-messages at <= 1e-9 (worst X %.2e P %.2e), N max %d, LLT failures compared %d, "
+          "filters dropped after a float-cast blip %d (first at message %d)"
+          % (checked, worst[0], worst[1], int(s["N"].max()), fails, int(dead.sum()), first_blip))
+    # promotion (message 9) and the first updates at N = 35 are compared on every filter
+    assert int(s["N"].max()) == 35 and first_blip >= 10 and checked >= 0.7 * B * T
+    f.close()

@@ -1,3 +1,7 @@
+// NOT PART OF THE PRODUCT LIBRARY (tools/probes/): a measured negative result kept for the record -- 74 M updates/s
+// against 107 M for the kernel in csrc/ekf_batched.cu. It needs csrc/ekf_batched_common.cuh and
+// a `case 36` hook in launch_ekf_batched to be built again.
+//
 // K1b: batched EKF-SLAM step, one WARP per filter, covariance update on the FP64 tensor pipe
 // (mma.sync.m8n8k4.f64 = SASS DMMA.8x8x4). Same contract and same mathematics as ekf_batched.cu
 // (updateZandA + slam, src/ekf/ekf.cpp:137-213, 293-311; models of include/awesome_slam/common.h:46-90),

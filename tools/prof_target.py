@@ -1,7 +1,7 @@
 """Short single-GPU programs for ncu captures (B200_PROFILING.md): a handful of launches of one kernel.
 
   python tools/prof_target.py batched [B] [msgs]   cfg3 batched EKF kernel, B filters at N = 35
-  python tools/prof_target.py ukf [B] [msgs]       batched UKF kernel
+  python tools/prof_target.py ukf [B] [msgs]       batched UKF kernel, cfg3 shape (n = 35); ukf19: the cfg2 shape (n = 19)
   python tools/prof_target.py large [side] [m]     cfg4 large-map EKF step (side^2 landmarks)
   python tools/prof_target.py ukf_large [side]     cfg5 large-map UKF step
   python tools/prof_target.py laser [B]            laser front end, B scans of the cfg3 map
@@ -15,17 +15,18 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import awesomeslam_b200 as A  # noqa: E402
 
 
-def batched(kind, B, msgs):
-    lmx, lmy = A.map_cfg3()
+def batched(kind, B, msgs, small=False):
+    lmx, lmy = A.map_cfg1() if small else A.map_cfg3()
+    L = len(lmx)
     warm = 24
     rp = A.Replay(lmx, lmy, B, warm + 4 * msgs, seed0=A.replay.SEED_CFG3)
-    f = A.BatchedFilter(kind, B, 0, max_state_dim=36)
+    f = A.BatchedFilter(kind, B, 0, max_state_dim=30 if small else 36)
     a = [rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing]
-    f.run_host(warm, *[v[:warm] for v in a], 16)
+    f.run_host(warm, *[v[:warm] for v in a], L)
     f.sync()
     for k in range(4):
         s = slice(warm + k * msgs, warm + (k + 1) * msgs)
-        f.run_host(msgs, *[v[s] for v in a], 16)
+        f.run_host(msgs, *[v[s] for v in a], L)
     f.sync()
     st = f.get_state(want_P=False, want_assoc=False)
     print(kind, "N", int(st["N"].min()), int(st["N"].max()), "status", int(st["status"].max()))
@@ -79,8 +80,9 @@ if __name__ == "__main__":
     arg = [int(v) for v in sys.argv[2:]]
     if mode == "laser":
         laser(arg[0] if arg else 65536)
-    elif mode in ("batched", "ukf"):
-        batched("ekf" if mode == "batched" else "ukf", arg[0] if arg else 65536, arg[1] if len(arg) > 1 else 8)
+    elif mode in ("batched", "ukf", "ukf19"):
+        batched("ekf" if mode == "batched" else "ukf", arg[0] if arg else 65536, arg[1] if len(arg) > 1 else 8,
+                small=mode == "ukf19")
     elif mode == "large":
         large(arg[0] if arg else 64, arg[1] if len(arg) > 1 else 8)
     elif mode == "ukf_large":
