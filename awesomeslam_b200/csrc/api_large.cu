@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <string>
 #include <vector>
 
 #include "dense_fp64.hpp"
@@ -20,6 +21,8 @@ void large_ukf_destroy(aslam_large* h);
 aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m);
 aslam_status large_ukf_load_z(aslam_large* h, const double* Z);
 aslam_status large_ukf_status(aslam_large* h, uint32_t* status, int32_t* llt_fail);
+aslam_status large_ukf_set_precision(aslam_large* h, int mode);
+aslam_status large_ukf_products_ms(aslam_large* h, float* ms);
 }  // namespace aslam
 
 using namespace aslam;
@@ -394,6 +397,56 @@ aslam_status aslam_dense_trsm(void* stream, double* d_B, size_t ldb, int32_t m, 
                               int32_t n, const double* d_inv_blocks) {
     if (!d_B || !d_L || !d_inv_blocks) return ASLAM_ERR_ARG;
     return dense::trsm_right_lower_t((cudaStream_t)stream, d_B, ldb, m, d_L, ldl, n, d_inv_blocks, nullptr);
+}
+
+aslam_status aslam_large_ukf_set_precision(aslam_large* h, int32_t mode) {
+    if (!h || h->kind != ASLAM_KIND_UKF) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    return large_ukf_set_precision(h, mode);
+}
+
+aslam_status aslam_large_ukf_products_ms(aslam_large* h, float* ms) {
+    if (!h || h->kind != ASLAM_KIND_UKF) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(h->device));
+    return large_ukf_products_ms(h, ms);
+}
+
+aslam_status aslam_dense_gemm_nt_tf32(void* stream, int32_t M, int32_t N, int32_t K, const double* d_A, size_t lda,
+                                      const double* d_B, size_t ldb, double* d_C, size_t ldc, double alpha, double beta,
+                                      int32_t lower_only, int32_t passes) {
+    if (!d_A || !d_B || !d_C || M <= 0 || N <= 0 || K <= 0 || (passes != 1 && passes != 3)) return ASLAM_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t ldf = dense::tf32_padded_k(K);
+    float *ahi = nullptr, *alo = nullptr, *bhi = nullptr, *blo = nullptr;
+    int* err = nullptr;
+    ASLAM_CUDA(cudaMalloc((void**)&ahi, (size_t)M * ldf * sizeof(float)));
+    ASLAM_CUDA(cudaMalloc((void**)&alo, (size_t)M * ldf * sizeof(float)));
+    ASLAM_CUDA(cudaMalloc((void**)&bhi, (size_t)N * ldf * sizeof(float)));
+    ASLAM_CUDA(cudaMalloc((void**)&blo, (size_t)N * ldf * sizeof(float)));
+    ASLAM_CUDA(cudaMalloc((void**)&err, sizeof(int)));
+    ASLAM_CUDA(cudaMemsetAsync(err, 0, sizeof(int), st));
+    aslam_status rc = dense::split_tf32(st, d_A, lda, M, K, ahi, alo);
+    if (rc == ASLAM_OK) rc = dense::split_tf32(st, d_B, ldb, N, K, bhi, blo);
+    dense::Epilogue e;
+    e.alpha = alpha;
+    e.beta = beta;
+    e.lower_only = lower_only != 0;
+    if (rc == ASLAM_OK) rc = dense::tf32_gemm_nt(st, M, N, K, ahi, alo, bhi, blo, d_C, ldc, e, passes, err);
+    int herr = 0;
+    if (rc == ASLAM_OK && !cuda_ok(cudaMemcpyAsync(&herr, err, sizeof(int), cudaMemcpyDeviceToHost, st), "tf32 err")) rc = ASLAM_ERR_CUDA;
+    if (!cuda_ok(cudaStreamSynchronize(st), "tf32 gemm")) rc = ASLAM_ERR_CUDA;
+    cudaFree(ahi); cudaFree(alo); cudaFree(bhi); cudaFree(blo); cudaFree(err);
+    if (rc == ASLAM_OK && herr) {
+        set_error("tf32 gemm: a wait inside the tcgen05 pipeline expired (code " + std::to_string(herr) + ")");
+        return ASLAM_ERR_CUDA;
+    }
+    return rc;
+}
+
+aslam_status aslam_probe_tf32_tflops(int32_t device, double* tflops) {
+    if (!tflops) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaSetDevice(device));
+    return dense::probe_tf32_tflops(tflops);
 }
 
 aslam_status aslam_probe_dmma_tflops(int32_t device, double* tflops) {

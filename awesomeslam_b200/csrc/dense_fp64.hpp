@@ -62,5 +62,17 @@ aslam_status side_stream(int slot, SideStream** out);
 // Measured throughput of the DMMA pipe of the current device, TFLOP/s (roofline denominator for the GEMMs).
 aslam_status probe_dmma_tflops(double* tflops);
 
+// ---- TF32 variant (gemm_tf32_tcgen05.cu): tcgen05.mma kind::tf32, accumulator in TMEM, operands by TMA.
+// hi = tf32(x), lo = tf32(x - hi) of an FP64 matrix [rows][ld], stored FP32 [rows][tf32_padded_k(K)] (lo may be null).
+size_t tf32_padded_k(int K);
+aslam_status split_tf32(cudaStream_t st, const double* src, size_t ld, int rows, int K, float* hi, float* lo);
+// C (FP64, M x N, ldc) = alpha * A B' + the Epilogue terms. passes = 1: A_hi B_hi'; passes = 3: + A_hi B_lo' + A_lo B_hi'.
+// *d_err (device int, 0 on entry) becomes non-zero when a bounded wait inside the kernel expired.
+aslam_status tf32_gemm_nt(cudaStream_t st, int M, int N, int K, const float* Ahi, const float* Alo, const float* Bhi,
+                          const float* Blo, double* C, size_t ldc, const Epilogue& e, int passes, int* d_err,
+                          uint64_t* launches = nullptr);
+// Measured kind::tf32 throughput of the current device (MMAs issued back to back from shared memory), TFLOP/s.
+aslam_status probe_tf32_tflops(double* tflops);
+
 }  // namespace dense
 }  // namespace aslam

@@ -59,6 +59,14 @@ struct UkfLarge {
     double* rdiag = nullptr;   // [n] diagonal of R
     double* invP = nullptr;    // [nb][64*64]
     double* invS = nullptr;
+    // TF32 variant of the three sigma-point products (gemm_tf32_tcgen05.cu): 0 = FP64 (default), 1 = TF32, 3 = 3xTF32
+    int precision = 0;
+    float* Dhi = nullptr;      // [n][tf32_padded_k(ns)] hi / lo parts of D and DZ
+    float* Dlo = nullptr;
+    float* Zhi = nullptr;
+    float* Zlo = nullptr;
+    int* tf32_err = nullptr;
+    cudaEvent_t evg0 = nullptr, evg1 = nullptr;  // around the three sigma-point products (incl. the TF32 split)
     int* fail = nullptr;       // [2]: first failing pivot of chol(P), chol(S)
     uint32_t* status = nullptr;
     float lambda = 0, wsq = 0;
@@ -348,8 +356,9 @@ __global__ void fill_diag_kernel(int n, double* q, double* r, double kq, double 
     r[i] = kr;                // ukf.cpp:59,242
 }
 
-__global__ void fail_to_status_kernel(const int* fail, uint32_t* status) {
+__global__ void fail_to_status_kernel(const int* fail, const int* tf32_err, uint32_t* status) {
     if (fail[0] >= 0 || fail[1] >= 0) atomicOr(status, (uint32_t)ASLAM_ST_LLT_FAILED);
+    if (tf32_err && *tf32_err) atomicOr(status, (uint32_t)ASLAM_ST_STEP_TIMEOUT);  // a bounded tcgen05 wait expired
 }
 
 }  // namespace
@@ -399,6 +408,8 @@ aslam_status large_ukf_create(aslam_large* h) {
     A((void**)&u->fail, 2 * sizeof(int));
     A((void**)&u->status, sizeof(uint32_t));
     if (rc != ASLAM_OK) return rc;
+    ASLAM_CUDA(cudaEventCreate(&u->evg0));
+    ASLAM_CUDA(cudaEventCreate(&u->evg1));
     ASLAM_CUDA(cudaMemsetAsync(u->Z, 0, n * sizeof(double), h->stream));
     ASLAM_CUDA(cudaMemsetAsync(u->status, 0, sizeof(uint32_t), h->stream));
     ASLAM_CUDA(cudaMemsetAsync(u->fail, 0xff, 2 * sizeof(int), h->stream));
@@ -413,11 +424,39 @@ void large_ukf_destroy(aslam_large* h) {
     UkfLarge* u = static_cast<UkfLarge*>(h->ukf);
     if (!u) return;
     void* ptrs[] = {u->Z, u->Lb, u->S, u->Tc, u->D, u->DZ, u->pose, u->mean, u->zpred, u->d0, u->dz0, u->dzv, u->gvec, u->coef,
-                    u->qdiag, u->rdiag, u->invP, u->invS, u->fail, u->status};
+                    u->qdiag, u->rdiag, u->invP, u->invS, u->fail, u->status, u->Dhi, u->Dlo, u->Zhi, u->Zlo, u->tf32_err};
     for (void* p : ptrs)
         if (p) cudaFree(p);
+    if (u->evg0) cudaEventDestroy(u->evg0);
+    if (u->evg1) cudaEventDestroy(u->evg1);
     delete u;
     h->ukf = nullptr;
+}
+
+// Precision of the three sigma-point products: 0 FP64 (DMMA, the parity path), 1 TF32, 3 error-compensated 3xTF32
+// (tcgen05.mma kind::tf32, accumulators in TMEM). The mean, the w0 rank-1 terms, both factorisations and the solves stay
+// in FP64 whatever the mode.
+aslam_status large_ukf_set_precision(aslam_large* h, int mode) {
+    UkfLarge* u = static_cast<UkfLarge*>(h->ukf);
+    if (!u || (mode != 0 && mode != 1 && mode != 3)) return ASLAM_ERR_ARG;
+    if (mode && !u->Dhi) {
+        const size_t bytes = (size_t)u->n * dense::tf32_padded_k(u->ns) * sizeof(float);
+        float** bufs[] = {&u->Dhi, &u->Dlo, &u->Zhi, &u->Zlo};
+        for (float** b : bufs) ASLAM_CUDA(cudaMalloc((void**)b, bytes));
+        ASLAM_CUDA(cudaMalloc((void**)&u->tf32_err, sizeof(int)));
+        ASLAM_CUDA(cudaMemset(u->tf32_err, 0, sizeof(int)));
+    }
+    u->precision = mode;
+    return ASLAM_OK;
+}
+
+// CUDA-event time of the three sigma-point products of the last step (TF32 modes: the hi/lo split included)
+aslam_status large_ukf_products_ms(aslam_large* h, float* ms) {
+    UkfLarge* u = static_cast<UkfLarge*>(h->ukf);
+    if (!u || !ms || !h->timed) return ASLAM_ERR_ARG;
+    ASLAM_CUDA(cudaEventSynchronize(u->evg1));
+    ASLAM_CUDA(cudaEventElapsedTime(ms, u->evg0, u->evg1));
+    return ASLAM_OK;
 }
 
 // Z of aslam_large_load_state; NULL: Z = h(X) (every landmark "seen" where the state says it is)
@@ -520,19 +559,35 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     e.r1 = u->w0 - u->wc;
     e.lower_only = true;
     e.u = u->d0; e.v = u->d0; e.diag = u->qdiag;
-    rc = dense::dgemm_nt(st, n, n, u->ns, u->D, u->nsld, u->D, u->nsld, h->P, u->ld, e, &nl);
+    const int tf = u->precision;
+    if (h->timed && u->evg0) ASLAM_CUDA(cudaEventRecord(u->evg0, st));
+    if (tf) {  // hi / lo FP32 copies of the centred sigma-point matrices (the only values that are rounded)
+        rc = dense::split_tf32(st, u->D, u->nsld, n, u->ns, u->Dhi, tf == 3 ? u->Dlo : nullptr);
+        if (rc != ASLAM_OK) return rc;
+        rc = dense::split_tf32(st, u->DZ, u->nsld, n, u->ns, u->Zhi, tf == 3 ? u->Zlo : nullptr);
+        if (rc != ASLAM_OK) return rc;
+        nl += 2;
+        mark("tf32 split");
+    }
+    auto gemm = [&](const double* A, const float* Ahi, const float* Alo, const double* B, const float* Bhi,
+                    const float* Blo, double* C) -> aslam_status {
+        if (tf) return dense::tf32_gemm_nt(st, n, n, u->ns, Ahi, Alo, Bhi, Blo, C, u->ld, e, tf, u->tf32_err, &nl);
+        return dense::dgemm_nt(st, n, n, u->ns, A, u->nsld, B, u->nsld, C, u->ld, e, &nl);
+    };
+    rc = gemm(u->D, u->Dhi, u->Dlo, u->D, u->Dhi, u->Dlo, h->P);
     if (rc != ASLAM_OK) return rc;
     mark("P gemm");
     // M = wc DZ DZ' + R: the positive definite part of S (its rank-1 term c dz_0 dz_0' is applied analytically below)
     e.u = nullptr; e.v = nullptr; e.r1 = 0.0; e.diag = u->rdiag;
-    rc = dense::dgemm_nt(st, n, n, u->ns, u->DZ, u->nsld, u->DZ, u->nsld, u->S, u->ld, e, &nl);
+    rc = gemm(u->DZ, u->Zhi, u->Zlo, u->DZ, u->Zhi, u->Zlo, u->S);
     if (rc != ASLAM_OK) return rc;
     mark("M gemm");
     e.lower_only = false;
     e.r1 = u->w0 - u->wc;
     e.u = u->d0; e.v = u->dz0; e.diag = nullptr;
-    rc = dense::dgemm_nt(st, n, n, u->ns, u->D, u->nsld, u->DZ, u->nsld, u->Tc, u->ld, e, &nl);
+    rc = gemm(u->D, u->Dhi, u->Dlo, u->DZ, u->Zhi, u->Zlo, u->Tc);
     if (rc != ASLAM_OK) return rc;
+    if (h->timed && u->evg1) ASLAM_CUDA(cudaEventRecord(u->evg1, st));
     mark("Tc gemm");
     // ---- M = Lm Lm';  [W; a'; b'] = [Tc; dz_0'; dz'] Lm^-T  (a = Lm^-1 dz_0, b = Lm^-1 dz ride along as two extra rows)
     rc = dense::cholesky_lower(st, u->S, u->ld, n, u->invS, u->fail + 1, &nl);
@@ -561,7 +616,7 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     if (rc != ASLAM_OK) return rc;
     rc = dense::symmetrize_from_lower(st, h->P, u->ld, n, &nl);
     if (rc != ASLAM_OK) return rc;
-    fail_to_status_kernel<<<1, 1, 0, st>>>(u->fail, u->status);
+    fail_to_status_kernel<<<1, 1, 0, st>>>(u->fail, tf ? u->tf32_err : nullptr, u->status);
     ASLAM_CUDA(cudaGetLastError());
     ++nl;
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, st));

@@ -396,6 +396,16 @@ class LargeFilter:
                                                     capi.ptr(rng), capi.ptr(brg), rng.size, capi.ptr(assoc)))
         return None if assoc is None else assoc[:self._m]
 
+    def set_precision(self, mode):
+        """UKF: precision of the three sigma-point products: 0 FP64 (default), 1 TF32, 3 = 3xTF32 (tcgen05 + TMEM)."""
+        capi.check(self._lib.aslam_large_ukf_set_precision(self._h, int(mode)))
+
+    def products_ms(self):
+        """UKF: CUDA-event time of the three sigma-point products of the last step (TF32 modes: split included)."""
+        ms = C.c_float()
+        capi.check(self._lib.aslam_large_ukf_products_ms(self._h, C.byref(ms)))
+        return float(ms.value)
+
     def set_timing(self, on=True):
         """EKF: record CUDA events around the streaming update of every later step (off by default: the event keeps
         the update from being launched early behind the solve kernel)."""

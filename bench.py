@@ -639,14 +639,44 @@ def ukf_large_leg(args, torch, dev):
         launches = f.launch_count - l0
         if it >= max(args.warmup, 3):
             ms.append(t)
-    X, _ = f.get_state(want_P=False)
+    X, P = f.get_state()
     status, fail = f.status()
     assert np.all(np.isfinite(X)) and status == 0 and fail == -1
-    f.close()
+    prod_ms64 = f.products_ms()
     tf = C.c_double()
     A.capi.check(A.capi.lib().aslam_probe_dmma_tflops(dev.index, C.byref(tf)))
     step_ms = float(np.mean(ms))
     N, NS = n, 2 * n + 5
+    # TF32 variant of the three sigma-point products (tcgen05 kind::tf32, accumulators in TMEM), separately toleranced:
+    # same state and message, compared with the FP64 path of this run
+    t32 = C.c_double()
+    A.capi.check(A.capi.lib().aslam_probe_tf32_tflops(dev.index, C.byref(t32)))
+    prod_flop = 2.0 * N * N * NS * 2  # P and M lower halves + Tc full = 2 full products
+    tf32_rows = {}
+    for mode, name in ((1, "tf32"), (3, "tf32x3")):
+        f.set_precision(mode)
+        tms, pms = [], []
+        for it in range(3 + min(args.steps, 10)):
+            f.load_state(X0, P0)
+            f.step(0.01, -0.01, 0.002, 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
+            if it >= 3:
+                tms.append(f.last_kernel_ms())
+                pms.append(f.products_ms())
+        Xt, Pt = f.get_state()
+        st_t, fail_t = f.status()
+        assert st_t == 0 and fail_t == -1
+        issued = prod_flop * (1 if mode == 1 else 3)
+        tf32_rows[name] = {
+            "ms_per_step": float(np.mean(tms)), "products_ms": float(np.mean(pms)), "products_ms_fp64": prod_ms64,
+            "relerr_X_vs_fp64": float(np.max(np.abs(Xt - X)) / np.max(np.abs(X))),
+            "relerr_P_vs_fp64": float(np.max(np.abs(Pt - P)) / np.max(np.abs(P))),
+            "roofline": {"bound": "tensor", "kernel": "tf32_gemm_nt_kernel<%d> (TMA + tcgen05.mma kind::tf32, TMEM)" % mode,
+                         "unit": "TFLOP/s", "achieved": issued / (float(np.mean(pms)) * 1e-3) / 1e12, "peak": t32.value,
+                         "frac": issued / (float(np.mean(pms)) * 1e-3) / 1e12 / t32.value if t32.value else None,
+                         "note": "issued TF32 flop of the three products (x3 for the hi/lo split) over their "
+                                 "CUDA-event time, FP64->hi/lo split kernels included",
+                         "peak_source": "aslam_probe_tf32_tflops (kind::tf32 M128 N256 K8 from shared memory, this run)"}}
+    f.close()
     executed = ((N ** 3) / 3 * 2 + 2 * N * N * NS + N * N * NS * 2 + N ** 3 * 2)  # 2 chol, P+M lower, Tc full, trsm+syrk
     reference_form = (N + 2) ** 3 / 3 + 3 * 2 * N * N * NS + 2 * N ** 3 * 4       # ~176 GF
     return {"workload": "cfg5: large-map UKF n=2051 (1024 landmarks), 4107 sigma points, FP64",
@@ -655,7 +685,8 @@ def ukf_large_leg(args, torch, dev):
                          "achieved": executed / (step_ms * 1e-3) / 1e12, "peak": tf.value,
                          "frac": executed / (step_ms * 1e-3) / 1e12 / tf.value if tf.value else None,
                          "executed_flop_per_step": executed, "reference_form_flop_per_step": reference_form,
-                         "peak_source": "aslam_probe_dmma_tflops (DMMA chain, this run)"}}
+                         "peak_source": "aslam_probe_dmma_tflops (DMMA chain, this run)"},
+            "products_ms": prod_ms64, "tf32_variant": tf32_rows}
 
 
 _REAL_STDOUT = None

@@ -274,6 +274,20 @@ aslam_status aslam_dense_trsm(void* stream, double* d_B, size_t ldb, int32_t m, 
                               int32_t n, const double* d_inv_blocks);
 /* Measured throughput of the FP64 tensor pipe (DMMA) of `device`, TFLOP/s. */
 aslam_status aslam_probe_dmma_tflops(int32_t device, double* tflops);
+/* TF32 variant of the sigma-point products of the large-map UKF (north_star: "FP64/TF32 tensor-core tiles via TMA"):
+ * tcgen05.mma kind::tf32 with the accumulator in tensor memory, operands by TMA. mode 0 = FP64 (default, the parity
+ * path), 1 = TF32, 3 = error-compensated 3xTF32 (hi/lo split). The sigma-point mean, the w0 rank-1 terms, the
+ * factorisations and the solves stay FP64 in every mode. Tolerances are stated separately (tests/util.py). */
+aslam_status aslam_large_ukf_set_precision(aslam_large* h, int32_t mode);
+/* CUDA-event time (ms) of the three sigma-point products of the last step, in every mode (TF32: split included). */
+aslam_status aslam_large_ukf_products_ms(aslam_large* h, float* ms);
+/* The TF32 GEMM by itself on FP64 DEVICE matrices (row-major, contraction index contiguous): C = alpha A B' + beta C,
+ * the operands are split into TF32 hi / lo parts internally. passes = 1 or 3. Synchronous. */
+aslam_status aslam_dense_gemm_nt_tf32(void* stream, int32_t M, int32_t N, int32_t K, const double* d_A, size_t lda,
+                                      const double* d_B, size_t ldb, double* d_C, size_t ldc, double alpha, double beta,
+                                      int32_t lower_only, int32_t passes);
+/* Measured kind::tf32 tensor throughput of `device` (MMAs issued back to back from shared memory), TFLOP/s. */
+aslam_status aslam_probe_tf32_tflops(int32_t device, double* tflops);
 
 /* ---------------------------------------------------------------- laser front end -------- */
 /* The step in front of the filters: the reference's sensor_landmark node,
