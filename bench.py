@@ -305,11 +305,46 @@ def batched_leg(args, torch, dist, rank, world, dev):
         st = f.get_state(want_P=False, want_assoc=False)
         assert np.all(st["N"] == 35) and not np.any(st["status"]) and np.all(np.isfinite(st["X"]))
         results[mode] = {"ms": ms, "launches": f.launch_count - l0, "clocks": clocks, "ld": f.ld}
+        if mode == "resident" and rank == 0 and not args.no_cpu:
+            results["parity"] = cfg3_parity(f, rp, B, total_msgs)
         f.close()
     per_msg = rp.nbytes_per_step()
     results["h2d_bytes_per_step"] = per_msg * FUSE
     results["d2h_bytes_per_step"] = B * results["e2e"]["ld"] * 8
     return results
+
+
+def cfg3_parity(f, rp, B, total_msgs):
+    """Driver-visible parity of the TIMED batch: after the timed region the state of 64 filters
+    spread over the batch -- first / last slot of the first / last CTA (7 filters per CTA) and 58 more -- is compared
+    with the CPU filter (oracle/_ref when built: the compiled reference) replaying the same messages from reset."""
+    from oracle import ref as R
+    ids = sorted(set([0, 6, 7, 13, B - 1, B - 2, (B - 1) // 7 * 7, (B - 1) // 7 * 7 - 1]
+                     + [int(i) for i in np.linspace(14, B - 3, 56)]))
+    ids = np.array(ids, dtype=np.int64)
+    st = f.get_state(want_P=True, want_assoc=False)
+    sl = (slice(0, total_msgs), ids)
+    c = lambda a: np.ascontiguousarray(a[sl])
+    if R.available("ekf", True):
+        sec, X, P, N = R.run_batch("ekf", ids.size, total_msgs, L_CFG3, c(rp.x), c(rp.y), c(rp.qw), c(rp.qz), c(rp.vx),
+                                   c(rp.az), c(rp.range), c(rp.bearing), host_threads(), 36, want_P=True, cap64=True)
+        kind = "reference"
+    else:
+        from oracle import oracle as O
+        O.build()
+        sec, X, P, N = O.run_batch("ekf", O.default_config(max_state_dim=64), ids.size, total_msgs, L_CFG3, c(rp.x),
+                                   c(rp.y), c(rp.yaw), c(rp.vx), c(rp.az), c(rp.dt), c(rp.range), c(rp.bearing),
+                                   host_threads(), 36, want_P=True)
+        kind = "port"
+    ex = [float(np.max(np.abs(st["X"][i] - X[k])) / np.max(np.abs(X[k]))) for k, i in enumerate(ids)]
+    ep = [float(np.max(np.abs(st["P"][i] - P[k])) / np.max(np.abs(P[k]))) for k, i in enumerate(ids)]
+    assert np.array_equal(st["N"][ids], N)
+    worst = max(max(ex), max(ep))
+    assert worst <= 1e-9, "timed cfg3 batch differs from the CPU filter: %.3e" % worst
+    return {"filters_compared": int(ids.size), "filter_ids": "0, 6, 7, 13, ..., %d, %d (first/last slots of the first/"
+            "last CTA + 56 spread over the batch)" % (B - 2, B - 1), "messages": int(total_msgs), "against": kind,
+            "worst_relerr_X": max(ex), "worst_relerr_P": max(ep),
+            "filters_beyond_1e-9": int(sum(1 for a, b in zip(ex, ep) if max(a, b) > 1e-9)), "tolerance": 1e-9}
 
 
 def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
@@ -841,6 +876,7 @@ def main():
                        "aslam_filter_read_state_async/read_wait every step"},
         "gpu_launches": res["resident"]["launches"],
         "clocks": res["resident"]["clocks"],
+        "parity": res.get("parity"),
         "roofline_batched": {
             "kernel": "ekf_batched_kernel<36,2>", "bound": "fp64",
             "achieved": per_gpu_ups * FLOP_PER_UPDATE / 1e12, "peak": fp64, "unit": "TFLOP/s",
