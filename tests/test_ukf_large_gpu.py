@@ -4,7 +4,8 @@
  * one UKF message at n = 131 (64 landmarks, Eigen's blocked-LLT regime) against the C++ oracle's verbatim
    UKFSlam::slam; at n = 35 against the same oracle (unblocked regime)
  * cfg5 full size (n = 2051, 4107 sigma points) against the vectorised numpy restatement, which tests/test_oracle.py
-   pins to the oracle; plus properties: P symmetric, positive definite, status clean
+   pins to the oracle, AND against the committed output of the C++ oracle's verbatim UKFSlam::slam at that size
+   (tests/golden/cfg5_ukf_large.npz); plus properties: P symmetric, positive definite, status clean
 Tolerance: norm-wise relative 1e-9 on X and P (FP64 path); association indices equal.
 """
 import ctypes as C
@@ -186,6 +187,17 @@ def test_cfg5_large_ukf_full_size(aslam):
     print("cfg5 n=2051 relerr X %.2e P %.2e" % (ex, ep))
     assert ex <= TOL_F64 and ep <= TOL_F64
     assert np.array_equal(P, P.T)
+    # ... and against the C++ oracle's VERBATIM UKFSlam::slam run once at this size (tests/golden/make_cfg5_golden.py,
+    # minutes on one host core): X, diag(P) and 32 sampled rows of P
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cfg5_ukf_large.npz"))
+    assert np.array_equal(assoc, g["assoc"]) and int(g["llt_fail"]) == -1
+    pmax = float(g["Pmax"])
+    gx = relerr(X, g["X"])
+    gd = float(np.max(np.abs(np.diag(P) - g["Pdiag"])) / pmax)
+    gr = float(np.max(np.abs(P[g["rows"]] - g["Prows"])) / pmax)
+    print("cfg5 n=2051 vs verbatim oracle golden: relerr X %.2e diag(P) %.2e sampled rows of P %.2e" % (gx, gd, gr))
+    assert gx <= TOL_F64 and gd <= TOL_F64 and gr <= TOL_F64
     # a second message: finite, and the LLT verdict (P - K S K' may have gone indefinite) agrees with the host
     f.step(*ODOM, rng, brg)
     X2, P2 = f.get_state()
