@@ -229,6 +229,105 @@ __global__ void __launch_bounds__(1024) trsv_lower_kernel(double* v, const doubl
     }
 }
 
+
+// ---------------------------------------------------------------------------------- 256-wide triangular solve
+// Inverse of the 256 x 256 diagonal blocks of L from the stored inverses of their 64 x 64 diagonal blocks:
+// for the block-lower-triangular T (4 x 4 blocks of 64), column block jb of T^-1 is
+//     Tinv[jb][jb] = inv64,   Tinv[i][jb] = -inv64_i * sum_{k = jb}^{i-1} T[i][k] Tinv[k][jb]    (i > jb)
+// Columns are independent: one CTA per (column block jb, 256-block b), 256 threads, each a 4 x 4 patch of the 64 x 64
+// output; operands pass through shared memory in slabs of 32. Writes the inverse (inv256, [r][c]) and its transpose
+// (inv256T, [c][r]); everything above the block diagonal stays zero (the buffers are zero-filled once).
+constexpr int TW = TRSM_WIDE;
+
+// acc += A (64 x 64, row-major lda, rows >= a_rows read as 0) * B (64 x 64, row-major ldb, rows >= b_rows read as 0)
+__device__ __forceinline__ void tri_prod64(double (&acc)[4][4], const double* __restrict__ A, size_t lda, int a_rows,
+                                           const double* __restrict__ B, size_t ldb, int b_rows, double (*As)[33],
+                                           double (*Bs)[65]) {
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    for (int k0 = 0; k0 < 64; k0 += 32) {
+        __syncthreads();  // the previous slab (or the caller's last use of the tiles) is done
+        for (int e = tid; e < 64 * 32; e += 256) {
+            const int r = e >> 5, k = e & 31;
+            As[r][k] = r < a_rows ? A[(size_t)r * lda + k0 + k] : 0.0;
+        }
+        for (int e = tid; e < 32 * 64; e += 256) {
+            const int k = e >> 6, c = e & 63;
+            Bs[k][c] = (k0 + k) < b_rows ? B[(size_t)(k0 + k) * ldb + c] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int k = 0; k < 32; ++k) {
+            double a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[4 * ty + i][k];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = Bs[k][4 * tx + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) tri_inv256_kernel(const double* __restrict__ L, size_t ldl, int n,
+                                                         const double* __restrict__ inv64, double* __restrict__ inv256,
+                                                         double* __restrict__ inv256T) {
+    __shared__ double As[64][33];
+    __shared__ double Bs[32][65];
+    const int jb = blockIdx.x, b = blockIdx.y;
+    const int base = b * TW;
+    const int bs256 = min(TW, n - base);
+    const int nsub = (bs256 + 63) / 64;
+    if (jb >= nsub) return;
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    double* out = inv256 + (size_t)b * TW * TW;
+    double* outT = inv256T + (size_t)b * TW * TW;
+    auto store = [&](int i, const double (&v)[4][4]) {  // block (i, jb) of the inverse, and its transpose
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int rr = 64 * i + 4 * ty + r, cc = 64 * jb + 4 * tx + c;
+                out[(size_t)rr * TW + cc] = v[r][c];
+                outT[(size_t)cc * TW + rr] = v[r][c];
+            }
+    };
+    {
+        const double* d = inv64 + (size_t)(4 * b + jb) * BS * BS;
+        double v[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) v[r][c] = d[(4 * ty + r) * BS + 4 * tx + c];
+        store(jb, v);
+    }
+    for (int i = jb + 1; i < nsub; ++i) {
+        double acc[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[r][c] = 0.0;
+        const int rows_i = min(64, n - (base + 64 * i));  // valid rows of block row i of L
+        for (int k = jb; k < i; ++k)  // T[i][k] * Tinv[k][jb]  (Tinv[k][jb] was written by this CTA: same column)
+            tri_prod64(acc, L + (size_t)(base + 64 * i) * ldl + base + 64 * k, ldl, rows_i, out + (size_t)(64 * k) * TW + 64 * jb,
+                       TW, 64, As, Bs);
+        store(i, acc);  // parked in the output block: the second product reads it back as its right operand
+        double res[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) res[r][c] = 0.0;
+        tri_prod64(res, inv64 + (size_t)(4 * b + i) * BS * BS, BS, 64, out + (size_t)(64 * i) * TW + 64 * jb, TW, 64, As, Bs);
+        __syncthreads();  // every thread has read the parked block
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) res[r][c] = -res[r][c];
+        store(i, res);
+    }
+}
+
 __global__ void symmetrize_kernel(double* A, size_t ld, int n) {
     __shared__ double tile[32][33];
     const int bi = blockIdx.y, bj = blockIdx.x;
@@ -315,6 +414,37 @@ aslam_status trsm_right_lower_t(cudaStream_t st, double* B, size_t ldb, int m, c
         }
     }
     return ASLAM_OK;
+}
+
+
+aslam_status trsm_right_lower_t_wide(cudaStream_t st, double* B, size_t ldb, int m, const double* L, size_t ldl, int n,
+                                     const double* inv_blocks, double* inv256, double* inv256T, double* Lt, size_t ldt,
+                                     double* X, size_t ldx, uint64_t* launches) {
+    const int nb = (n + TW - 1) / TW;
+    tri_inv256_kernel<<<dim3(4, nb), 256, 0, st>>>(L, ldl, n, inv_blocks, inv256, inv256T);
+    ASLAM_CUDA(cudaGetLastError());
+    if (launches) ++*launches;
+    aslam_status rc;
+    if (nb > 1) {  // Lt[r][c] = sum_{k in blk(c)} L[r][k] inv256[k][c]: rows below the block diagonal are what is used
+        Epilogue e;
+        e.lower_only = true;
+        e.kblock = TW;
+        e.a_cols = n;
+        rc = dgemm_nt(st, n, n, TW, L, ldl, inv256T, TW, Lt, ldt, e, launches);
+        if (rc != ASLAM_OK) return rc;
+    }
+    for (int j0 = 0; j0 + TW < n; j0 += TW) {  // B[:, > j] -= B[:, j] Lt[> j, j]'
+        const int rest = n - j0 - TW;
+        Epilogue e;
+        e.alpha = -1.0;
+        e.beta = 1.0;
+        rc = dgemm_nt(st, m, rest, TW, B + j0, ldb, Lt + (size_t)(j0 + TW) * ldt + j0, ldt, B + j0 + TW, ldb, e, launches);
+        if (rc != ASLAM_OK) return rc;
+    }
+    Epilogue x;  // X[:, j] = B[:, j] inv256_j'
+    x.kblock = TW;
+    x.a_cols = n;
+    return dgemm_nt(st, m, n, TW, B, ldb, inv256, TW, X, ldx, x, launches);
 }
 
 aslam_status trsv_lower(cudaStream_t st, double* v, const double* L, size_t ldl, int n, const double* inv_blocks,

@@ -24,6 +24,12 @@ struct Epilogue {
     const double* r1_dev = nullptr;  // when set, the coefficient is read from device memory instead of r1
     const double* diag = nullptr;  // added to C[i][i]
     bool lower_only = false;       // skip tiles that lie entirely above the diagonal
+    // Block-diagonal second operand: when kblock > 0, B is [N][kblock] (the kblock x kblock diagonal blocks stacked)
+    // and column tile c contracts A's columns [blk, blk + kblock) with blk = (c / kblock) * kblock:
+    //     C[i][c] = alpha * sum_{k < kblock} A[i][blk + k] * B[c][k] + ...      (K must equal kblock)
+    // a_cols = number of valid columns of A (the tensor map zero-fills beyond it).
+    int kblock = 0;
+    int a_cols = 0;
 };
 
 // C (M x N, ldc) = alpha * A (M x K, lda) * B (N x K, ldb)' + ...   Base pointers 16-byte aligned, ld even.
@@ -42,6 +48,18 @@ aslam_status cholesky_lower(cudaStream_t st, double* A, size_t ld, int n, double
 // B (m x n, ldb) <- B * L^-T for the lower-triangular L (n x n, ldl) whose diagonal-block inverses are inv_blocks.
 aslam_status trsm_right_lower_t(cudaStream_t st, double* B, size_t ldb, int m, const double* L, size_t ldl, int n,
                                 const double* inv_blocks, uint64_t* launches);
+
+// The same solve OUT of place with 256-wide blocks (the form the large-map UKF uses): X (m x n, ldx) = B L^-T; B is
+// destroyed. inv256 / inv256T: scratch [ceil(n/256)][256*256] each (zero-filled once by the caller), Lt: scratch
+// n x ldt. Critical chain = ceil(n/256) wide GEMMs with K = 256 instead of 2 n/64 dependent ones with K = 64:
+//   inv256_j = inverse of the j-th 256 x 256 diagonal block of L (tri_inv256_kernel, from the 64-block inverses)
+//   Lt[>j, j] = L[>j, j] inv256_j      (one launch for all j: block-diagonal operand)
+//   for j: B[:, >j] -= B[:, j] Lt[>j, j]'
+//   X = B blockdiag(inv256_j)'          (one launch)
+aslam_status trsm_right_lower_t_wide(cudaStream_t st, double* B, size_t ldb, int m, const double* L, size_t ldl, int n,
+                                     const double* inv_blocks, double* inv256, double* inv256T, double* Lt, size_t ldt,
+                                     double* X, size_t ldx, uint64_t* launches);
+constexpr int TRSM_WIDE = 256;
 
 // v (n) <- L^-1 v (forward substitution with the same blocked data), one CTA.
 aslam_status trsv_lower(cudaStream_t st, double* v, const double* L, size_t ldl, int n, const double* inv_blocks,

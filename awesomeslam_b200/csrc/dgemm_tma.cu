@@ -36,6 +36,7 @@ struct GemmParams {
     const double* diag;
     const double* r1_dev;
     int lower_only;
+    int kblock;  // > 0: block-diagonal second operand (Epilogue::kblock)
 };
 
 __device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* map, int c_inner, int c_outer,
@@ -95,12 +96,13 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
     if (warp == G::NW) {  // ---------------- producer
         if (lane == 0) {
+            const int ka0 = p.kblock ? (col0 / p.kblock) * p.kblock : 0;  // block-diagonal operand: A's column window
             for (int kt = 0; kt < KT; ++kt) {
                 const int st = kt % NST;
                 if (kt >= NST) bulk::mbar_wait(&empty[st], ((kt / NST) - 1) & 1);
                 bulk::mbar_expect_tx(&full[st], (uint32_t)G::STAGE);
                 unsigned char* sa = smem + st * G::STAGE;
-                tma_load_2d(sa, &tmA, kt * BK, row0, &full[st]);
+                tma_load_2d(sa, &tmA, ka0 + kt * BK, row0, &full[st]);
                 tma_load_2d(sa + G::A_BYTES, &tmB, kt * BK, col0, &full[st]);
             }
         }
@@ -226,11 +228,13 @@ bool make_map(CUtensorMap* m, const double* base, int rows, int K, size_t ld, in
 }
 
 template <int BM, int BN, int WARPS_M, int WARPS_N>
-aslam_status launch(cudaStream_t st, const double* A, size_t lda, const double* B, size_t ldb, const GemmParams& p) {
+aslam_status launch(cudaStream_t st, const double* A, size_t lda, const double* B, size_t ldb, const GemmParams& p,
+                    int a_cols = 0) {
     using G = Geo<BM, BN, WARPS_M, WARPS_N>;
     ASLAM_DYN_SMEM((dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N>), G::SMEM);
     CUtensorMap ta, tb;
-    if (!make_map(&ta, A, p.M, p.K, lda, BM) || !make_map(&tb, B, p.N, p.K, ldb, BN)) return ASLAM_ERR_CUDA;
+    if (!make_map(&ta, A, p.M, a_cols ? a_cols : p.K, lda, BM) || !make_map(&tb, B, p.N, p.K, ldb, BN))
+        return ASLAM_ERR_CUDA;
     dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
     dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N><<<grid, G::THREADS, G::SMEM, st>>>(ta, tb, p);
     ASLAM_CUDA(cudaGetLastError());
@@ -324,8 +328,13 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K;
     p.alpha = e.alpha; p.beta = e.beta; p.r1 = e.r1; p.u = e.u; p.v = e.v; p.diag = e.diag; p.r1_dev = e.r1_dev;
     p.lower_only = e.lower_only ? 1 : 0;
+    p.kblock = e.kblock;
+    if (e.kblock && (K != e.kblock || e.kblock % 128 != 0 || e.a_cols <= 0)) {
+        set_error("dgemm_nt: block-diagonal operand needs K == kblock (a multiple of 128) and a_cols");
+        return ASLAM_ERR_ARG;
+    }
     // ragged edge (see dgemm_skinny_kernel); not when C aliases an operand (the in-place panel products)
-    const bool alias = C == A || C == B || K < 512;  // short K: the ragged tile is cheap, an extra launch is not
+    const bool alias = C == A || C == B || K < 512 || e.kblock;  // short K: the ragged tile is cheap, an extra launch is not
     int Mm = M, Nm = N;
     if (!alias && M > 128 && M % 128 != 0 && M % 128 <= SKINNY_MAX) Mm = M - M % 128;
     if (!alias && N > 128 && N % 128 != 0 && N % 128 <= SKINNY_MAX) Nm = N - N % 128;
@@ -354,8 +363,9 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     }
     const long sms = 148;
     const double cost128 = 2.0 * (double)((t128 + sms - 1) / sms), cost64 = 1.08 * (double)((t64 + sms - 1) / sms);
-    const aslam_status rc = (Nm > 64 && cost128 <= cost64) ? launch<128, 128, 4, 2>(st, A, lda, B, ldb, p)
-                                                           : launch<128, 64, 4, 2>(st, A, lda, B, ldb, p);
+    const int ac = e.kblock ? e.a_cols : 0;
+    const aslam_status rc = (Nm > 64 && cost128 <= cost64) ? launch<128, 128, 4, 2>(st, A, lda, B, ldb, p, ac)
+                                                           : launch<128, 64, 4, 2>(st, A, lda, B, ldb, p, ac);
     if (rc != ASLAM_OK) return rc;
     // the tile kernel goes to the GPU first (one CTA per SM); the ragged-edge CTAs then fit beside it
     p.M = M;

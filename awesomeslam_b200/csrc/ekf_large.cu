@@ -421,7 +421,9 @@ __global__ void __launch_bounds__(256) large_gather_fast_kernel(uint32_t n, uint
     }
     }
     if constexpr (PEER) {
-        __threadfence_system();
+        // One system-scope fence per CTA, by the thread that signals: the CTA barrier orders every thread's stores
+        // before it and the fence is cumulative, so the counter bump below publishes all of them (256 per-thread
+        // system fences here cost ~20 us per step).
         __syncthreads();
         if (tid == 0) {
             __threadfence_system();
@@ -1294,71 +1296,59 @@ __device__ __forceinline__ void warp_gauss_jordan(double* bufA, double* bufB, in
     }
 }
 
-// Cholesky factor of the (symmetric positive definite) innovation covariance by ONE warp, lane i holding row i of the
-// lower triangle in registers: S = H_o P H_o' + R with R = 0.2 I, so S >= R > 0 whenever P is positive semi-definite.
-// Right-looking, fully unrolled (static register indices): per column one rsqrt, one shuffle of the pivot and one
-// shuffle per remaining row. 19 short steps instead of the 19 long ones of a pivoted Gauss-Jordan sweep (measured:
-// the sweep kept warp 0 busy for ~27 us while the other seven warps sat in the barrier behind it). K then comes from
-// two triangular solves per column instead of a product with an explicit S^-1 -- the same 2 q^2 flop.
+// Cholesky factor of the (symmetric positive definite) innovation covariance by ONE warp, in shared memory, with
+// ROLLED loops: S = H_o P H_o' + R with R = 0.2 I, so S >= R > 0 whenever P is positive semi-definite. Lane i owns row i.
+// Right-looking: per column one broadcast load of the pivot, one rsqrt, the column scaled in place, then the
+// trailing rows updated (lane i: S(i, j) -= l_ik l_jk for k < j <= i). About 60 instructions of code: the fully
+// unrolled register version this replaces was 3,500 instructions that each step fetched cold (the kernel runs once per
+// step between two passes of the streaming update, so nothing of it is in the instruction cache): 9 -> 3 us.
 // The reference takes `S.inverse()` (PartialPivLU, ekf.cpp:301); for an SPD S both are backward stable and differ in
 // the last bits only (tests: <= 1e-9, measured ~1e-16). Returns false -- and the caller falls back to the pivoted sweep
-// -- when a pivot is not positive.
+// -- when a pivot is not positive. The factor overwrites the lower triangle of S (row stride ld), invd = 1 / diagonal.
 template <int QT>
 __device__ __forceinline__ bool warp_cholesky(double* S, int ld, int q, int lane, double* invd) {
-    // lane i holds row i of the lower triangle in registers (static indices: fully unrolled); right-looking: per column
-    // one shuffle of the pivot, one rsqrt, one shuffle + fma per remaining column. The factor is written back over
-    // the lower triangle of S (row stride ld), the reciprocal diagonal to invd.
-    double s[QT];
-#pragma unroll
-    for (int j = 0; j < QT; ++j) s[j] = (lane < q && j <= lane && j < q) ? S[lane * ld + j] : 0.0;
     bool ok = true;
-#pragma unroll
-    for (int k = 0; k < QT; ++k) {
-        const double akk = __shfl_sync(0xffffffffu, s[k], k);
-        const bool live = k < q;  // warp-uniform
-        if (live && !(akk > 0.0)) ok = false;
-        const double inv = live ? rsqrt(akk) : 1.0;
-        const double lik = lane == k ? akk * inv : s[k] * inv;  // column k of L (rows >= k; zero above)
-        s[k] = live ? lik : s[k];
-        if (lane == k) invd[k] = inv;
-#pragma unroll
-        for (int j = k + 1; j < QT; ++j) {
-            const double ljk = __shfl_sync(0xffffffffu, lik, j);
-            if (live && j < q && lane >= j) s[j] = fma(-lik, ljk, s[j]);
+#pragma unroll 1
+    for (int k = 0; k < q; ++k) {
+        const double akk = S[k * ld + k];
+        if (!(akk > 0.0)) ok = false;
+        const double inv = rsqrt(akk);
+        double lik = 0.0;
+        if (lane >= k && lane < q) {
+            lik = lane == k ? akk * inv : S[lane * ld + k] * inv;
+            S[lane * ld + k] = lik;
         }
-    }
-    if (lane < q) {
-#pragma unroll
-        for (int j = 0; j < QT; ++j)
-            if (j <= lane) S[lane * ld + j] = s[j];
+        if (lane == k) invd[k] = inv;
+        __syncwarp();
+        if (lane > k && lane < q) {
+#pragma unroll 4
+            for (int j = k + 1; j <= lane; ++j) S[lane * ld + j] = fma(-lik, S[j * ld + k], S[lane * ld + j]);
+        }
+        __syncwarp();
     }
     return ok;
 }
 
-// W = L^-1 (lower triangular), lane c computing column c by forward substitution in registers:
-// W(i, c) = -(sum_{c <= j < i} L(i, j) W(j, c)) / L(i, i), W(c, c) = 1 / L(c, c). Every lane runs the full (unrolled)
-// triangle with zeros above its own diagonal, so the loads of L are warp-wide broadcasts and the code has no
-// lane-dependent control flow; two partial sums per row halve the dependent chain.
+// W = L^-1 (lower triangular) by forward substitution, lane c computing column c in place in W (pitch ldw, zero above
+// the diagonal on entry): W(c, c) = 1 / L(c, c), W(i, c) = -(sum_{c <= j < i} L(i, j) W(j, c)) / L(i, i). Rolled loops
+// (see warp_cholesky); two partial sums halve the dependent chain.
 template <int QT>
 __device__ __forceinline__ void warp_lower_inverse(const double* L, int ld, int q, int lane, const double* invd,
-                                                   double* W) {
-    double w[QT];
-#pragma unroll
-    for (int j = 0; j < QT; ++j) w[j] = (j == lane && lane < q) ? invd[j] : 0.0;
-#pragma unroll
-    for (int i = 1; i < QT; ++i) {
-        double acc0 = 0.0, acc1 = 0.0;
-#pragma unroll
-        for (int jx = 0; jx < i; jx += 2) {
-            acc0 = fma(L[i * ld + jx], w[jx], acc0);
-            if (jx + 1 < i) acc1 = fma(L[i * ld + jx + 1], w[jx + 1], acc1);
-        }
-        if (i < q && i > lane) w[i] = -(acc0 + acc1) * invd[i];
-    }
+                                                   double* W, int ldw) {
     if (lane < q) {
-#pragma unroll
-        for (int i = 0; i < QT; ++i)
-            if (i < q) W[i * ld + lane] = w[i];
+        W[lane * ldw + lane] = invd[lane];
+#pragma unroll 1
+        for (int i = lane + 1; i < q; ++i) {
+            double acc0 = 0.0, acc1 = 0.0;
+            int j = lane;
+#pragma unroll 2
+            for (; j + 1 < i; j += 2) {
+                acc0 = fma(L[i * ld + j], W[j * ldw + lane], acc0);
+                acc1 = fma(L[i * ld + j + 1], W[(j + 1) * ldw + lane], acc1);
+            }
+            if (j < i) acc0 = fma(L[i * ld + j], W[j * ldw + lane], acc0);
+            W[i * ldw + lane] = -(acc0 + acc1) * invd[i];
+        }
     }
 }
 
@@ -1455,7 +1445,7 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
     constexpr int LD = QT + 1;
     __shared__ double S[QT * LD];
     __shared__ double T[QT * LD];
-    __shared__ double Sinv[QT * QT];
+    __shared__ __align__(16) double Sinv[QT * QT];
     __shared__ double s_hval[QT][5];
     __shared__ int s_hk[QT][5], s_hnnz[QT], s_rows[QT], s_piv[QT], s_perm[QT];
     __shared__ double s_y[QT], s_rdiag[QT], s_invd[QT];
@@ -1506,10 +1496,16 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
     trace_mark(trace, epoch, 8);  // own columns gathered
     if constexpr (MODE == SOLVE_PEER) {
         if (mine) {
+            // destination loop outside and ROLLED: with it unrolled inside the 20 rows the kernel grew to 12,000
+            // instructions (192 KB) -- more than the instruction cache holds next to the streaming update, and the
+            // straight-line factorisation of warp 0 then ran from cold instruction fetches every step (17 us instead of 3)
+#pragma unroll 1
+            for (int p = 0; p < ps.world; ++p) {
+                double* Ep = ps.E[p] + t;
 #pragma unroll
-            for (int k = 0; k < QT; ++k)
-                if (k < q)
-                    for (int p = 0; p < ps.world; ++p) ps.E[p][(size_t)k * n + t] = pht[k];
+                for (int k = 0; k < QT; ++k)
+                    if (k < q) Ep[(size_t)k * n] = pht[k];
+            }
         }
         if (blockIdx.x == 0) {  // the rows of the q x q block this shard owns
             for (int idx = tid; idx < QT * QT; idx += 256) {
@@ -1517,11 +1513,14 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
                 const uint32_t r1 = (uint32_t)s_rows[k1];
                 if (k1 < q && k2 < q && r1 >= rb && r1 < re) {
                     const double v = pred_entry(P, ldp, rb, r1, (uint32_t)s_rows[k2], a00, a10, kq);
+#pragma unroll 1
                     for (int p = 0; p < ps.world; ++p) ps.E[p][exch_psub_offset(q_ub, n) + idx] = v;
                 }
             }
         }
-        __threadfence_system();
+        // One system-scope fence per CTA, by the thread that signals: the CTA barrier orders every thread's stores
+        // before it and the fence is cumulative, so the counter bump below publishes all of them (256 per-thread
+        // system fences here cost ~20 us per step).
         __syncthreads();
         if (tid == 0) {
             __threadfence_system();
@@ -1544,10 +1543,16 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
     }
     const bool abort_step = MODE == SOLVE_PEER && s_abort != 0;
     // ---- (P H_o')(t, :) of every row t and the q x q block P(rows, rows)
-    if constexpr (MODE != SOLVE_DIRECT) {
+    if constexpr (MODE == SOLVE_EXCH) {
 #pragma unroll
-        for (int k = 0; k < QT; ++k)
-            pht[k] = (k < q && !abort_step) ? ld_exch<MODE == SOLVE_PEER>(E + (size_t)k * n + tc) : 0.0;
+        for (int k = 0; k < QT; ++k) pht[k] = k < q ? *(E + (size_t)k * n + tc) : 0.0;
+    }
+    if constexpr (MODE == SOLVE_PEER) {  // the shard's own rows are still in registers; the others come from the peers
+        if (!mine || abort_step) {
+#pragma unroll
+            for (int k = 0; k < QT; ++k)
+                pht[k] = (k < q && !abort_step) ? ld_exch<true>(E + (size_t)k * n + tc) : 0.0;
+        }
     }
     for (int idx = tid; idx < QT * QT; idx += 256) {
         const int k1 = idx / QT, k2 = idx % QT;
@@ -1578,52 +1583,134 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
     }
     __syncthreads();
     trace_mark(trace, epoch, 10);  // S built
-    // warp 0: S = L L' in place on a copy (T), then W = L^-1 (into S); every thread then adds up its entries of
-    // S^-1 = W' W. If S is not positive definite: S^-1 by the pivoted sweep -- what `S.inverse()` of ekf.cpp:301 does
-    // through PartialPivLU -- straight into Sinv.
-    if (tid < 32) {
-        for (int idx = tid; idx < QT * LD; idx += 32) T[idx] = S[idx];
-        __syncwarp();
-        const bool ok = warp_cholesky<QT>(T, LD, q, tid, s_invd);
-        const bool all_ok = __all_sync(0xffffffffu, ok);
-        if (tid == 0) s_chol_ok = all_ok ? 1 : 0;
-        if (all_ok) {
-            warp_lower_inverse<QT>(T, LD, q, tid, s_invd, S);
-        } else {
-            for (int idx = tid; idx < QT * QT; idx += 32) Sinv[idx] = 0.0;
-            __syncwarp();
-            warp_gauss_jordan<QT>(S, T, LD, q, tid, s_piv, s_perm, Sinv);
-        }
-    }
-    // ---- column t of H_o P (= row t of P H_o', see above): independent of S^-1, stored while warp 0 factorises
+    // ---- column t of H_o P (= row t of P H_o', see above): independent of S^-1, on its way before the factorisation
     if (valid) {
         double* hpo = hp + (size_t)t * QT;
 #pragma unroll
         for (int k = 0; k < QT; k += 2)
             *reinterpret_cast<double2*>(hpo + k) = abort_step ? make_double2(0.0, 0.0) : make_double2(pht[k], pht[k + 1]);
     }
-    __syncthreads();
-    trace_mark(trace, epoch, 11);  // factorised, H_o P stored
-    if (s_chol_ok) {  // S^-1(a, b) = sum_{k >= max(a, b)} W(k, a) W(k, b); the padding of Sinv stays zero
-        for (int idx = tid; idx < QT * QT; idx += 256) {
-            const int a = idx / QT, b = idx % QT;
-            if (a < q && b < q) {
-                double sum = 0.0;
-                for (int k = a > b ? a : b; k < q; ++k) sum = fma(S[k * LD + a], S[k * LD + b], sum);
-                Sinv[idx] = sum;
+    // ---- S = L L' and W = L^-1 together, by the whole CTA: thread e < q (q + 1) / 2 owns ONE entry (i, j), i >= j, of
+    // the lower triangle -- S(i, j) and the matching entry of X, which starts as the identity and ends as L^-1 (the
+    // elimination of [L | I], as in chol_panel_kernel). Right-looking, a rolled loop over the columns with ONE barrier per
+    // column: the owners of column k publish l_ik, the owners of row k publish the scaled pivot row of X, and after the
+    // barrier every thread applies both rank-1 updates to its own two registers. The next pivot is recomputed by every
+    // thread from the published diagonal (same fma as its owner's update), so nobody waits for it. ~50 instructions
+    // of code and ~200 cycles per column; the one-warp register version this replaces was 3,500 instructions that each
+    // step fetched cold (the kernel runs once per step between two passes of the streaming update) and, rolled into
+    // shared memory, paid ~500 cycles per column.
+    // If a pivot is not positive, S is not positive definite: S^-1 then comes from the pivoted sweep -- what `S.inverse()`
+    // of ekf.cpp:301 does through PartialPivLU -- by warp 0, straight into Sinv.
+    {
+        double* colb = T;                 // [2][QT]   l_ik of the column in flight
+        double* xrb = T + 2 * QT;         // [2][QT]   scaled pivot row of X (zero beyond the pivot)
+        double* dgb = T + 4 * QT;         // [2][QT]   diagonal of the trailing matrix
+        int ei = 0, ej = 0;
+        {   // e -> (i, j), e = i (i + 1) / 2 + j
+            int e = tid;
+            ei = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+            while ((ei + 1) * (ei + 2) / 2 <= e) ++ei;
+            while (ei * (ei + 1) / 2 > e) --ei;
+            ej = e - ei * (ei + 1) / 2;
+        }
+        const bool own = ei < q;          // (j <= i < q)
+        double sv = own ? S[ei * LD + ej] : 0.0;
+        double xv = (own && ei == ej) ? 1.0 : 0.0;
+        for (int idx = tid; idx < 6 * QT; idx += 256) T[idx] = 0.0;
+        __syncthreads();
+        if (own && ei == ej) dgb[ei] = sv;
+        __syncthreads();
+        double akk = dgb[0];
+        bool ok = true;
+#pragma unroll 1
+        for (int k = 0; k < q; ++k) {
+            const int b = k & 1;
+            if (!(akk > 0.0)) {  // every thread sees the same pivot: uniform exit
+                ok = false;
+                break;
+            }
+            const double inv = rsqrt(akk);
+            if (own && ej == k) {  // column k of L
+                sv = ei == k ? akk * inv : sv * inv;
+                colb[b * QT + ei] = sv;
+            }
+            if (own && ei == k) {  // pivot row of X
+                xv *= inv;
+                xrb[b * QT + ej] = xv;
+            }
+            __syncthreads();
+            if (own && ei > k) {
+                const double ci = colb[b * QT + ei];
+                if (ej > k) {
+                    sv = fma(-ci, colb[b * QT + ej], sv);
+                    if (ei == ej) dgb[(b ^ 1) * QT + ei] = sv;
+                }
+                xv = fma(-ci, xrb[b * QT + ej], xv);
+            }
+            if (k + 1 < q) {  // next pivot: the fma its owner has just done, redone here from the published operands
+                const double c1 = colb[b * QT + k + 1];
+                akk = fma(-c1, c1, dgb[b * QT + k + 1]);
             }
         }
-        __syncthreads();
+        if (tid == 0) s_chol_ok = ok ? 1 : 0;
+        if (ok && own) Sinv[ei * QT + ej] = xv;  // W = L^-1 (zero above the diagonal)
+        trace_mark(trace, epoch, 13);
+        if (!ok) {
+            __syncthreads();
+            if (tid < 32) {
+                for (int idx = tid; idx < QT * LD; idx += 32) T[idx] = S[idx];
+                for (int idx = tid; idx < QT * QT; idx += 32) Sinv[idx] = 0.0;
+                __syncwarp();
+                warp_gauss_jordan<QT>(S, T, LD, q, tid, s_piv, s_perm, Sinv);
+            }
+        }
     }
+    __syncthreads();
+    trace_mark(trace, epoch, 11);  // factorised, H_o P stored
     if (valid) {
+        // K row t = (P H_o')(t, :) S^-1, 20 independent accumulators, rows of the factor read as 16-byte broadcasts.
+        //   S = L L', W = L^-1 (in Sinv's storage, zero above the diagonal): S^-1 = W' W, so with u = W p,
+        //   K row = W' u -- one pass over the rows of W: u_k = W(k, :) . p, then acc(:) += u_k W(k, :).
+        //   (not positive definite: Sinv holds the pivoted-sweep inverse and the pass is the plain product)
+        double acc[QT];
+#pragma unroll
+        for (int k = 0; k < QT; ++k) acc[k] = 0.0;
+        if (s_chol_ok) {
+#pragma unroll
+            for (int k = 0; k < QT; ++k) {
+                double w[QT];
+#pragma unroll
+                for (int a = 0; a <= k; a += 2) {
+                    const double2 v = *reinterpret_cast<const double2*>(&Sinv[k * QT + a]);
+                    w[a] = v.x;
+                    w[a + 1] = v.y;  // (a + 1 == k + 1 reads the zero above the diagonal)
+                }
+                double u0 = 0.0, u1 = 0.0;
+#pragma unroll
+                for (int a = 0; a <= k; a += 2) {
+                    u0 = fma(w[a], pht[a], u0);
+                    if (a + 1 <= k) u1 = fma(w[a + 1], pht[a + 1], u1);
+                }
+                const double u = u0 + u1;
+#pragma unroll
+                for (int a = 0; a <= k; ++a) acc[a] = fma(u, w[a], acc[a]);
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < QT; ++e) {
+#pragma unroll
+                for (int k = 0; k < QT; k += 2) {
+                    const double2 v = *reinterpret_cast<const double2*>(&Sinv[e * QT + k]);
+                    acc[k] = fma(pht[e], v.x, acc[k]);
+                    acc[k + 1] = fma(pht[e], v.y, acc[k + 1]);
+                }
+            }
+        }
         double dx = 0.0;
 #pragma unroll
-        for (int k = 0; k < QT; ++k) {  // K row t = (P H_o')(t, :) S^-1
-            double sum = 0.0;
-#pragma unroll
-            for (int e = 0; e < QT; ++e) sum += pht[e] * Sinv[e * QT + k];
-            if (abort_step) sum = 0.0;
-            dx += sum * s_y[k];
+        for (int k = 0; k < QT; ++k) {
+            const double sum = abort_step ? 0.0 : acc[k];
+            dx = fma(sum, s_y[k], dx);
             K[(size_t)k * n + t] = sum;
         }
         X[t] += dx;  // ekf.cpp:309

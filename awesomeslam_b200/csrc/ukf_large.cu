@@ -59,6 +59,8 @@ struct UkfLarge {
     double* rdiag = nullptr;   // [n] diagonal of R
     double* invP = nullptr;    // [nb][64*64]
     double* invS = nullptr;
+    double* inv256 = nullptr;  // [ceil(n/256)][256*256] inverses of the 256-wide diagonal blocks of chol(M), and transposed
+    double* inv256T = nullptr;
     // TF32 variant of the three sigma-point products (gemm_tf32_tcgen05.cu): 0 = FP64 (default), 1 = TF32, 3 = 3xTF32
     int precision = 0;
     float* Dhi = nullptr;      // [n][tf32_padded_k(ns)] hi / lo parts of D and DZ
@@ -388,7 +390,7 @@ aslam_status large_ukf_create(aslam_large* h) {
     };
     const size_t mat = (size_t)n * u->ld * sizeof(double), sig = (size_t)n * u->nsld * sizeof(double);
     A((void**)&u->Z, n * sizeof(double));
-    A((void**)&u->Lb, mat);
+    A((void**)&u->Lb, (size_t)(n + 2) * u->ld * sizeof(double));  // chol(Paug); later W = [Tc; dz_0'; dz'] Lm^-T
     A((void**)&u->S, mat);
     A((void**)&u->Tc, (size_t)(n + 2) * u->ld * sizeof(double));
     A((void**)&u->D, sig);
@@ -405,12 +407,17 @@ aslam_status large_ukf_create(aslam_large* h) {
     A((void**)&u->rdiag, n * sizeof(double));
     A((void**)&u->invP, (size_t)nb * 64 * 64 * sizeof(double));
     A((void**)&u->invS, (size_t)nb * 64 * 64 * sizeof(double));
+    const size_t w256 = (size_t)((n + dense::TRSM_WIDE - 1) / dense::TRSM_WIDE) * dense::TRSM_WIDE * dense::TRSM_WIDE * sizeof(double);
+    A((void**)&u->inv256, w256);
+    A((void**)&u->inv256T, w256);
     A((void**)&u->fail, 2 * sizeof(int));
     A((void**)&u->status, sizeof(uint32_t));
     if (rc != ASLAM_OK) return rc;
     ASLAM_CUDA(cudaEventCreate(&u->evg0));
     ASLAM_CUDA(cudaEventCreate(&u->evg1));
     ASLAM_CUDA(cudaMemsetAsync(u->Z, 0, n * sizeof(double), h->stream));
+    ASLAM_CUDA(cudaMemsetAsync(u->inv256, 0, w256, h->stream));   // the blocks above the block diagonal stay zero
+    ASLAM_CUDA(cudaMemsetAsync(u->inv256T, 0, w256, h->stream));
     ASLAM_CUDA(cudaMemsetAsync(u->status, 0, sizeof(uint32_t), h->stream));
     ASLAM_CUDA(cudaMemsetAsync(u->fail, 0xff, 2 * sizeof(int), h->stream));
     fill_diag_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(n, u->qdiag, u->rdiag, (double)h->cfg.ukf_kq,
@@ -424,7 +431,7 @@ void large_ukf_destroy(aslam_large* h) {
     UkfLarge* u = static_cast<UkfLarge*>(h->ukf);
     if (!u) return;
     void* ptrs[] = {u->Z, u->Lb, u->S, u->Tc, u->D, u->DZ, u->pose, u->mean, u->zpred, u->d0, u->dz0, u->dzv, u->gvec, u->coef,
-                    u->qdiag, u->rdiag, u->invP, u->invS, u->fail, u->status, u->Dhi, u->Dlo, u->Zhi, u->Zlo, u->tf32_err};
+                    u->qdiag, u->rdiag, u->invP, u->invS, u->inv256, u->inv256T, u->fail, u->status, u->Dhi, u->Dlo, u->Zhi, u->Zlo, u->tf32_err};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (u->evg0) cudaEventDestroy(u->evg0);
@@ -597,11 +604,17 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     double* brow = arow + u->ld;
     ASLAM_CUDA(cudaMemcpyAsync(arow, u->dz0, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     ASLAM_CUDA(cudaMemcpyAsync(brow, u->dzv, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
-    rc = dense::trsm_right_lower_t(st, u->Tc, u->ld, n + 2, u->S, u->ld, n, u->invS, &nl);
+    // 256-wide out-of-place solve: W lands in the storage of chol(Paug) (dead since the sigma points), the scaled
+    // panels L[>j, j] inv256_j in the storage of D (dead since the three products)
+    double* W = u->Lb;
+    rc = dense::trsm_right_lower_t_wide(st, u->Tc, u->ld, n + 2, u->S, u->ld, n, u->invS, u->inv256, u->inv256T, u->D,
+                                        u->ld, W, u->ld, &nl);
     if (rc != ASLAM_OK) return rc;
     mark("trsm");
+    arow = W + (size_t)n * u->ld;
+    brow = arow + u->ld;
     sm_scalars_kernel<<<1, 256, 0, st>>>(n, arow, brow, u->w0 - u->wc, u->coef, u->status);
-    state_update_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, u->ld, u->Tc, arow, brow, u->coef, u->mean, u->gvec, h->X,
+    state_update_kernel<<<(n + 7) / 8, 256, 0, st>>>(n, u->ld, W, arow, brow, u->coef, u->mean, u->gvec, h->X,
                                                    u->status);
     ASLAM_CUDA(cudaGetLastError());
     nl += 2;
@@ -612,7 +625,7 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     d.beta = 1.0;
     d.lower_only = true;
     d.u = u->gvec; d.v = u->gvec; d.r1_dev = u->coef;
-    rc = dense::dgemm_nt(st, n, n, n, u->Tc, u->ld, u->Tc, u->ld, h->P, u->ld, d, &nl);
+    rc = dense::dgemm_nt(st, n, n, n, W, u->ld, W, u->ld, h->P, u->ld, d, &nl);
     if (rc != ASLAM_OK) return rc;
     rc = dense::symmetrize_from_lower(st, h->P, u->ld, n, &nl);
     if (rc != ASLAM_OK) return rc;

@@ -430,7 +430,7 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
             exchange = ("fused: peer stores over NVLink + arrival counters inside the solve kernel "
                         "(no collective call, 3 launches per step)")
             parity = large_parity(f, step_nccl, step_fused, torch, dist, rank, world, dev, rb, re, X0, G, d,
-                                  rng, brg, ODOM)
+                                  rng, brg, ODOM, stream)
         except AssertionError:
             raise
         except Exception as e:  # noqa: BLE001  (reported, and the NCCL numbers stand)
@@ -460,7 +460,8 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
     }
 
 
-def large_parity(f, step_nccl, step_fused, torch, dist, rank, world, dev, rb, re, X0, G, d, rng, brg, ODOM, steps=3):
+def large_parity(f, step_nccl, step_fused, torch, dist, rank, world, dev, rb, re, X0, G, d, rng, brg, ODOM, stream,
+                 steps=3):
     """Driver-visible parity of the multi-process exchange (bit-identical by design, asserted here on hardware):
     from the same loaded state, `steps` steps through the NCCL all-reduce form and through the fused peer-store form
     must leave EQUAL X and EQUAL local rows of P on every rank; and rank 0 runs the same steps on an UNSHARDED handle
@@ -474,9 +475,11 @@ def large_parity(f, step_nccl, step_fused, torch, dist, rank, world, dev, rb, re
         f.load_state_colmajor(X0, P0)
         if world > 1:
             dist.barrier()
-        for _ in range(steps):
-            step()
+        with torch.cuda.stream(stream):  # the all-reduce of the NCCL form must be ordered on the handle's stream
+            for _ in range(steps):
+                step()
         f.sync()
+        torch.cuda.synchronize(dev)
         res[name] = f.get_state()
         if world > 1:
             dist.barrier()
