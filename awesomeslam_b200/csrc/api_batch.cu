@@ -27,6 +27,10 @@ uint32_t batched_padded_dim(int32_t max_state_dim, int kind) {
     const int nmax = max_state_dim - 1;
     if (nmax < 3) return 0;
     if (kind == ASLAM_KIND_UKF) {
+        // the kernel's shared-memory footprint (and with it the number of resident filters per SM, which is what sets its
+        // throughput) follows the cap the handle asks for: 20 (<= 8 landmarks: 7 per SM), 24, 30, 36
+        if (nmax <= 19) return 20;
+        if (nmax <= 23) return 24;
         if (nmax <= 29) return 30;  // the reference's cap (config.h:45)
         if (nmax <= 35) return 36;  // the cfg3 shape: 16 landmarks, N = 35, 75 sigma points
         return 0;                   // larger UKF maps: aslam_large_ukf_*

@@ -30,6 +30,9 @@ struct Epilogue {
     // a_cols = number of valid columns of A (the tensor map zero-fills beyond it).
     int kblock = 0;
     int a_cols = 0;
+    // > 0: persistent form on at most max_ctas CTAs (one per SM), each walking a list of 128 x 128 tiles. Leaves the
+    // other SMs to whatever runs on other streams (the large-map UKF factors M while the P and Tc products run).
+    int max_ctas = 0;
 };
 
 // C (M x N, ldc) = alpha * A (M x K, lda) * B (N x K, ldb)' + ...   Base pointers 16-byte aligned, ld even.
@@ -70,7 +73,7 @@ aslam_status symmetrize_from_lower(cudaStream_t st, double* A, size_t ld, int n,
 
 // A side stream with a fork and a join event, owned by the calling thread, one per (slot, device): small kernels that
 // are independent of the caller's stream for a while (the Cholesky's lookahead panel, a GEMM's ragged-edge rows) run on
-// it. Created on first use for the CURRENT device. Slots: 0 the Cholesky, 1 dgemm_nt.
+// it. Created on first use for the CURRENT device. Slots: 0 the Cholesky, 1 dgemm_nt, 2 the large-map UKF (chol(M) beside the products).
 struct SideStream {
     cudaStream_t s = nullptr;
     cudaEvent_t fork = nullptr, join = nullptr;

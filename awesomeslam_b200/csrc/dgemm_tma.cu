@@ -37,6 +37,9 @@ struct GemmParams {
     const double* r1_dev;
     int lower_only;
     int kblock;  // > 0: block-diagonal second operand (Epilogue::kblock)
+    // persistent form (Epilogue::max_ctas): the grid is 1-D, CTA b walks tiles b, b + gridDim.x, ... of the list
+    // (row-major over the tile grid; lower_only: the tiles on or below the block diagonal, row by row)
+    int persist, tiles, tcols;
 };
 
 __device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* map, int c_inner, int c_outer,
@@ -79,11 +82,9 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + NST * G::STAGE);
     uint64_t* empty = full + NST;
-    const int bm = blockIdx.y, bn = blockIdx.x;
-    const int row0 = bm * BM, col0 = bn * BN;
-    if (p.lower_only && row0 + BM - 1 < col0) return;  // tile entirely above the diagonal
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KT = (p.K + BK - 1) / BK;
+    if (!p.persist && p.lower_only && (int)blockIdx.y * BM + BM - 1 < (int)blockIdx.x * BN) return;  // above the diagonal
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NST; ++s) {
@@ -94,16 +95,41 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     __syncthreads();
 
+    // tile list of this CTA: one tile (bm, bn) = blockIdx in the plain form; tiles first, first + step, ... in the
+    // persistent one. The slab counter `it` runs on across tiles, so the mbarrier ring never restarts.
+    const int first = p.persist ? (int)blockIdx.x : 0, step = p.persist ? (int)gridDim.x : 1;
+    const int ntiles = p.persist ? p.tiles : 1;
+    auto tile_of = [&](int id, int& bm, int& bn) {
+        if (!p.persist) {
+            bm = blockIdx.y;
+            bn = blockIdx.x;
+        } else if (p.lower_only) {  // (BM == BN) id = bm (bm + 1) / 2 + bn, bn <= bm
+            bm = (int)((sqrtf(8.0f * (float)id + 1.0f) - 1.0f) * 0.5f);
+            while ((bm + 1) * (bm + 2) / 2 <= id) ++bm;
+            while (bm * (bm + 1) / 2 > id) --bm;
+            bn = id - bm * (bm + 1) / 2;
+        } else {
+            bm = id / p.tcols;
+            bn = id % p.tcols;
+        }
+    };
+
     if (warp == G::NW) {  // ---------------- producer
         if (lane == 0) {
-            const int ka0 = p.kblock ? (col0 / p.kblock) * p.kblock : 0;  // block-diagonal operand: A's column window
-            for (int kt = 0; kt < KT; ++kt) {
-                const int st = kt % NST;
-                if (kt >= NST) bulk::mbar_wait(&empty[st], ((kt / NST) - 1) & 1);
-                bulk::mbar_expect_tx(&full[st], (uint32_t)G::STAGE);
-                unsigned char* sa = smem + st * G::STAGE;
-                tma_load_2d(sa, &tmA, ka0 + kt * BK, row0, &full[st]);
-                tma_load_2d(sa + G::A_BYTES, &tmB, kt * BK, col0, &full[st]);
+            int it = 0;
+            for (int id = first; id < ntiles; id += step) {
+                int bm, bn;
+                tile_of(id, bm, bn);
+                const int row0 = bm * BM, col0 = bn * BN;
+                const int ka0 = p.kblock ? (col0 / p.kblock) * p.kblock : 0;  // block-diagonal operand: A's column window
+                for (int kt = 0; kt < KT; ++kt, ++it) {
+                    const int st = it % NST;
+                    if (it >= NST) bulk::mbar_wait(&empty[st], ((it / NST) - 1) & 1);
+                    bulk::mbar_expect_tx(&full[st], (uint32_t)G::STAGE);
+                    unsigned char* sa = smem + st * G::STAGE;
+                    tma_load_2d(sa, &tmA, ka0 + kt * BK, row0, &full[st]);
+                    tma_load_2d(sa + G::A_BYTES, &tmB, kt * BK, col0, &full[st]);
+                }
             }
         }
         return;
@@ -112,20 +138,25 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ---------------- consumers
     const int wm = (warp / WARPS_N) * G::WM, wn = (warp % WARPS_N) * G::WN;
     const int g = lane >> 2, t = lane & 3;
+    int it = 0;
+    for (int id = first; id < ntiles; id += step) {
+    int bm, bn;
+    tile_of(id, bm, bn);
+    const int row0 = bm * BM, col0 = bn * BN;
     double acc[G::MI][G::NI][2];
 #pragma unroll
     for (int mi = 0; mi < G::MI; ++mi)
 #pragma unroll
         for (int ni = 0; ni < G::NI; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
-    for (int kt = 0; kt < KT; ++kt) {
-        const int st = kt % NST;
-        bulk::mbar_wait(&full[st], (kt / NST) & 1);
-        // Release the PREVIOUS stage here, behind the spin loop: every mma of slab kt-1 was issued before the loop, and an
-        // mma cannot issue until the shared loads feeding it have returned, so the stage is no longer being read.
-        // (Arriving at the end of the slab's own iteration is wrong: ptxas hoists the arrive above the DMMAs -- there is
-        // no register dependence -- and the TMA refill then races the loads still in flight.)
-        if (kt > 0 && lane == 0) mbar_arrive(&empty[(kt - 1) % NST]);
+    for (int kt = 0; kt < KT; ++kt, ++it) {
+        const int st = it % NST;
+        bulk::mbar_wait(&full[st], (it / NST) & 1);
+        // Release the PREVIOUS stage here, behind the spin loop: every mma of the previous slab was issued before the
+        // loop, and an mma cannot issue until the shared loads feeding it have returned, so the stage is no longer
+        // being read. (Arriving at the end of the slab's own iteration is wrong: ptxas hoists the arrive above the DMMAs
+        // -- there is no register dependence -- and the TMA refill then races the loads still in flight.)
+        if (it > 0 && lane == 0) mbar_arrive(&empty[(it - 1) % NST]);
         const double* As = reinterpret_cast<const double*>(smem + st * G::STAGE);
         const double* Bs = reinterpret_cast<const double*>(smem + st * G::STAGE + G::A_BYTES);
 #pragma unroll
@@ -185,6 +216,7 @@ dgemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 crow[c] = o0;
         }
     }
+    }  // tiles
 }
 
 // ---------------------------------------------------------------------------------- tensor maps
@@ -236,6 +268,7 @@ aslam_status launch(cudaStream_t st, const double* A, size_t lda, const double* 
     if (!make_map(&ta, A, p.M, a_cols ? a_cols : p.K, lda, BM) || !make_map(&tb, B, p.N, p.K, ldb, BN))
         return ASLAM_ERR_CUDA;
     dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
+    if (p.persist) grid = dim3((unsigned)p.persist);
     dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N><<<grid, G::THREADS, G::SMEM, st>>>(ta, tb, p);
     ASLAM_CUDA(cudaGetLastError());
     return ASLAM_OK;
@@ -301,7 +334,7 @@ __global__ void __launch_bounds__(256) dgemm_skinny_kernel(GemmParams p, const d
 }  // namespace
 
 aslam_status side_stream(int slot, SideStream** out) {
-    constexpr int MAXDEV = 64, SLOTS = 2;
+    constexpr int MAXDEV = 64, SLOTS = 3;
     static thread_local SideStream ctx[SLOTS][MAXDEV];
     int dev = 0;
     ASLAM_CUDA(cudaGetDevice(&dev));
@@ -329,6 +362,9 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     p.alpha = e.alpha; p.beta = e.beta; p.r1 = e.r1; p.u = e.u; p.v = e.v; p.diag = e.diag; p.r1_dev = e.r1_dev;
     p.lower_only = e.lower_only ? 1 : 0;
     p.kblock = e.kblock;
+    p.persist = 0;
+    p.tiles = 0;
+    p.tcols = 0;
     if (e.kblock && (K != e.kblock || e.kblock % 128 != 0 || e.a_cols <= 0)) {
         set_error("dgemm_nt: block-diagonal operand needs K == kblock (a multiple of 128) and a_cols");
         return ASLAM_ERR_ARG;
@@ -364,8 +400,15 @@ aslam_status dgemm_nt(cudaStream_t st, int M, int N, int K, const double* A, siz
     const long sms = 148;
     const double cost128 = 2.0 * (double)((t128 + sms - 1) / sms), cost64 = 1.08 * (double)((t64 + sms - 1) / sms);
     const int ac = e.kblock ? e.a_cols : 0;
-    const aslam_status rc = (Nm > 64 && cost128 <= cost64) ? launch<128, 128, 4, 2>(st, A, lda, B, ldb, p, ac)
-                                                           : launch<128, 64, 4, 2>(st, A, lda, B, ldb, p, ac);
+    const bool use128 = (Nm > 64 && cost128 <= cost64) || e.max_ctas > 0;
+    if (e.max_ctas > 0 && !(e.lower_only && tc128 < tr)) {  // persistent: 128 x 128 tiles, row-major (lower_only: on or below the block diagonal)
+        p.tcols = (int)tc128;
+        p.tiles = (int)t128;
+        p.persist = (int)std::min<long>(e.max_ctas, t128);
+    }
+    const aslam_status rc = use128 ? launch<128, 128, 4, 2>(st, A, lda, B, ldb, p, ac)
+                                   : launch<128, 64, 4, 2>(st, A, lda, B, ldb, p, ac);
+    p.persist = 0;
     if (rc != ASLAM_OK) return rc;
     // the tile kernel goes to the GPU first (one CTA per SM); the ragged-edge CTAs then fit beside it
     p.M = M;

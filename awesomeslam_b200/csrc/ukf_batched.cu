@@ -30,6 +30,10 @@ namespace {
 
 constexpr int UTHREADS = 128;
 
+// e / d for 0 <= e < 2^15 and 1 <= d <= 80 without the integer-division sequence (~20 instructions): the float
+// quotient of two small integers is within 1 ulp of the true one, so truncating (e + 0.5) / d is exact.
+__device__ __forceinline__ int fdiv_small(int e, float rcp_d) { return (int)(((float)e + 0.5f) * rcp_d); }
+
 template <int UNP>
 struct __align__(16) UkfSlot {
     static constexpr int UNA = UNP + 2;      // augmented
@@ -148,8 +152,9 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         // weights(0) = lambda / (lambda + N + 2) and the common weight 0.5 / (..), both rounded to float (ukf.h:75-80)
         const double w0 = (double)__fdiv_rn(lambda, denom), wc = (double)(float)(0.5 / (double)denom);
         // ---- Paug (ukf.cpp:262-277) into L
+        const float rNA = 1.0f / (float)NA;
         for (int k = tid; k < NA * NA; k += UTHREADS) {
-            const int i = k / NA, j = k % NA;
+            const int i = fdiv_small(k, rNA), j = k - i * NA;
             double v = 0.0;
             if (i < N && j < N) v = s.P[i][j];
             else if (i == j) v = (double)(i == N ? __fmul_rn(kp.std_a, kp.std_a) : __fmul_rn(kp.std_yaw, kp.std_yaw));
@@ -163,12 +168,36 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         // patched in with the upper triangle below.
         for (int k = 0; k < NA; ++k) {
             if (s.fail_k >= 0) break;
-            double x = s.L[k][k];
-            {
-                double sum = 0.0;
-                for (int j = 0; j < k; ++j) sum += s.L[k][j] * s.L[k][j];
-                if (k > 0) x -= sum;
+            // The pivot sum (row k against itself) and this thread's row sum (row i against row k) are independent
+            // sequential sums over the same row k: they run in ONE loop, sharing the loads of row k, products formed
+            // eight at a time before the dependent adds (the shared-memory latency otherwise sits inside every term
+            // of the chain). Same operations in the same order per sum as Eigen's unblocked LLT.
+            const int i = k + 1 + tid;  // (NA - k - 1 <= 36 < UTHREADS rows below the pivot: at most one per thread)
+            const bool row = i < NA;
+            const double* lk = s.L[k];
+            const double* li = s.L[row ? i : k];
+            double sumx = 0.0, sumi = 0.0;
+            int j = 0;
+            for (; j + 8 <= k; j += 8) {
+                double a[8], b[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    a[u] = lk[j + u];
+                    b[u] = li[j + u];
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    sumx += a[u] * a[u];
+                    sumi += b[u] * a[u];
+                }
             }
+            for (; j < k; ++j) {
+                const double a = lk[j];
+                sumx += a * a;
+                sumi += li[j] * a;
+            }
+            double x = s.L[k][k];
+            if (k > 0) x -= sumx;
             if (x <= 0.0) {  // every thread computes the same x: uniform decision
                 __syncthreads();
                 if (tid == 0) s.fail_k = k;
@@ -176,18 +205,14 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
                 break;
             }
             x = sqrt(x);
-            for (int i = k + 1 + tid; i < NA; i += UTHREADS) {
-                double sum = 0.0;
-                for (int j = 0; j < k; ++j) sum += s.L[i][j] * s.L[k][j];
-                s.L[i][k] = (s.L[i][k] - sum) / x;
-            }
+            if (row) s.L[i][k] = (s.L[i][k] - sumi) / x;
             if (tid == 0) s.Ld[k] = x;
             __syncthreads();
         }
         {
             const int done = s.fail_k >= 0 ? s.fail_k : NA;  // columns that were factorised
             for (int k = tid; k < NA * NA; k += UTHREADS) {
-                const int i = k / NA, j = k % NA;
+                const int i = fdiv_small(k, rNA), j = k - i * NA;
                 if (j > i) s.L[i][j] = 0.0;
                 else if (i == j && i < done) s.L[i][i] = s.Ld[i];
             }
@@ -220,14 +245,16 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         __syncthreads();
         // ---- predicted mean (ukf.cpp:300-304) and Zsig (ukf.cpp:322-326)
         for (int k = tid; k < N; k += UTHREADS) {
-            double acc = 0.0;
-            for (int i = 0; i < NS; ++i) acc += (i == 0 ? w0 : wc) * s.XS[k][i];
+            double acc = 0.0 + w0 * s.XS[k][0];
+#pragma unroll 8
+            for (int i = 1; i < NS; ++i) acc += wc * s.XS[k][i];
             s.X[k] = acc;
         }
         {
             const int nl = (N - 3) / 2;
+            const float rNSz = 1.0f / (float)NS;
             for (int e = tid; e < NS * (nl + 1); e += UTHREADS) {
-                const int c = e % NS, l = e / NS;
+                const int l = fdiv_small(e, rNSz), c = e - l * NS;
                 if (l == nl) {
                     s.ZS[0][c] = s.XS[0][c];
                     s.ZS[1][c] = s.XS[1][c];
@@ -243,13 +270,15 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         __syncthreads();
         // ---- Zpred (ukf.cpp:329-339); Xdiff in place (ukf.cpp:312-313)
         for (int k = tid; k < N; k += UTHREADS) {
-            double acc = 0.0;
-            for (int i = 0; i < NS; ++i) acc += (i == 0 ? w0 : wc) * s.ZS[k][i];
+            double acc = 0.0 + w0 * s.ZS[k][0];
+#pragma unroll 8
+            for (int i = 1; i < NS; ++i) acc += wc * s.ZS[k][i];
             if (k >= 2 && (k & 1) == 0) acc = (double)normalize_angle((float)acc, pi);
             s.Zp[k] = acc;
         }
+        const float rNS = 1.0f / (float)NS;
         for (int e = tid; e < N * NS; e += UTHREADS) {
-            const int k = e / NS, c = e % NS;
+            const int k = fdiv_small(e, rNS), c = e - k * NS;
             double d = s.XS[k][c] - s.X[k];
             if (k == 2) d = (double)normalize_angle((float)d, pi);
             s.XS[k][c] = d;
@@ -257,27 +286,66 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         __syncthreads();
         // ---- Zdiff in place (ukf.cpp:347-351)
         for (int e = tid; e < N * NS; e += UTHREADS) {
-            const int k = e / NS, c = e % NS;
+            const int k = fdiv_small(e, rNS), c = e - k * NS;
             double d = s.ZS[k][c] - s.Zp[k];
             if (k >= 2 && (k & 1) == 0) d = (double)normalize_angle((float)d, pi);
             s.ZS[k][c] = d;
         }
         __syncthreads();
-        // ---- P (ukf.cpp:307-319), S (ukf.cpp:342-357), Tc (ukf.cpp:360-375): one thread per entry
-        for (int e = tid; e < 3 * N * N; e += UTHREADS) {
-            const int which = e / (N * N), r = e % (N * N), a = r / N, b = r % N;
-            const double* da = which == 1 ? s.ZS[a] : s.XS[a];
-            const double* db = which == 0 ? s.XS[b] : s.ZS[b];
-            double acc = 0.0 + (w0 * da[0]) * db[0];
-            for (int i = 1; i < NS; ++i) acc = acc + (wc * da[i]) * db[i];
-            if (which == 0) s.P[a][b] = acc + ((a == b && a < 3) ? kp.kq : 0.0);
-            else if (which == 1) {
-                const double v = acc + (a == b ? kp.kr : 0.0);
-                s.S[a][b] = v;
-            } else s.Tc[a][b] = acc;
+        // ---- P (ukf.cpp:307-319), S (ukf.cpp:342-357), Tc (ukf.cpp:360-375): one thread per entry, FOUR entries in flight
+        // per thread -- each entry is still one sequential sum over the sigma points in the reference's order (the
+        // chains are independent, so interleaving them changes no rounding), but the 8-cycle dependent add of one
+        // chain now hides behind the other three.
+        {
+            const float rNN = 1.0f / (float)(N * N), rN = 1.0f / (float)N;
+            auto entry = [&](int e, int& which, int& a, int& b, const double*& pa, const double*& pb) {
+                which = fdiv_small(e, rNN);
+                const int r = e - which * N * N;
+                a = fdiv_small(r, rN);
+                b = r - a * N;
+                pa = which == 1 ? s.ZS[a] : s.XS[a];
+                pb = which == 0 ? s.XS[b] : s.ZS[b];
+            };
+            auto put = [&](int which, int a, int b, double acc) {
+                if (which == 0) s.P[a][b] = acc + ((a == b && a < 3) ? kp.kq : 0.0);
+                else if (which == 1) s.S[a][b] = acc + (a == b ? kp.kr : 0.0);
+                else s.Tc[a][b] = acc;
+            };
+            const int total = 3 * N * N;
+            int e0 = tid;
+            for (; e0 + 3 * UTHREADS < total; e0 += 4 * UTHREADS) {
+                const double* da[4];
+                const double* db[4];
+                double acc[4];
+                int wh[4], ea[4], eb[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    entry(e0 + q * UTHREADS, wh[q], ea[q], eb[q], da[q], db[q]);
+                    acc[q] = 0.0 + (w0 * da[q][0]) * db[q][0];
+                }
+                for (int i = 1; i < NS; ++i) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[q] = acc[q] + (wc * da[q][i]) * db[q][i];
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) put(wh[q], ea[q], eb[q], acc[q]);
+            }
+            for (; e0 < total; e0 += UTHREADS) {
+                const double *da, *db;
+                int which, a, b;
+                entry(e0, which, a, b, da, db);
+                double acc = 0.0 + (w0 * da[0]) * db[0];
+#pragma unroll 4
+                for (int i = 1; i < NS; ++i) acc = acc + (wc * da[i]) * db[i];
+                put(which, a, b, acc);
+            }
         }
         __syncthreads();  // last read of the sigma-point matrices: LU / Si / K take over their storage
-        for (int e = tid; e < N * N; e += UTHREADS) s.LU[e / N][e % N] = s.S[e / N][e % N];
+        const float rNl = 1.0f / (float)N;
+        for (int e = tid; e < N * N; e += UTHREADS) {
+            const int i = fdiv_small(e, rNl), j = e - i * N;
+            s.LU[i][j] = s.S[i][j];
+        }
         __syncthreads();
         // ---- S.inverse(): PartialPivLU (unblocked, first largest pivot). Per pivot: warp 0 finds the pivot row with a
         // shuffle reduction (largest |a(i,k)|, i >= k, ties to the lowest row: Eigen's first maximum); the row swap
@@ -322,8 +390,10 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
                 __syncthreads();
             }
             const int m = N - k - 1;
+            const float rm = 1.0f / (float)(m > 0 ? m : 1);
             for (int e = tid; e < m * m; e += UTHREADS) {
-                const int i = k + 1 + e / m, j = k + 1 + e % m;
+                const int q = fdiv_small(e, rm);
+                const int i = k + 1 + q, j = k + 1 + (e - q * m);
                 s.LU[i][j] -= s.LU[i][k] * s.LU[k][j];
             }
             __syncthreads();
@@ -331,7 +401,10 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         double* F = &s.LU[0][0];  // the LU factors
         double* I = &s.Si[0][0];  // S^-1 is built here
         // ... then solve against the permuted identity, one column per thread
-        for (int e = tid; e < N * N; e += UTHREADS) I[(e / N) * UNP + e % N] = (e / N == e % N) ? 1.0 : 0.0;
+        for (int e = tid; e < N * N; e += UTHREADS) {
+            const int i = fdiv_small(e, rNl), j = e - i * N;
+            I[i * UNP + j] = (i == j) ? 1.0 : 0.0;
+        }
         __syncthreads();
         for (int j = tid; j < N; j += UTHREADS) {
             for (int k = 0; k < N; ++k) {
@@ -355,13 +428,34 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
             }
         }
         __syncthreads();
-        // ---- K = Tc S^-1 (ukf.cpp:378); residual (ukf.cpp:381-386)
-        for (int e = tid; e < N * N; e += UTHREADS) {
-            const int i = e / N, j = e % N;
-            double acc = 0.0;
-            for (int k = 0; k < N; ++k) acc += s.Tc[i][k] * I[k * UNP + j];
-            s.K[i][j] = acc;
-        }
+        // ---- K = Tc S^-1 (ukf.cpp:378); residual (ukf.cpp:381-386). The three N x N products below keep one
+        // sequential k-ascending sum per entry; a thread runs its (up to three) entries side by side.
+        const float rN1 = 1.0f / (float)N;
+        auto product3 = [&](auto&& lhs, auto&& rhs, auto&& store) {
+            for (int e0 = tid; e0 < N * N; e0 += 3 * UTHREADS) {
+                int ii[3], jj[3];
+                bool in[3];
+                double acc[3];
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    const int e = e0 + q * UTHREADS;
+                    in[q] = e < N * N;
+                    const int ee = in[q] ? e : tid;
+                    ii[q] = fdiv_small(ee, rN1);
+                    jj[q] = ee - ii[q] * N;
+                    acc[q] = 0.0;
+                }
+                for (int k = 0; k < N; ++k) {
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) acc[q] += lhs(ii[q], k) * rhs(k, jj[q]);
+                }
+#pragma unroll
+                for (int q = 0; q < 3; ++q)
+                    if (in[q]) store(ii[q], jj[q], acc[q]);
+            }
+        };
+        product3([&](int i, int k) { return s.Tc[i][k]; }, [&](int k, int j) { return I[k * UNP + j]; },
+                 [&](int i, int j, double v) { s.K[i][j] = v; });
         for (int k = tid; k < N; k += UTHREADS) {
             double d = s.Z[k] - s.Zp[k];
             if (k >= 2 && (k & 1) == 0) d = (double)normalize_angle((float)d, pi);
@@ -375,20 +469,12 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
             s.X[i] = s.X[i] + acc;
         }
         double* KS = &s.L[0][0];  // N x N, pitch UNP
-        for (int e = tid; e < N * N; e += UTHREADS) {
-            const int i = e / N, j = e % N;
-            double acc = 0.0;
-            for (int k = 0; k < N; ++k) acc += s.K[i][k] * s.S[k][j];
-            KS[i * UNP + j] = acc;
-        }
+        product3([&](int i, int k) { return s.K[i][k]; }, [&](int k, int j) { return s.S[k][j]; },
+                 [&](int i, int j, double v) { KS[i * UNP + j] = v; });
         __syncthreads();
         // ---- P -= (K S) K' (ukf.cpp:391)
-        for (int e = tid; e < N * N; e += UTHREADS) {
-            const int i = e / N, j = e % N;
-            double acc = 0.0;
-            for (int k = 0; k < N; ++k) acc += KS[i * UNP + k] * s.K[j][k];
-            s.P[i][j] = s.P[i][j] - acc;
-        }
+        product3([&](int i, int k) { return KS[i * UNP + k]; }, [&](int k, int j) { return s.K[j][k]; },
+                 [&](int i, int j, double v) { s.P[i][j] = s.P[i][j] - v; });
         if (tid == 0 && s.fail_k >= 0) s.fr.status |= ASLAM_ST_LLT_FAILED;
         __syncthreads();
     }
@@ -447,6 +533,8 @@ aslam_status launch_ukf_batched(const aslam_config& cfg, const BatchState& st, c
     kp.std_a = cfg.ukf_std_a;
     kp.std_yaw = cfg.ukf_std_yaw;
     switch (st.ld) {
+        case 20: return launch_ukf_t<20>(kp, stream);
+        case 24: return launch_ukf_t<24>(kp, stream);
         case 30: return launch_ukf_t<30>(kp, stream);
         case 36: return launch_ukf_t<36>(kp, stream);
         default:

@@ -581,14 +581,43 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
         if (tf) return dense::tf32_gemm_nt(st, n, n, u->ns, Ahi, Alo, Bhi, Blo, C, u->ld, e, tf, u->tf32_err, &nl);
         return dense::dgemm_nt(st, n, n, u->ns, A, u->nsld, B, u->nsld, C, u->ld, e, &nl);
     };
+    // M = wc DZ DZ' + R first: the positive definite part of S (its rank-1 term c dz_0 dz_0' is applied analytically
+    // below). Its factorisation is a latency chain (one-CTA panels, narrow products: 1.6 ms on an otherwise idle GPU),
+    // the P and Tc products are throughput work (1.7 ms) that does not depend on it: in the FP64 mode they run as
+    // PERSISTENT grids on all SMs but `chol_sms`, and the factorisation runs beside them on a side stream with the SMs
+    // that are left (a product CTA needs 131 KB of shared memory, so nothing else fits on an SM that holds one).
+    dense::Epilogue em = e;
+    em.u = nullptr; em.v = nullptr; em.r1 = 0.0; em.diag = u->rdiag;
+    {
+        dense::Epilogue keep = e;
+        e = em;
+        rc = gemm(u->DZ, u->Zhi, u->Zlo, u->DZ, u->Zhi, u->Zlo, u->S);
+        e = keep;
+    }
+    if (rc != ASLAM_OK) return rc;
+    mark("M gemm");
+    static cudaEvent_t dbg0 = nullptr, dbg1 = nullptr;  // ASLAM_UKF_PHASES: the factorisation on the side stream
+    static const int chol_sms = std::getenv("ASLAM_UKF_CHOL_SMS") ? std::atoi(std::getenv("ASLAM_UKF_CHOL_SMS")) : 16;
+    dense::SideStream* cs = nullptr;
+    const bool beside = tf == 0 && chol_sms > 0 && n >= 1024;
+    if (beside) {
+        rc = dense::side_stream(2, &cs);
+        if (rc != ASLAM_OK) return rc;
+        ASLAM_CUDA(cudaEventRecord(cs->fork, st));
+        ASLAM_CUDA(cudaStreamWaitEvent(cs->s, cs->fork, 0));
+        if (phases && !dbg0) { cudaEventCreate(&dbg0); cudaEventCreate(&dbg1); }
+        if (phases) cudaEventRecord(dbg0, cs->s);
+        rc = dense::cholesky_lower(cs->s, u->S, u->ld, n, u->invS, u->fail + 1, &nl);
+        if (rc != ASLAM_OK) return rc;
+        if (phases) cudaEventRecord(dbg1, cs->s);
+        ASLAM_CUDA(cudaEventRecord(cs->join, cs->s));
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+        e.max_ctas = sms - chol_sms;
+    }
     rc = gemm(u->D, u->Dhi, u->Dlo, u->D, u->Dhi, u->Dlo, h->P);
     if (rc != ASLAM_OK) return rc;
     mark("P gemm");
-    // M = wc DZ DZ' + R: the positive definite part of S (its rank-1 term c dz_0 dz_0' is applied analytically below)
-    e.u = nullptr; e.v = nullptr; e.r1 = 0.0; e.diag = u->rdiag;
-    rc = gemm(u->DZ, u->Zhi, u->Zlo, u->DZ, u->Zhi, u->Zlo, u->S);
-    if (rc != ASLAM_OK) return rc;
-    mark("M gemm");
     e.lower_only = false;
     e.r1 = u->w0 - u->wc;
     e.u = u->d0; e.v = u->dz0; e.diag = nullptr;
@@ -597,8 +626,12 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     if (h->timed && u->evg1) ASLAM_CUDA(cudaEventRecord(u->evg1, st));
     mark("Tc gemm");
     // ---- M = Lm Lm';  [W; a'; b'] = [Tc; dz_0'; dz'] Lm^-T  (a = Lm^-1 dz_0, b = Lm^-1 dz ride along as two extra rows)
-    rc = dense::cholesky_lower(st, u->S, u->ld, n, u->invS, u->fail + 1, &nl);
-    if (rc != ASLAM_OK) return rc;
+    if (beside) {
+        ASLAM_CUDA(cudaStreamWaitEvent(st, cs->join, 0));
+    } else {
+        rc = dense::cholesky_lower(st, u->S, u->ld, n, u->invS, u->fail + 1, &nl);
+        if (rc != ASLAM_OK) return rc;
+    }
     mark("chol(M)");
     double* arow = u->Tc + (size_t)n * u->ld;
     double* brow = arow + u->ld;
@@ -636,6 +669,12 @@ aslam_status large_ukf_step(aslam_large* h, double x, double y, float yaw, doubl
     mark("W W' + symmetrize");
     if (nph > 1) {
         cudaEventSynchronize(pev[nph - 1]);
+        if (beside && dbg0) {
+            float a = 0, b = 0;
+            cudaEventElapsedTime(&a, pev[0], dbg0);
+            cudaEventElapsedTime(&b, dbg0, dbg1);
+            std::fprintf(stderr, "ukf chol(M) beside the products: starts %.3f ms into the step, takes %.3f ms\n", a, b);
+        }
         for (int i = 1; i < nph; ++i) {
             float ms = 0.0f;
             cudaEventElapsedTime(&ms, pev[i - 1], pev[i]);

@@ -555,10 +555,12 @@ def ukf_batched_leg(args, torch, dev, B=16384, shape="cfg2"):
     import awesomeslam_b200 as A
     if shape == "cfg2":
         (lmx, lmy), msd, seed = A.map_cfg1(), 30, 0x0CF20000
+    elif shape == "cfg2_cap20":  # the same filters under a cap of 20 (N = 19 still fits): smaller footprint, 6 per SM
+        (lmx, lmy), msd, seed = A.map_cfg1(), 20, 0x0CF20000
     else:
         (lmx, lmy), msd, seed = A.map_cfg3(), 36, 0x0CF30000
     L = len(lmx)
-    K, W = min(args.steps, 10 if shape == "cfg2" else 5), max(args.warmup, 3)
+    K, W = min(args.steps, 5 if shape == "cfg3" else 10), max(args.warmup, 3)
     total = WARM_MSGS + (W + K) * FUSE
     rp = A.Replay(lmx, lmy, B, max(total, 120), seed0=seed)
     dev_t = [torch.from_numpy(a).to(dev) for a in (rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing)]
@@ -597,7 +599,7 @@ def ukf_batched_leg(args, torch, dev, B=16384, shape="cfg2"):
            "kernel": "ukf_batched_kernel<%d>" % msd,
            "updates_per_s": ups, "ms_per_launch": ms / K, "filters_with_llt_failure": failed,
            "fp64_tflops_20n3": ups * 20.0 * n ** 3 / 1e12}
-    if not args.no_cpu:
+    if not args.no_cpu and shape != "cfg2_cap20":
         nthr = host_threads()
         sample, msgs = ((1024 if nthr < 16 else 4096), 120) if shape == "cfg2" else ((256 if nthr < 16 else 1024), 80)
         sec, N, kind = cpu_filters_run("ukf", rp, sample, msgs, L, nthr, shape != "cfg2")
@@ -862,6 +864,7 @@ def main():
     if not args.no_large:
         laser = laser_leg(args, torch, dev)
         ukf_batched = ukf_batched_leg(args, torch, dev)
+        ukf_batched["max_state_dim_20"] = ukf_batched_leg(args, torch, dev, shape="cfg2_cap20")
         ukf_batched35 = ukf_batched_leg(args, torch, dev, B=65536, shape="cfg3")
 
     per_gpu_ups = value / world

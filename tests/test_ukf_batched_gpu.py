@@ -134,3 +134,27 @@ def test_cfg3_shape_batched_ukf(aslam, orc):
     # promotion (message 9) and the first updates at N = 35 are compared on every filter
     assert int(s["N"].max()) == 35 and first_blip >= 10 and checked >= 0.7 * B * T
     f.close()
+
+
+def test_ukf_footprint_instantiations_agree_bit_for_bit(aslam):
+    """The batched UKF kernel is instantiated per cap (padded dimensions 20, 24, 30, 36: the shared-memory footprint, and
+    with it the resident filters per SM, follows max_state_dim). The arithmetic does not depend on the padding: the same
+    8-landmark filters (N = 19) under caps 20, 24, 30 and 36 end bit-identical."""
+    lmx, lmy = aslam.map_cfg1()
+    B, T, L = 96, 40, len(lmx)
+    rp = aslam.Replay(lmx, lmy, B, T, seed0=0x0CF20000)
+    ref = None
+    for msd in (20, 24, 30, 36):
+        f = aslam.BatchedFilter("ukf", B, 0, max_state_dim=msd)
+        assert f.ld == msd
+        f.run_host(T, rp.x, rp.y, rp.yaw, rp.vx, rp.az, rp.dt, rp.range, rp.bearing, L)
+        s = f.get_state()
+        f.close()
+        n = 19
+        cur = (s["N"].copy(), s["X"][:, :n].copy(), s["P"][:, :n, :n].copy(), s["status"].copy())
+        assert np.all(cur[0] == n)
+        if ref is None:
+            ref = cur
+        else:
+            for a, b in zip(ref, cur):
+                assert np.array_equal(a, b), msd
