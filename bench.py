@@ -533,15 +533,21 @@ def large_parity(f, step_nccl, step_fused, torch, dist, rank, world, dev, rb, re
     return out
 
 
-def _ncu_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the cfg4 streaming update, from the committed
-    `ncu --set full` capture (profiles/r01_traffic.json names the capture); None when the file is absent."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+def _ncu_traffic(kernel="large_update_stream_kernel"):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the cfg4 streaming update, from the NEWEST committed
+    `ncu --set full` capture (profiles/rNN_traffic.json names the capture and the kernel it was taken from). None when
+    no file is there or when the newest capture is of another kernel (a stale number is worse than none)."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r[0-9][0-9]_traffic.json")))
+    if not files:
+        return None
     try:
-        with open(p) as fh:
+        with open(files[-1]) as fh:
             t = json.load(fh)
+        if kernel not in t.get("kernel", ""):
+            return None
         return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
-    except (OSError, KeyError, ValueError):
+    except (OSError, ValueError, KeyError):
         return None
 
 

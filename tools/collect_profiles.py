@@ -27,7 +27,11 @@ def main():
     shutil.copy(g("bench.json"), p("bench_n1.json"))
     shutil.copy(g("ref.json"), p("bench_reference_arm.json"))
     shutil.copy(g("launches.csv"), p("launches_bench.csv"))
-    for src, dst in (("large", "ncu_large_update.csv"), ("batched", "ncu_ekf_batched.csv"), ("laser", "ncu_laser_extract.csv")):
+    if os.path.exists(g("launches_ukf_large.csv")):
+        shutil.copy(g("launches_ukf_large.csv"), p("launches_ukf_large_step.csv"))
+    for src, dst in (("large", "ncu_large_update.csv"), ("batched", "ncu_ekf_batched.csv"), ("laser", "ncu_laser_extract.csv"),
+                     ("solve", "ncu_large_solve.csv"), ("dgemm", "ncu_dgemm_nt.csv"), ("chol", "ncu_chol_panel.csv"),
+                     ("tf32", "ncu_tf32_gemm.csv"), ("ukfb", "ncu_ukf_batched.csv")):
         if os.path.exists(g(src + ".ncu-rep")):
             raw_csv(g(src + ".ncu-rep"), p(dst))
             subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_digest.py"), p(dst)], check=True)

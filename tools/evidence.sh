@@ -27,4 +27,19 @@ fi
 if timeout 300 python tools/prof_target.py laser 65536 > /dev/null 2>&1; then
   timeout 900 $NCU -k 'regex:laser_(extract|fit)' -s 2 -c 4 -o $O/${T}_laser -f python tools/prof_target.py laser 65536 > $O/${T}_ncu_laser.log 2>&1; echo "laser rc=$?"
 fi
+# round 2: the solve kernel of the cfg4 step, the cfg5 kernels (DMMA GEMM, Cholesky panel, 256-block inverse; TF32 GEMM), the batched UKF
+if timeout 300 python tools/prof_target.py large 64 8 > /dev/null 2>&1; then
+  timeout 900 $NCU -k regex:large_solve -s 3 -c 1 -o $O/${T}_solve -f python tools/prof_target.py large 64 8 > $O/${T}_ncu_solve.log 2>&1; echo "solve rc=$?"
+fi
+if timeout 300 python tools/prof_target.py ukf_large 32 > /dev/null 2>&1; then
+  timeout 900 $NCU -k regex:dgemm_nt_kernel -s 150 -c 6 -o $O/${T}_dgemm -f python tools/prof_target.py ukf_large 32 > $O/${T}_ncu_dgemm.log 2>&1; echo "dgemm rc=$?"
+  timeout 900 $NCU -k 'regex:chol_panel|tri_inv256' -s 30 -c 3 -o $O/${T}_chol -f python tools/prof_target.py ukf_large 32 > $O/${T}_ncu_chol.log 2>&1; echo "chol rc=$?"
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file $O/${T}_launches_ukf_large.csv python tools/prof_target.py ukf_large 32 > $O/${T}_ncu_ukfl.log 2>&1; echo "ukf_large launch list rc=$?"
+fi
+if timeout 300 python tools/prof_target.py ukf_large 32 1 > /dev/null 2>&1; then
+  timeout 900 $NCU -k regex:tf32_gemm -s 3 -c 3 -o $O/${T}_tf32 -f python tools/prof_target.py ukf_large 32 1 > $O/${T}_ncu_tf32.log 2>&1; echo "tf32 rc=$?"
+fi
+if timeout 300 python tools/prof_target.py ukf 65536 8 > /dev/null 2>&1; then
+  timeout 900 $NCU -k regex:ukf_batched -s 1 -c 1 -o $O/${T}_ukfb -f python tools/prof_target.py ukf 65536 8 > $O/${T}_ncu_ukfb.log 2>&1; echo "ukf batched rc=$?"
+fi
 ls -la $O | grep ${T}_

@@ -3,7 +3,7 @@
   python tools/prof_target.py batched [B] [msgs]   cfg3 batched EKF kernel, B filters at N = 35
   python tools/prof_target.py ukf [B] [msgs]       batched UKF kernel, cfg3 shape (n = 35); ukf19: the cfg2 shape (n = 19)
   python tools/prof_target.py large [side] [m]     cfg4 large-map EKF step (side^2 landmarks)
-  python tools/prof_target.py ukf_large [side]     cfg5 large-map UKF step
+  python tools/prof_target.py ukf_large [side] [p] cfg5 large-map UKF step (p = 0 FP64, 1 TF32, 3 3xTF32 products)
   python tools/prof_target.py laser [B]            laser front end, B scans of the cfg3 map
 """
 import os
@@ -44,10 +44,12 @@ def large(side, m):
     print("large n", X0.size)
 
 
-def ukf_large(side):
+def ukf_large(side, precision=0):
     tx, ty, X0, G, d = A.large_map_state(side, pitch=100.0 / side)
     P0 = A.dense_P(G, d)
     f = A.LargeFilter("ukf", X0.size)
+    if precision:
+        f.set_precision(precision)
     f.load_state_colmajor(X0, P0)
     rng, brg, idx = A.large_observations(tx, ty, (0, 0, 0), m=8)
     for _ in range(3):
@@ -86,4 +88,4 @@ if __name__ == "__main__":
     elif mode == "large":
         large(arg[0] if arg else 64, arg[1] if len(arg) > 1 else 8)
     elif mode == "ukf_large":
-        ukf_large(arg[0] if arg else 32)
+        ukf_large(arg[0] if arg else 32, arg[1] if len(arg) > 1 else 0)
