@@ -134,6 +134,7 @@ SIGNATURES = {
     "aslam_large_ukf_set_precision": (_i32, [_vp, _i32]),
     "aslam_large_ukf_products_ms": (_i32, [_vp, C.POINTER(C.c_float)]),
     "aslam_dense_gemm_nt_tf32": (_i32, [_vp, _i32, _i32, _i32, _vp, _sz, _vp, _sz, _vp, _sz, _f64, _f64, _i32, _i32]),
+    "aslam_dense_gemm_nt_tf32_static": (_i32, [_vp, _i32, _i32, _i32, _vp, _sz, _vp, _sz, _vp, _sz, _f64, _f64, _i32, _i32]),
     "aslam_probe_tf32_tflops": (_i32, [_i32, C.POINTER(_f64)]),
     "aslam_replay_generate": (_i32, [_vp, _vp, _u32, _u32, _u32, _u32, _f64, _f64, C.c_uint64, _u32,
                                      _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

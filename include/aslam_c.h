@@ -286,6 +286,20 @@ aslam_status aslam_large_ukf_products_ms(aslam_large* h, float* ms);
 aslam_status aslam_dense_gemm_nt_tf32(void* stream, int32_t M, int32_t N, int32_t K, const double* d_A, size_t lda,
                                       const double* d_B, size_t ldb, double* d_C, size_t ldc, double alpha, double beta,
                                       int32_t lower_only, int32_t passes);
+/* aslam_dense_gemm_nt_tf32 for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels in the same order, same result; the scratch (FP32 hi / lo copies of both operands + the
+ * pipeline's error flag) lives in a file-scope static __device__ array of ASLAM_TF32_STATIC_SCRATCH_BYTES that every
+ * GPU loading the library holds until exit, so the call allocates and frees nothing. Runs on the CURRENT device.
+ * Limit: (round256(4 M Kp) + round256(4 N Kp)) * (passes == 3 ? 2 : 1) <= ASLAM_TF32_STATIC_SCRATCH_BYTES with
+ * Kp = K rounded up to 32 (e.g. M = N = 512, K = 1024, passes 3; or M = N = 1024, K = 1024, passes 1); beyond it the
+ * call returns ASLAM_ERR_UNSUPPORTED with the sizes in aslam_last_error() and touches nothing.
+ * Every call on a GPU shares the one array: calls that overlap on the same GPU (two streams, two host threads) RACE
+ * on it -- serialise them. Synchronous like the allocating form. */
+#define ASLAM_TF32_STATIC_SCRATCH_BYTES (8u * 1024u * 1024u)
+aslam_status aslam_dense_gemm_nt_tf32_static(void* stream, int32_t M, int32_t N, int32_t K, const double* d_A, size_t lda,
+                                             const double* d_B, size_t ldb, double* d_C, size_t ldc, double alpha,
+                                             double beta, int32_t lower_only, int32_t passes);
 /* Measured kind::tf32 tensor throughput of `device` (MMAs issued back to back from shared memory), TFLOP/s. */
 aslam_status aslam_probe_tf32_tflops(int32_t device, double* tflops);
 
