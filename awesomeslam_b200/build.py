@@ -69,7 +69,7 @@ def build_library(force=False, verbose=False):
         raise RuntimeError("nvcc failed")
     if force or procs or not os.path.exists(LIB):
         cmd = ["nvcc", "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a",
-               "-Xcompiler", "-pthread", "-o", LIB] + objs
+               "-Xcompiler", "-pthread", "-o", LIB] + objs + ["-ldl"]
         subprocess.check_call(cmd)
     return LIB
 

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "internal.hpp"
+#include "nvtx_range.hpp"
 
 namespace aslam {
 
@@ -476,6 +477,7 @@ aslam_status aslam_filter_step_device(aslam_filter* h, const aslam_odom* o) {
 }
 
 aslam_status aslam_filter_step(aslam_filter* h, const aslam_odom* o) {
+    ASLAM_NVTX("aslam_filter_step");
     if (!h || !o || !o->x || !o->y || !o->yaw || !o->vx || !o->az || !o->dt) return ASLAM_ERR_ARG;
     if (!h->have_obs) {
         set_error("step before the first set_observations (cbOdom returns while init_z, ekf.cpp:76)");
@@ -501,6 +503,7 @@ aslam_status aslam_filter_step(aslam_filter* h, const aslam_odom* o) {
 
 aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const aslam_odom* o, const float* d_range,
                                      const float* d_bearing, uint32_t obs_per_filter) {
+    ASLAM_NVTX("aslam_filter_run_device");
     if (!h || !o || !o->x || !o->y || !o->yaw || !o->vx || !o->az || !o->dt) return ASLAM_ERR_ARG;
     if (steps == 0) return ASLAM_OK;
     if (obs_per_filter && (!d_range || !d_bearing)) return ASLAM_ERR_ARG;
@@ -555,6 +558,7 @@ aslam_status aslam_filter_run_device(aslam_filter* h, uint32_t steps, const asla
 
 aslam_status aslam_filter_run_host(aslam_filter* h, uint32_t steps, const aslam_odom* o, const float* range,
                                    const float* bearing, uint32_t obs_per_filter) {
+    ASLAM_NVTX("aslam_filter_run_host");
     if (!h || !o || !o->x || !o->y || !o->yaw || !o->vx || !o->az || !o->dt) return ASLAM_ERR_ARG;
     if (steps == 0) return ASLAM_OK;
     if (obs_per_filter && (!range || !bearing)) return ASLAM_ERR_ARG;

@@ -11,6 +11,7 @@
 
 #include "dense_fp64.hpp"
 #include "large.hpp"
+#include "nvtx_range.hpp"
 
 namespace aslam {
 aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt, uint32_t m,
@@ -209,6 +210,7 @@ aslam_status aslam_large_get_state(aslam_large* h, double* X, double* P, size_t 
 
 aslam_status aslam_large_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
                               const float* range, const float* bearing, uint32_t m, int32_t* assoc_out) {
+    ASLAM_NVTX("aslam_large_step");
     if (!h) return ASLAM_ERR_ARG;
     ASLAM_CUDA(cudaSetDevice(h->device));
     aslam_status rc = stage_obs(h, range, bearing, m);
@@ -227,6 +229,7 @@ aslam_status aslam_large_step(aslam_large* h, double x, double y, float yaw, dou
 
 aslam_status aslam_large_step_phase1(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
                                      const float* range, const float* bearing, uint32_t m, uint32_t* q_out) {
+    ASLAM_NVTX("aslam_large_step_phase1");
     if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
     ASLAM_CUDA(cudaSetDevice(h->device));
     aslam_status rc = stage_obs(h, range, bearing, m);
@@ -245,6 +248,7 @@ aslam_status aslam_large_exchange_buffer(aslam_large* h, double** d_buf, size_t*
 }
 
 aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out) {
+    ASLAM_NVTX("aslam_large_step_phase2");
     if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
     ASLAM_CUDA(cudaSetDevice(h->device));
     aslam_status rc = large_ekf_phase2(h);
@@ -322,6 +326,7 @@ aslam_status aslam_large_peer_attach(aslam_large* h, uint32_t world, uint32_t ra
 
 aslam_status aslam_large_step_fused(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
                                     const float* range, const float* bearing, uint32_t m, int32_t* assoc_out) {
+    ASLAM_NVTX("aslam_large_step_fused");
     if (!h || h->kind != ASLAM_KIND_EKF) return ASLAM_ERR_ARG;
     ASLAM_CUDA(cudaSetDevice(h->device));
     aslam_status rc = stage_obs(h, range, bearing, m);

@@ -40,13 +40,15 @@ struct FrontParams {
     uint32_t* whits;
 };
 
+// The functions below are templates on the slot type: any struct with FrontSlot's member names will do (the batched
+// UKF keeps the arrays in storage it shares with its sigma-point matrices and passes a struct of pointers).
 // Phase A. X, Z: the filter's state vectors in shared memory (Z[0..2] already hold the
 // odometry pose); X may be a float copy of the state (the reference rounds the landmark coordinates
 // to float before the distance, ekf.cpp:161,166). lane/width: this thread's index in the filter's
 // thread group; observation o is range[obs_first + o]. TRACK: also fill owner[] / unassoc (both zeroed
 // by the caller before the call).
-template <bool TRACK = false, typename XT = double>
-__device__ __forceinline__ void front_phase_a(FrontSlot& s, const FrontParams& fp, const XT* X,
+template <bool TRACK = false, typename XT = double, typename Slot = FrontSlot>
+__device__ __forceinline__ void front_phase_a(Slot& s, const FrontParams& fp, const XT* X,
                                               const double* Z, const float* range, const float* bearing,
                                               uint32_t obs_first, uint32_t f, int lane, int width) {
     const double z0 = Z[0], z1 = Z[1], z2 = Z[2];
@@ -87,7 +89,8 @@ __device__ __forceinline__ void front_phase_a(FrontSlot& s, const FrontParams& f
 }
 
 // updateNewLandmarkWait (ekf.cpp:217-253) for observation o; runs on one thread.
-__device__ __forceinline__ void wait_list_update(FrontSlot& s, const FrontParams& fp, uint32_t f, uint32_t o) {
+template <typename Slot>
+__device__ __forceinline__ void wait_list_update(Slot& s, const FrontParams& fp, uint32_t f, uint32_t o) {
     float* wr = fp.wrange + (size_t)f * ASLAM_MAX_WAIT;
     float* wb = fp.wbearing + (size_t)f * ASLAM_MAX_WAIT;
     uint32_t* wh = fp.whits + (size_t)f * ASLAM_MAX_WAIT;
@@ -127,7 +130,8 @@ __device__ __forceinline__ void wait_list_update(FrontSlot& s, const FrontParams
 
 // Promotion of wait-list entries seen exactly `occ` times and growth of X/Z (ekf.cpp:190-203,
 // 255-290; the caller grows P). One thread per filter.
-__device__ __forceinline__ void front_promote(FrontSlot& s, const FrontParams& fp, double* X, double* Z, uint32_t f) {
+template <typename Slot>
+__device__ __forceinline__ void front_promote(Slot& s, const FrontParams& fp, double* X, double* Z, uint32_t f) {
     if (!s.promote) return;
     s.promote = 0;
     float* wr = fp.wrange + (size_t)f * ASLAM_MAX_WAIT;
@@ -164,7 +168,8 @@ __device__ __forceinline__ void front_promote(FrontSlot& s, const FrontParams& f
 // Phase B, one thread per filter. Writes Z for associated observations, maintains the
 // wait-list, promotes entries seen exactly `occ` times and grows X/Z (the caller grows P).
 // assoc: per-observation output for this filter or nullptr.
-__device__ __forceinline__ void front_phase_b(FrontSlot& s, const FrontParams& fp, double* X, double* Z,
+template <typename Slot>
+__device__ __forceinline__ void front_phase_b(Slot& s, const FrontParams& fp, double* X, double* Z,
                                               uint32_t f, int32_t* assoc) {
     s.grew_from = 0;
     for (uint32_t o = 0; o < s.nobs; ++o) {

@@ -17,6 +17,7 @@
 
 #include "device_math.cuh"
 #include "internal.hpp"
+#include "nvtx_range.hpp"
 
 namespace aslam {
 
@@ -517,6 +518,7 @@ aslam_status aslam_laser_destroy(aslam_laser* h) {
 
 aslam_status aslam_laser_extract_device(aslam_laser* h, const float* d_ranges, uint32_t nscan, float* d_range_out,
                                         float* d_bearing_out, int32_t* d_counts) {
+    ASLAM_NVTX("aslam_laser_extract_device");
     if (!h || !d_ranges || !d_range_out || !d_bearing_out || !d_counts) return ASLAM_ERR_ARG;
     if (nscan == 0) return ASLAM_OK;
     ASLAM_CUDA(cudaSetDevice(h->device));
@@ -539,6 +541,7 @@ aslam_status aslam_laser_extract_device(aslam_laser* h, const float* d_ranges, u
 
 aslam_status aslam_laser_extract(aslam_laser* h, const float* ranges, uint32_t nscan, float* range_out,
                                  float* bearing_out, int32_t* counts) {
+    ASLAM_NVTX("aslam_laser_extract");
     if (!h || !ranges || !range_out || !bearing_out || !counts || nscan > h->max_scans) return ASLAM_ERR_ARG;
     if (nscan == 0) return ASLAM_OK;
     ASLAM_CUDA(cudaSetDevice(h->device));

@@ -34,14 +34,42 @@ constexpr int UTHREADS = 128;
 // quotient of two small integers is within 1 ulp of the true one, so truncating (e + 0.5) / d is exact.
 __device__ __forceinline__ int fdiv_small(int e, float rcp_d) { return (int)(((float)e + 0.5f) * rcp_d); }
 
+// The front end's per-message arrays (FrontSlot's, frontend.cuh): dead once the association / wait-list phase is over,
+// so they share the bytes of the sigma-point matrices.
+struct UkfFrontArrays {
+    float2 opt[ASLAM_MAX_OBS];
+    float orng[ASLAM_MAX_OBS];
+    float obrg[ASLAM_MAX_OBS];
+    float omind[ASLAM_MAX_OBS];
+    int32_t ocorr[ASLAM_MAX_OBS];
+    float2 wpt[ASLAM_MAX_WAIT];
+};
+// FrontSlot's member names, the arrays as pointers into UkfFrontArrays (owner / ohit belong to the TRACK mode of phase
+// A, which this kernel does not use: null).
+struct UkfFront {
+    float2* opt;
+    float* orng;
+    float* obrg;
+    float* omind;
+    int32_t* ocorr;
+    float2* wpt;
+    int32_t* owner;
+    uint8_t* ohit;
+    uint32_t nobs, obs_base, wcount, N, status, flags, grew_from, unassoc;
+    int32_t promote;
+    double ox, oy, vx, az;
+    float yaw, dt;
+};
+
 template <int UNP>
 struct __align__(16) UkfSlot {
     static constexpr int UNA = UNP + 2;      // augmented
     static constexpr int UNS = 2 * UNP + 5;  // sigma points
     static constexpr int USP = UNS | 1;      // row pitch of the sigma-point matrices (odd: conflict-free row walks)
-    // The sigma-point matrices are dead once P, S and Tc have been formed; the LU factors of S, its inverse and K live
-    // in the same bytes from then on (a barrier separates the two uses): 3 instead of 2 CTAs per SM.
+    // Three generations share these bytes, a barrier between each: the front end's arrays (association, wait-list);
+    // the sigma-point matrices; and, once P, S and Tc have been formed, the LU factors of S, its inverse and K.
     union {
+        UkfFrontArrays fa;
         struct {
             double XS[UNP][USP];   // XsigPred, later Xdiff       (row = state index, col = sigma point)
             double ZS[UNP][USP];   // Zsig, later Zdiff
@@ -52,14 +80,16 @@ struct __align__(16) UkfSlot {
             double Si[UNP][UNP];
         };
     };
-    double L[UNA][UNA];    // Paug -> L (ukf.cpp:263-280); later K S
+    // Paug -> L (ukf.cpp:263-280), dead after the sigma points; then Tc (written by the covariance sums, dead once K is
+    // formed); then K S. UNA^2 >= UNP^2 doubles.
+    double L[UNA][UNA];
     double P[UNP][UNP];
     double S[UNP][UNP];
-    double Tc[UNP][UNP];
     double X[UNP], Z[UNP], Zp[UNP], Zd[UNP], Ld[UNA];
     int piv[UNP];
     int fail_k;
-    FrontSlot fr;
+    UkfFront fr;
+    __device__ __forceinline__ double (*Tc())[UNP] { return reinterpret_cast<double(*)[UNP]>(&L[0][0]); }
 };
 
 struct UkfParams {
@@ -90,6 +120,15 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
         s.fr.flags = kp.st.flags[f];
         s.fr.wcount = kp.st.wcount[f];
         s.fr.promote = 0;
+        s.fr.opt = s.fa.opt;
+        s.fr.orng = s.fa.orng;
+        s.fr.obrg = s.fa.obrg;
+        s.fr.omind = s.fa.omind;
+        s.fr.ocorr = s.fa.ocorr;
+        s.fr.wpt = s.fa.wpt;
+        s.fr.owner = nullptr;
+        s.fr.ohit = nullptr;
+        s.fr.unassoc = 0;
         s.fail_k = kp.st.llt_fail[f];
     }
     __syncthreads();
@@ -309,7 +348,7 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
             auto put = [&](int which, int a, int b, double acc) {
                 if (which == 0) s.P[a][b] = acc + ((a == b && a < 3) ? kp.kq : 0.0);
                 else if (which == 1) s.S[a][b] = acc + (a == b ? kp.kr : 0.0);
-                else s.Tc[a][b] = acc;
+                else s.Tc()[a][b] = acc;
             };
             const int total = 3 * N * N;
             int e0 = tid;
@@ -454,7 +493,7 @@ __global__ void __launch_bounds__(UTHREADS) ukf_batched_kernel(const UkfParams k
                     if (in[q]) store(ii[q], jj[q], acc[q]);
             }
         };
-        product3([&](int i, int k) { return s.Tc[i][k]; }, [&](int k, int j) { return I[k * UNP + j]; },
+        product3([&](int i, int k) { return s.Tc()[i][k]; }, [&](int k, int j) { return I[k * UNP + j]; },
                  [&](int i, int j, double v) { s.K[i][j] = v; });
         for (int k = tid; k < N; k += UTHREADS) {
             double d = s.Z[k] - s.Zp[k];

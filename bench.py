@@ -551,6 +551,20 @@ def _ncu_traffic(kernel="large_update_stream_kernel"):
         return None
 
 
+def _ncu_batched_pipe():
+    """FP64-pipe utilisation of the cfg3 batched kernel from the newest committed ncu capture
+    (profiles/rNN_batched_pipe.json, written by tools/collect_profiles.py); None when absent."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r[0-9][0-9]_batched_pipe.json")))
+    if not files:
+        return None
+    try:
+        with open(files[-1]) as fh:
+            return json.load(fh).get("pipe_fp64_active_pct")
+    except (OSError, ValueError):
+        return None
+
+
 def ukf_batched_leg(args, torch, dev, B=16384, shape="cfg2"):
     """Batched UKF-SLAM (K2). shape "cfg2": the reference's UKFSlam at its own size -- the landmarks.yaml map, n = 19,
     43 sigma points, max_state_dim 30 (the reference's cap). shape "cfg3": 16 landmarks, n = 35, n_aug = 37, 75 sigma
@@ -634,8 +648,30 @@ def large_cpu_leg(steps=10):
         sec.append(time.perf_counter() - t0)
     assert q == 19 and np.all(np.isfinite(X))
     t = float(np.mean(sec[1:]))
-    return {"value": 1.0 / t, "unit": "steps/s", "cores": O.num_threads(), "kind": "port",
-            "sample": "%d full-size steps (n=8195, q=19) after one warm-up step, %.2f s each" % (steps, t)}
+    out = {"value": 1.0 / t, "unit": "steps/s", "cores": O.num_threads(), "kind": "port",
+           "sample": "%d full-size steps (n=8195, q=19) after one warm-up step, %.2f s each" % (steps, t)}
+    # the reference's own form -- the verbatim DENSE EKFSlam::slam (ekf.cpp:293-311: N x N S, S.inverse(),
+    # K = P H' S^-1, (I - K H) P) -- timed on one core at L = 121 and L = 256 landmarks and extrapolated by n^3 to
+    # n = 8195 (labelled: an extrapolation; at full size the 537 MB matrices no longer fit any cache, so it favours the CPU)
+    from oracle import np_restatement as R
+    dense = []
+    for side in (11, 16):
+        tx, ty, X0, G, d = A.large_map_state(side)
+        P0 = A.dense_P(G, d)
+        rng, brg, idx = A.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8)
+        o = O.Filter("ekf", max_state_dim=100000)
+        o.load_state(X0, R.measurement(X0.size, X0), P0)
+        o.set_observations(rng, brg)
+        t0 = time.perf_counter()
+        o.step(0.0, 0.0, 0.0, 0.05, 0.1, 1.0)
+        dense.append((X0.size, time.perf_counter() - t0))
+    n1, t1 = dense[-1]
+    full = t1 * (8195.0 / n1) ** 3
+    out["dense_reference_form"] = {
+        "value": 1.0 / full, "unit": "steps/s", "cores": 1, "kind": "port", "extrapolated": True,
+        "sample": "verbatim dense slam: n=%d %.2f s, n=%d %.2f s (exponent %.2f); x (8195/%d)^3 = %.0f s per full-size step"
+                  % (dense[0][0], dense[0][1], n1, t1, np.log(t1 / dense[0][1]) / np.log(n1 / dense[0][0]), n1, full)}
+    return out
 
 
 def ukf_large_cpu_leg():
@@ -894,6 +930,9 @@ def main():
             "achieved": per_gpu_ups * FLOP_PER_UPDATE / 1e12, "peak": fp64, "unit": "TFLOP/s",
             "frac": (per_gpu_ups * FLOP_PER_UPDATE / 1e12 / fp64) if fp64 else None,
             "flop_convention": "6 n^3 = 257,250 per update (SURVEY 8d); the kernel executes ~n^3 fma",
+            "achieved_executed": per_gpu_ups * 2.0 * 35 ** 3 / 1e12,
+            "frac_executed": (per_gpu_ups * 2.0 * 35 ** 3 / 1e12 / fp64) if fp64 else None,
+            "pipe_fp64_active_pct_ncu": _ncu_batched_pipe(),
             "hbm_frac_if_streamed": per_gpu_ups * BYTES_PER_UPDATE / 1e9 / hbm_peak,
             "peak_source": "aslam_probe_fp64_tflops (DFMA chain, this run)"},
     }

@@ -333,3 +333,60 @@ def test_cfg3_long_free_run_blip_count(aslam, orc):
     print("cfg3 free run, %d filters x %d messages: %d beyond 1e-9, worst %.3e" % (B, T, beyond, err.max()))
     assert beyond == 0
     f.close()
+
+
+def _far_apart_observations(count, skip=0):
+    """(range, bearing) float32 pairs of `count` points on a 1 m grid around a robot at rest at the origin (so every
+    pair of points is at least 1 m apart, twice the association threshold), none closer than 2 m to the robot."""
+    pts = [(i, j) for i in range(-12, 13) for j in range(-12, 13) if i * i + j * j >= 4]
+    pts = np.array(pts[skip:skip + count], dtype=np.float64)
+    assert pts.shape[0] == count
+    return np.hypot(pts[:, 0], pts[:, 1]).astype(np.float32), np.arctan2(pts[:, 1], pts[:, 0]).astype(np.float32)
+
+
+@pytest.mark.parametrize("kind", ["ekf", "ukf"])
+def test_wait_list_and_observation_bounds(aslam, orc, kind):
+    """ASLAM_MAX_OBS = 64 observations per message and ASLAM_MAX_WAIT = 256 wait-list entries bound what the reference
+    leaves unbounded (std::vector, ekf.h:104). AT the bound the kernels equal the oracle: 4 messages x 64 new, mutually
+    distant observations fill the wait-list to exactly 256 entries with a clean status. BEYOND it they say so: one more
+    new observation raises ASLAM_ST_WAIT_OVERFLOW (the list keeps its 256 entries), a message of 65 observations raises
+    ASLAM_ST_OBS_OVERFLOW (the first 64 are used)."""
+    f = aslam.BatchedFilter(kind, 1, 0)
+    o = orc.Filter(kind)
+    odom = ([0.0], [0.0], [0.0], [0.0], [0.0], [1.0])
+    for msg in range(4):
+        r, b = _far_apart_observations(64, skip=64 * msg)
+        f.set_observations(r, b)
+        f.step(*odom)
+        o.set_observations(r, b)
+        o.step(0.0, 0.0, 0.0, 0.0, 0.0, 1.0)
+    w = f.get_wait()
+    wr, wb, wh = o.wait(cap=512)
+    s = f.get_state()
+    assert int(w["count"][0]) == 256 == wr.size and int(s["status"][0]) == 0 and int(s["N"][0]) == 3 == o.N
+    assert np.array_equal(w["range"][0], wr) and np.array_equal(w["bearing"][0], wb) and np.array_equal(w["hits"][0], wh)
+    assert np.all(wh == 1)
+    # a re-observation of an entry is a hit, not an append: still no overflow
+    r, b = _far_apart_observations(1, skip=100)
+    f.set_observations(r, b)
+    f.step(*odom)
+    w = f.get_wait()
+    assert int(f.get_state()["status"][0]) == 0 and int(w["count"][0]) == 256 and int(w["hits"][0, 100]) == 2
+    # entry 257
+    r, b = _far_apart_observations(1, skip=256)
+    f.set_observations(r, b)
+    f.step(*odom)
+    st = int(f.get_state()["status"][0])
+    assert st & aslam.capi.ST_WAIT_OVERFLOW and not st & aslam.capi.ST_OBS_OVERFLOW
+    assert int(f.get_wait()["count"][0]) == 256
+    f.close()
+    # 65 observations in one message
+    g = aslam.BatchedFilter(kind, 1, 0)
+    r, b = _far_apart_observations(65)
+    g.set_observations(r, b)
+    g.step(*odom)
+    st = int(g.get_state()["status"][0])
+    assert st & aslam.capi.ST_OBS_OVERFLOW
+    w = g.get_wait()
+    assert int(w["count"][0]) == 64 and np.array_equal(w["range"][0, :64], r[:64])
+    g.close()

@@ -32,8 +32,11 @@ def main():
     for src, dst in (("large", "ncu_large_update.csv"), ("batched", "ncu_ekf_batched.csv"), ("laser", "ncu_laser_extract.csv"),
                      ("solve", "ncu_large_solve.csv"), ("dgemm", "ncu_dgemm_nt.csv"), ("chol", "ncu_chol_panel.csv"),
                      ("tf32", "ncu_tf32_gemm.csv"), ("ukfb", "ncu_ukf_batched.csv")):
-        if os.path.exists(g(src + ".ncu-rep")):
+        if os.path.exists(g(src + ".raw.csv")):
+            shutil.copy(g(src + ".raw.csv"), p(dst))
+        elif os.path.exists(g(src + ".ncu-rep")):
             raw_csv(g(src + ".ncu-rep"), p(dst))
+        if os.path.exists(p(dst)) and (os.path.exists(g(src + ".raw.csv")) or os.path.exists(g(src + ".ncu-rep"))):
             subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_digest.py"), p(dst)], check=True)
     # dram traffic of the cfg4 streaming update (bench.py reports it as roofline.traffic)
     import csv
@@ -56,6 +59,19 @@ def main():
     with open(p("traffic.json"), "w") as fh:
         json.dump(t, fh, indent=1)
     print(json.dumps(t))
+    # FP64-pipe utilisation of the cfg3 batched kernel (bench.py reports it beside the flop-convention fraction)
+    if os.path.exists(p("ncu_ekf_batched.csv")):
+        rows = list(csv.reader(open(p("ncu_ekf_batched.csv"))))
+        col = {h: i for i, h in enumerate(rows[0])}
+        key = "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"
+        data = [r for r in rows[2:] if "ekf_batched" in r[col["Kernel Name"]]]
+        if data and key in col:
+            b = {"source": "profiles/%s_ncu_ekf_batched.csv (ncu --set full, evidence run %s)" % (rnd, tag),
+                 "kernel": data[0][col["Kernel Name"]].split("(")[0].split("::")[-1],
+                 "pipe_fp64_active_pct": statistics.median(float(r[col[key]].replace(",", "")) for r in data)}
+            with open(p("batched_pipe.json"), "w") as fh:
+                json.dump(b, fh, indent=1)
+            print(json.dumps(b))
     subprocess.run([sys.executable, os.path.join(ROOT, "tools", "launch_summary.py"), p("launches_bench.csv")], check=True)
 
 

@@ -42,4 +42,11 @@ fi
 if timeout 300 python tools/prof_target.py ukf 65536 8 > /dev/null 2>&1; then
   timeout 900 $NCU -k regex:ukf_batched -s 1 -c 1 -o $O/${T}_ukfb -f python tools/prof_target.py ukf 65536 8 > $O/${T}_ncu_ukfb.log 2>&1; echo "ukf batched rc=$?"
 fi
+# gpurun brings back at most 64 MiB: keep the raw-page CSV of every capture (what tools/collect_profiles.py reads) and
+# drop the .ncu-rep files unless KEEP_REP=1
+for rep in $O/${T}_*.ncu-rep; do
+  [ -f "$rep" ] || continue
+  ncu -i "$rep" --page raw --csv > "${rep%.ncu-rep}.raw.csv" 2>/dev/null
+  [ "${KEEP_REP:-0}" = "1" ] || rm -f "$rep"
+done
 ls -la $O | grep ${T}_
