@@ -145,7 +145,6 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
             // ekf.cpp:87-91 X = Z on the first processed message: the pose rows here, the landmark rows
             // (other threads may still be writing Z) behind the next barrier
             const bool initx = s.fr.flags & FLAG_INIT_X;
-            motion_jacobian(s.fr.vx, s.fr.az, s.fr.dt, s.Z[2], s.a00, s.a10);  // ekf.cpp:206-212
             // slam(): ekf.cpp:295-296
             double x = initx ? s.Z[0] : s.X[0], y = initx ? s.Z[1] : s.X[1], th = initx ? s.Z[2] : s.X[2];
             motion_model(x, y, th, (float)s.fr.vx, (float)s.fr.az, s.fr.dt);
@@ -154,6 +153,9 @@ __global__ void __launch_bounds__(Geo<NP, CPT>::THREADS) ekf_batched_kernel(cons
             s.X[2] = (double)normalize_angle((float)th, kp.fp.pi);
             atomicMax(&s_lcta, (int)(s.fr.N - 3) / 2);
         }
+        // ekf.cpp:206-212 on the filter's second thread, beside the pose predict of the first: the two are independent
+        // (inputs: the message and Z[2], the odometry yaw) and each is a chain of two double-precision sincos
+        if (ct == 1 && !gated) motion_jacobian(s.fr.vx, s.fr.az, s.fr.dt, s.Z[2], s.a00, s.a10);
         __syncthreads();
         const uint32_t N = s.fr.N;
         const int lcta = s_lcta;
