@@ -69,7 +69,7 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
     A((void**)&h->P, (size_t)n * h->ldp * sizeof(double));
     A((void**)&h->X, (size_t)n * sizeof(double));
     A((void**)&h->A, 2 * sizeof(double));
-    A((void**)&h->predA, 2 * sizeof(double));
+    A((void**)&h->predA, 4 * sizeof(double));
     A((void**)&h->sync, 4 * sizeof(unsigned long long));
     A((void**)&h->ctx, sizeof(LargeCtx));
     A((void**)&h->d_obs, 2 * ASLAM_MAX_OBS * sizeof(float));
@@ -79,6 +79,16 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
         A((void**)&h->K, (size_t)132 * n * sizeof(double));
     }
     if (rc == ASLAM_OK && !cuda_ok(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+    if (rc == ASLAM_OK && kind == ASLAM_KIND_EKF) {
+        // highest priority: its few small CTAs are placed ahead of the next update's 148 when an SM has room for either
+        int prio_lo = 0, prio_hi = 0;
+        cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+        if (!cuda_ok(cudaStreamCreateWithPriority(&h->solve_stream, cudaStreamNonBlocking, prio_hi), "cudaStreamCreate")) rc = ASLAM_ERR_CUDA;
+        cudaEvent_t* evs[] = {&h->ev_before_upd, &h->ev_now, &h->ev_solve};
+        for (cudaEvent_t* e : evs)
+            if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(e, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
+        h->no_overlap = std::getenv("ASLAM_LARGE_NO_OVERLAP") != nullptr;  // diagnostic switch, same kernels either way
+    }
     if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(&h->ev_ctx_free, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
     if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
     if (rc == ASLAM_OK && !cuda_ok(cudaEventCreate(&h->ev0), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
@@ -154,14 +164,19 @@ aslam_status aslam_large_destroy(aslam_large* h) {
     if (!h) return ASLAM_OK;
     cudaSetDevice(h->device);
     if (h->side) cudaStreamSynchronize(h->side);
+    if (h->solve_stream) cudaStreamSynchronize(h->solve_stream);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ukf) large_ukf_destroy(h);
+    if (h->solve_stream) cudaStreamDestroy(h->solve_stream);
+    if (h->ev_before_upd) cudaEventDestroy(h->ev_before_upd);
+    if (h->ev_now) cudaEventDestroy(h->ev_now);
+    if (h->ev_solve) cudaEventDestroy(h->ev_solve);
     if (h->ev_ctx_free) cudaEventDestroy(h->ev_ctx_free);
     if (h->ev_front) cudaEventDestroy(h->ev_front);
     if (h->side) cudaStreamDestroy(h->side);
     for (int p = 0; p < LARGE_MAX_PEERS; ++p)
         if (h->peer_ipc[p] && h->peer_base[p]) cudaIpcCloseMemHandle(h->peer_base[p]);
-    void* ptrs[] = {h->P, h->X, h->A, h->predA, h->sync, h->trace, h->ctx, h->d_obs, h->exch, h->hp, h->K, h->peer_block};
+    void* ptrs[] = {h->P, h->P_alt, h->X, h->A, h->predA, h->sync, h->trace, h->ctx, h->d_obs, h->exch, h->hp, h->K, h->peer_block};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -184,6 +199,7 @@ aslam_status aslam_large_load_state(aslam_large* h, const double* X, const doubl
     if (!h || !X || !P || ldp < h->n) return ASLAM_ERR_ARG;
     ASLAM_CUDA(cudaSetDevice(h->device));
     const size_t n = h->n, rows = h->row_end - h->row_begin;
+    h->pending = false;  // (ordered on `stream` behind the last update, which ends after the last solve kernel)
     ASLAM_CUDA(cudaMemcpyAsync(h->X, X, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     ASLAM_CUDA(cudaMemcpy2DAsync(h->P, h->ldp * sizeof(double), P + h->row_begin, ldp * sizeof(double),
                                  rows * sizeof(double), n, cudaMemcpyHostToDevice, h->stream));
@@ -344,6 +360,7 @@ aslam_status aslam_large_trace(aslam_large* h, unsigned long long* out1024) {
     if (!h->trace) return ASLAM_ERR_UNSUPPORTED;
     ASLAM_CUDA(cudaSetDevice(h->device));
     ASLAM_CUDA(cudaStreamSynchronize(h->side));
+    if (h->solve_stream) ASLAM_CUDA(cudaStreamSynchronize(h->solve_stream));
     ASLAM_CUDA(cudaStreamSynchronize(h->stream));
     ASLAM_CUDA(cudaMemcpy(out1024, h->trace, 64 * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return ASLAM_OK;

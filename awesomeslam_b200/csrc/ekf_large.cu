@@ -118,6 +118,16 @@ __global__ void __launch_bounds__(FRONT_THREADS) large_front_kernel(FrontArgs a,
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t L = (n - 3) / 2;
     const double z0 = a.ox, z1 = a.oy, z2 = (double)a.yaw;
+    // (issued now, used by thread 32 after the association: one memory round trip less on the way)
+    double pa00 = 0.0, pa10 = 0.0, px = 0.0, py = 0.0, pth = 0.0;
+    if (tid == 32) {
+        px = X[0];
+        py = X[1];
+        pth = X[2];
+    } else if (tid == 64) {
+        pa00 = A[0];
+        pa10 = A[1];
+    }
     // ---- nearest landmark of every observation. Thread o < m projects observation o (structures.h:104-111); then
     // every thread keeps a few landmarks in registers and scans all observations against them: one pass over X,
     // one round of warp reductions, one CTA barrier, one final reduction per observation.
@@ -129,7 +139,8 @@ __global__ void __launch_bounds__(FRONT_THREADS) large_front_kernel(FrontArgs a,
         s_pt[tid] = to_point(a.range[tid], b, z0, z1, z2);
     }
     __syncthreads();
-    constexpr int LPT = 4;  // landmarks per thread and pass
+    constexpr int LPT = 16;  // landmarks per thread and pass: 4096 landmarks in ONE pass -- every load of X in flight at once, one
+                             // round of warp reductions per observation (the kernel is on the critical path of the sharded step)
     if (lane == 0)
         for (uint32_t o = 0; o < a.m; ++o) s_red[o][warp] = ~0ull;
     __syncwarp();
@@ -200,13 +211,15 @@ __global__ void __launch_bounds__(FRONT_THREADS) large_front_kernel(FrontArgs a,
         }
         s_cnt = cnt;
         ctx->q = 3 + 2 * cnt;
-    } else if (tid == 32) {
-        // ---- A (ekf.cpp:206-212) and the pose predict (ekf.cpp:295-296)
-        double a00 = A[0], a10 = A[1];
+    } else if (tid == 64) {
+        // ---- A (ekf.cpp:206-212), beside the pose predict of thread 32: two independent chains of two sincos each
+        double a00 = pa00, a10 = pa10;
         motion_jacobian(a.vx, a.az, a.dt, z2, a00, a10);
         A[0] = a00;
         A[1] = a10;
-        double x = X[0], y = X[1], th = X[2];
+    } else if (tid == 32) {
+        // ---- the pose predict (ekf.cpp:295-296)
+        double x = px, y = py, th = pth;
         motion_model(x, y, th, (float)a.vx, (float)a.az, a.dt);
         th = (double)normalize_angle((float)th, a.pi);
         s_pose[0] = x;
@@ -897,7 +910,7 @@ struct StreamGeo {
 
 template <int CW, int R, int Q, int CS, int NST>
 __global__ void __launch_bounds__((CW + 1) * 32, 1) large_update_stream_kernel(
-    StreamPlan pl, size_t ldp, double* __restrict__ P, const double* __restrict__ K, const double* __restrict__ hp,
+    StreamPlan pl, size_t ldp, const double* Pin, double* Pout, const double* __restrict__ K, const double* __restrict__ hp,
     const double* __restrict__ predA, double kq, const unsigned long long* sync, unsigned long long epoch,
     unsigned long long* trace) {
     using G = StreamGeo<CW, R, Q, CS, NST>;
@@ -934,7 +947,7 @@ __global__ void __launch_bounds__((CW + 1) * 32, 1) large_update_stream_kernel(
             bulk::mbar_expect_tx(&full[st], cw * seg_bytes + cw * Q * (uint32_t)sizeof(double));
             double* dp = stage_p(st);
             for (uint32_t c = 0; c < cw; ++c)
-                bulk::g2s(dp + c * G::ROWS, P + (size_t)(c0 + c) * ldp + (size_t)b * pl.blk_rows, seg_bytes, &full[st]);
+                bulk::g2s(dp + c * G::ROWS, Pin + (size_t)(c0 + c) * ldp + (size_t)b * pl.blk_rows, seg_bytes, &full[st]);
         };
         auto issue_h = [&](uint32_t g) {
             const int st = (g - g_begin) % NST;
@@ -956,7 +969,7 @@ __global__ void __launch_bounds__((CW + 1) * 32, 1) large_update_stream_kernel(
             bulk::mbar_wait(&done[st], (li / NST) & 1u);
             const double* sp = stage_p(st);
             for (uint32_t c = 0; c < cw; ++c)
-                bulk::s2g(P + (size_t)(c0 + c) * ldp + (size_t)b * pl.blk_rows, sp + c * G::ROWS, seg_bytes);
+                bulk::s2g(Pout + (size_t)(c0 + c) * ldp + (size_t)b * pl.blk_rows, sp + c * G::ROWS, seg_bytes);
             bulk::commit_group();
             const uint32_t nxt = g + NST - 1;  // goes into the stage drained one chunk ago
             if (nxt < g_end) {
@@ -1167,6 +1180,106 @@ __device__ __forceinline__ void gather_cols(const double* __restrict__ P, size_t
 #pragma unroll 1
         for (int k = 0; k < QT; ++k) {
             const double cv = k < q ? pred_entry(P, ldp, rb, t, (uint32_t)s_rows[k], a00, a10, kq) : 0.0;
+#pragma unroll
+            for (int kk = 0; kk < QT; ++kk)
+                if (kk == k) colv[kk] = cv;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Overlapped steps (large_ekf_phase2_fast): the solve kernel of step k+1 runs WHILE the streaming update of step k
+// is still writing P_k -- out of place, into the handle's second buffer. What the solve kernel needs of P_k (q rows /
+// columns and the q x q block) it computes itself from the stored P_{k-1} and the previous step's K, H_o P and A:
+// exactly what large_update_stream_kernel writes for that entry -- its predict (pred_entry with the previous A) and
+// then its rank-Q update, k ascending, one fma per term -- so the value is bit-identical to the one in flight.
+// ------------------------------------------------------------------------------------------
+struct PrevUpd {
+    const double* K;      // [QT][n] gain of the previous step; nullptr: nothing in flight, the stored entries are final
+    const double* hp;     // [n][QT] its H_o P
+    const double* predA;  // [2] its A(0,0), A(1,0)
+    double kq;
+};
+
+// The predict of pred_entry() on top of any accessor at(i, j) of the un-predicted matrix (same expressions).
+template <class Acc>
+__device__ __forceinline__ double pred_entry_acc(Acc at, uint32_t i, uint32_t j, double a00, double a10, double kq) {
+    if (i < 2 && j < 2) {
+        const double p00 = at(0u, 0u), p10 = at(1u, 0u), p01 = at(0u, 1u), p11 = at(1u, 1u);
+        const double r00 = a00 * p00, r01 = a00 * p01;
+        const double r10 = a10 * p00 + p10, r11 = a10 * p01 + p11;
+        if (i == 0) return j == 0 ? r00 * a00 + kq : r00 * a10 + r01;
+        return j == 0 ? r10 * a00 : r10 * a10 + r11 + kq;
+    }
+    if (i < 2) {
+        const double p0 = at(0u, j);
+        return i == 0 ? a00 * p0 : a10 * p0 + at(1u, j);
+    }
+    if (j < 2) {
+        const double p0 = at(i, 0u);
+        return j == 0 ? p0 * a00 : p0 * a10 + at(i, 1u);
+    }
+    const double v = at(i, j);
+    return (i == 2 && j == 2) ? v + kq : v;
+}
+
+// Entry (i, j) of the matrix the previous step's update is producing (row i owned by this shard), from the stored one.
+template <int QT>
+__device__ __forceinline__ double pv_entry(const double* __restrict__ P, size_t ldp, uint32_t rb, uint32_t n, uint32_t i,
+                                           uint32_t j, const PrevUpd& pu) {
+    if (!pu.K) return P[(size_t)j * ldp + (i - rb)];
+    double v = pred_entry(P, ldp, rb, i, j, pu.predA[0], pu.predA[1], pu.kq);
+#pragma unroll
+    for (int k = 0; k < QT; ++k) v = fma(-pu.K[(size_t)k * n + i], pu.hp[(size_t)j * QT + k], v);
+    return v;
+}
+
+// gather_cols() on top of the update in flight: colv[k] = predicted P_k(t, rows[k]) for the shard's own row t.
+// s_hpp[k][:] = row rows[k] of the previous H_o P (staged by the caller; rows[0..2] = 0, 1, 2).
+template <int QT>
+__device__ __forceinline__ void gather_cols_v(const double* __restrict__ P, size_t ldp, uint32_t rb, uint32_t n,
+                                              uint32_t t, bool mine, int q, const int* s_rows, double a00, double a10,
+                                              double kq, const PrevUpd& pu, const double (*s_hpp)[QT],
+                                              double (&colv)[QT]) {
+    if (!pu.K) {
+        gather_cols<QT>(P, ldp, rb, t, mine, q, s_rows, a00, a10, kq, colv);
+        return;
+    }
+    if (!mine) {
+#pragma unroll
+        for (int k = 0; k < QT; ++k) colv[k] = 0.0;
+    } else if (t >= 2) {
+        double nk[QT];
+#pragma unroll
+        for (int m = 0; m < QT; ++m) nk[m] = -pu.K[(size_t)m * n + t];
+        const double pa00 = pu.predA[0], pa10 = pu.predA[1];
+        // the previous predict on the stored row t (columns 0, 1 and the (2,2) entry), then the previous rank-Q update
+        const double p0 = P[t - rb];
+        double e[QT];
+        e[0] = p0 * pa00;
+        e[1] = p0 * pa10 + P[ldp + (t - rb)];
+        const double p2 = P[2 * ldp + (t - rb)];
+        e[2] = t == 2 ? p2 + pu.kq : p2;
+#pragma unroll
+        for (int k = 3; k < QT; ++k) e[k] = k < q ? P[(size_t)s_rows[k] * ldp + (t - rb)] : 0.0;
+#pragma unroll
+        for (int k = 0; k < QT; ++k) {
+            double v = e[k];
+#pragma unroll
+            for (int m = 0; m < QT; ++m) v = fma(nk[m], s_hpp[k][m], v);
+            e[k] = v;
+        }
+        // this step's predict (gather_cols)
+        colv[0] = 0 < q ? e[0] * a00 : 0.0;
+        colv[1] = 1 < q ? e[0] * a10 + e[1] : 0.0;
+        colv[2] = 2 < q ? (t == 2 ? e[2] + kq : e[2]) : 0.0;
+#pragma unroll
+        for (int k = 3; k < QT; ++k) colv[k] = k < q ? e[k] : 0.0;
+    } else {
+        auto at = [&](uint32_t i, uint32_t j) { return pv_entry<QT>(P, ldp, rb, n, i, j, pu); };
+#pragma unroll 1
+        for (int k = 0; k < QT; ++k) {
+            const double cv = k < q ? pred_entry_acc(at, t, (uint32_t)s_rows[k], a00, a10, kq) : 0.0;
 #pragma unroll
             for (int kk = 0; kk < QT; ++kk)
                 if (kk == k) colv[kk] = cv;
@@ -1430,15 +1543,22 @@ __device__ __forceinline__ void gather_rows_cols(const double* __restrict__ P, s
 //           destination, and only then waits (bounded) for the counters of all sources. On a timeout the step is
 //           ABANDONED cleanly: K = 0, X keeps its predicted value, H_o P = 0 -- the update then applies the predict
 //           only -- and ASLAM_ST_PEER_TIMEOUT is raised (aslam_large_status returns ASLAM_ERR_TIMEOUT).
+// SOLVE_NT threads per CTA (4 warps, at most 168 registers each: one warp per SM sub-partition), so that a CTA of this
+// kernel is co-resident with a CTA of the persistent streaming update (8 warps x 168 registers, 180 KB of shared memory)
+// on every SM: in the overlapped mode the solve kernel of step k+1 runs under the update of step k, and the update of
+// step k+1 -- which may already hold every SM -- spins until this kernel has finished.
+constexpr int SOLVE_NT = 128;
 template <int QT, int MODE>
-__global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp,
-                                                         const double* __restrict__ P, const double* __restrict__ A,
-                                                         double kq, LargeCtx* __restrict__ ctx, uint32_t q_ub,
-                                                         const double* __restrict__ E, double* __restrict__ hp,
-                                                         double* __restrict__ K, double* __restrict__ X,
-                                                         double* __restrict__ predA, const PeerSet ps,
-                                                         unsigned long long target, unsigned long long* sync,
-                                                         unsigned long long epoch, unsigned long long* trace) {
+__global__ void __launch_bounds__(SOLVE_NT, 3) large_solve_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp,
+                                                                 const double* __restrict__ P, const double* __restrict__ A,
+                                                                 double kq, LargeCtx* __restrict__ ctx, uint32_t q_ub,
+                                                                 const double* __restrict__ E, double* __restrict__ hp,
+                                                                 double* __restrict__ K, double* __restrict__ X,
+                                                                 double* __restrict__ predA, const PeerSet ps,
+                                                                 unsigned long long target, unsigned long long* sync,
+                                                                 unsigned long long epoch, unsigned long long* trace,
+                                                                 const PrevUpd pu) {
+    constexpr int NT = SOLVE_NT;
     // let the streaming update become resident and prefetch its first P tiles while this kernel works
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     static_assert(QT <= 32 && QT + 1 <= 32, "one lane per row");
@@ -1450,6 +1570,7 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
     __shared__ int s_hk[QT][5], s_hnnz[QT], s_rows[QT], s_piv[QT], s_perm[QT];
     __shared__ double s_y[QT], s_rdiag[QT], s_invd[QT];
     __shared__ int s_abort, s_chol_ok;
+    __shared__ double s_hpp[QT][QT];  // rows rows[k] of the previous step's H_o P (overlapped mode)
     const int tid = threadIdx.x;
     if (tid == 0) {
         s_abort = 0;
@@ -1457,20 +1578,31 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
         if (!spin_until(sync + SYNC_FRONT, epoch)) atomicOr(&ctx->status, (uint32_t)ASLAM_ST_STEP_TIMEOUT);
         trace_min(trace, epoch, 2);
     }
-    for (int idx = tid; idx < QT * QT; idx += 256) Sinv[idx] = 0.0;  // padding must not contribute
+    for (int idx = tid; idx < QT * QT; idx += NT) Sinv[idx] = 0.0;  // padding must not contribute
     __syncthreads();
     const int q = ctx->q;
     const double a00 = A[0], a10 = A[1];
     if (tid < QT) {
-        const bool in = tid < q;
-        s_rows[tid] = in ? ctx->rows[tid] : 0;
-        s_hnnz[tid] = in ? ctx->hnnz[tid] : 0;
-        s_y[tid] = in ? ctx->y[tid] : 0.0;
-        s_rdiag[tid] = in ? ctx->rdiag[tid] : 1.0;
+        // (loaded unconditionally and masked afterwards: the loads do not wait for q -- every dependent round trip
+        // to memory costs several microseconds under a streaming update that keeps the memory system saturated)
+        const int r_ = ctx->rows[tid], nz_ = ctx->hnnz[tid];
+        const double y_ = ctx->y[tid], rd_ = ctx->rdiag[tid];
+        double hv_[5];
+        int hk_[5];
 #pragma unroll
         for (int e = 0; e < 5; ++e) {
-            s_hval[tid][e] = in ? ctx->hval[tid][e] : 0.0;
-            s_hk[tid][e] = in ? ctx->hk[tid][e] : 0;
+            hv_[e] = ctx->hval[tid][e];
+            hk_[e] = ctx->hk[tid][e];
+        }
+        const bool in = tid < q;
+        s_rows[tid] = in ? r_ : 0;
+        s_hnnz[tid] = in ? nz_ : 0;
+        s_y[tid] = in ? y_ : 0.0;
+        s_rdiag[tid] = in ? rd_ : 1.0;
+#pragma unroll
+        for (int e = 0; e < 5; ++e) {
+            s_hval[tid][e] = in ? hv_[e] : 0.0;
+            s_hk[tid][e] = in ? hk_[e] : 0;
         }
     }
     if (blockIdx.x == 0 && tid == 0) {  // the streaming update applies the predict with these two entries of A
@@ -1478,7 +1610,7 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
         predA[1] = a10;
     }
     __syncthreads();
-    const uint32_t t = blockIdx.x * 256 + tid;
+    const uint32_t t = blockIdx.x * NT + tid;
     const bool valid = t < n;
     const uint32_t tc = valid ? t : n - 1;
     const bool mine = valid && t >= rb && t < re;
@@ -1487,11 +1619,74 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
     // differ by the rounding-level asymmetry of P only (1.7e-16 between the covariance forms) and it
     // replaces 19 strided row reads of a column-major matrix per step (155 k scattered sectors, 20 us behind the
     // streaming kernel's prefetch) by 19 contiguous column reads.
+    auto at_prev = [&](uint32_t i, uint32_t j) { return pv_entry<QT>(P, ldp, rb, n, i, j, pu); };
     double pht[QT];
-    {
-        double colv[QT];
-        gather_cols<QT>(P, ldp, rb, tc, mine, q, s_rows, a00, a10, kq, colv);
+    double colv[QT];
+    // Rows 0 and 1 of the matrix are the only ones whose predicted entries need more than the stored entry of their own
+    // row (pred_entry): one thread per (row, k) computes them side by side -- 2 q entries in one memory round trip
+    // instead of the two threads t = 0, 1 walking their q entries one after the other (10 us alone, 50 us under the
+    // streaming update: it was the longest chain of the kernel).
+    __shared__ double s_c01[2][QT];
+    if constexpr (MODE != SOLVE_EXCH) {
+        if (blockIdx.x == 0 && rb == 0 && tid < 2 * QT) {
+            const int tt = tid / QT, k = tid % QT;
+            s_c01[tt][k] = k < q ? pred_entry_acc(at_prev, (uint32_t)tt, (uint32_t)s_rows[k], a00, a10, kq) : 0.0;
+        }
+    }
+    if constexpr (MODE != SOLVE_EXCH) {
+        // Overlapped mode: every load this thread needs goes out FIRST (the previous gain of row t, the stored row t at
+        // the q columns), then the CTA stages the q rows of the previous H_o P -- one memory round trip, under a
+        // streaming update that keeps the memory system saturated, instead of three.
+        const bool vfast = pu.K != nullptr && mine && tc >= 2;
+        double nk[QT], e[QT];
+        double pa00 = 1.0, pa10 = 0.0;
+        if (vfast) {
+            pa00 = pu.predA[0];
+            pa10 = pu.predA[1];
+#pragma unroll
+            for (int m = 0; m < QT; ++m) nk[m] = pu.K[(size_t)m * n + tc];
+            e[0] = P[tc - rb];
+            e[1] = P[ldp + (tc - rb)];
+            e[2] = P[2 * ldp + (tc - rb)];
+#pragma unroll
+            for (int k = 3; k < QT; ++k) e[k] = k < q ? P[(size_t)s_rows[k] * ldp + (tc - rb)] : 0.0;
+        }
+        if (pu.K) {
+            for (int idx = tid; idx < QT * QT; idx += NT) {
+                const int k1 = idx / QT, m = idx % QT;
+                s_hpp[k1][m] = k1 < q ? pu.hp[(size_t)s_rows[k1] * QT + m] : 0.0;
+            }
+        }
+        __syncthreads();  // s_hpp and s_c01 are complete
+        if (vfast) {
+            // what the update in flight writes for these entries: its predict, then its rank-Q update (k ascending)
+            const double p0 = e[0];
+            e[0] = p0 * pa00;
+            e[1] = p0 * pa10 + e[1];
+            if (tc == 2) e[2] = e[2] + pu.kq;
+#pragma unroll
+            for (int k = 0; k < QT; ++k) {
+                double v = e[k];
+#pragma unroll
+                for (int m = 0; m < QT; ++m) v = fma(-nk[m], s_hpp[k][m], v);
+                e[k] = v;
+            }
+            // ... and this step's predict on top (gather_cols)
+            colv[0] = 0 < q ? e[0] * a00 : 0.0;
+            colv[1] = 1 < q ? e[0] * a10 + e[1] : 0.0;
+            colv[2] = 2 < q ? (tc == 2 ? e[2] + kq : e[2]) : 0.0;
+#pragma unroll
+            for (int k = 3; k < QT; ++k) colv[k] = k < q ? e[k] : 0.0;
+        } else if (mine && tc < 2) {
+#pragma unroll
+            for (int k = 0; k < QT; ++k) colv[k] = s_c01[tc][k];
+        } else {
+            gather_cols_v<QT>(P, ldp, rb, n, tc, mine, q, s_rows, a00, a10, kq, pu, s_hpp, colv);
+        }
         pht_from_cols<QT>(colv, s_hval, pht);
+    } else {
+#pragma unroll
+        for (int k = 0; k < QT; ++k) pht[k] = colv[k] = 0.0;
     }
     trace_mark(trace, epoch, 8);  // own columns gathered
     if constexpr (MODE == SOLVE_PEER) {
@@ -1506,15 +1701,19 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
                 for (int k = 0; k < QT; ++k)
                     if (k < q) Ep[(size_t)k * n] = pht[k];
             }
-        }
-        if (blockIdx.x == 0) {  // the rows of the q x q block this shard owns
-            for (int idx = tid; idx < QT * QT; idx += 256) {
-                const int k1 = idx / QT, k2 = idx % QT;
-                const uint32_t r1 = (uint32_t)s_rows[k1];
-                if (k1 < q && k2 < q && r1 >= rb && r1 < re) {
-                    const double v = pred_entry(P, ldp, rb, r1, (uint32_t)s_rows[k2], a00, a10, kq);
+            // the rows of the q x q block this shard owns: row k1 is what the thread of state row rows[k1] has just
+            // gathered -- colv[k2] = predicted P(rows[k1], rows[k2]), the same entry by the same expressions as pred_entry()
+            int k1 = -1;
+#pragma unroll
+            for (int k = 0; k < QT; ++k)
+                if (k < q && (uint32_t)s_rows[k] == t) k1 = k;
+            if (k1 >= 0) {
 #pragma unroll 1
-                    for (int p = 0; p < ps.world; ++p) ps.E[p][exch_psub_offset(q_ub, n) + idx] = v;
+                for (int p = 0; p < ps.world; ++p) {
+                    double* Eb = ps.E[p] + exch_psub_offset(q_ub, n) + k1 * QT;
+#pragma unroll
+                    for (int k2 = 0; k2 < QT; ++k2)
+                        if (k2 < q) Eb[k2] = colv[k2];
                 }
             }
         }
@@ -1554,12 +1753,12 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
                 pht[k] = (k < q && !abort_step) ? ld_exch<true>(E + (size_t)k * n + tc) : 0.0;
         }
     }
-    for (int idx = tid; idx < QT * QT; idx += 256) {
+    for (int idx = tid; idx < QT * QT; idx += NT) {
         const int k1 = idx / QT, k2 = idx % QT;
         double v = 0.0;
         if (k1 < q && k2 < q && !abort_step) {
             if constexpr (MODE == SOLVE_DIRECT)
-                v = pred_entry(P, ldp, rb, (uint32_t)s_rows[k1], (uint32_t)s_rows[k2], a00, a10, kq);
+                v = pred_entry_acc(at_prev, (uint32_t)s_rows[k1], (uint32_t)s_rows[k2], a00, a10, kq);
             else
                 v = ld_exch<MODE == SOLVE_PEER>(E + exch_psub_offset(q_ub, n) + idx);
         }
@@ -1568,14 +1767,14 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
     __syncthreads();
     trace_mark(trace, epoch, 9);  // exchange waited for, q x q block in shared memory
     // S = H_s Psub H_s' + R (H_s: the q x q sparse form of H_o), zero-padded to QT x QT with the identity on the padding
-    for (int idx = tid; idx < QT * QT; idx += 256) {
+    for (int idx = tid; idx < QT * QT; idx += NT) {
         const int a = idx / QT, jx = idx % QT;
         double hpaj = 0.0;
         for (int f = 0; f < s_hnnz[a]; ++f) hpaj += s_hval[a][f] * S[s_hk[a][f] * LD + jx];
         T[a * LD + jx] = hpaj;
     }
     __syncthreads();
-    for (int idx = tid; idx < QT * QT; idx += 256) {
+    for (int idx = tid; idx < QT * QT; idx += NT) {
         const int a = idx / QT, b = idx % QT;
         double sum = 0.0;
         for (int e = 0; e < s_hnnz[b]; ++e) sum += T[a * LD + s_hk[b][e]] * s_hval[b][e];
@@ -1605,20 +1804,27 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
         double* colb = T;                 // [2][QT]   l_ik of the column in flight
         double* xrb = T + 2 * QT;         // [2][QT]   scaled pivot row of X (zero beyond the pivot)
         double* dgb = T + 4 * QT;         // [2][QT]   diagonal of the trailing matrix
-        int ei = 0, ej = 0;
-        {   // e -> (i, j), e = i (i + 1) / 2 + j
-            int e = tid;
-            ei = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-            while ((ei + 1) * (ei + 2) / 2 <= e) ++ei;
-            while (ei * (ei + 1) / 2 > e) --ei;
-            ej = e - ei * (ei + 1) / 2;
+        constexpr int NE = QT * (QT + 1) / 2, EPT = (NE + NT - 1) / NT;  // entries of the triangle per thread
+        int ei[EPT], ej[EPT];
+        bool own[EPT];
+        double sv[EPT], xv[EPT];
+#pragma unroll
+        for (int u = 0; u < EPT; ++u) {   // e -> (i, j), e = i (i + 1) / 2 + j
+            const int e = tid + u * NT;
+            int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+            while ((i + 1) * (i + 2) / 2 <= e) ++i;
+            while (i * (i + 1) / 2 > e) --i;
+            ei[u] = i;
+            ej[u] = e - i * (i + 1) / 2;
+            own[u] = e < NE && i < q;     // (j <= i < q)
+            sv[u] = own[u] ? S[ei[u] * LD + ej[u]] : 0.0;
+            xv[u] = (own[u] && ei[u] == ej[u]) ? 1.0 : 0.0;
         }
-        const bool own = ei < q;          // (j <= i < q)
-        double sv = own ? S[ei * LD + ej] : 0.0;
-        double xv = (own && ei == ej) ? 1.0 : 0.0;
-        for (int idx = tid; idx < 6 * QT; idx += 256) T[idx] = 0.0;
+        for (int idx = tid; idx < 6 * QT; idx += NT) T[idx] = 0.0;
         __syncthreads();
-        if (own && ei == ej) dgb[ei] = sv;
+#pragma unroll
+        for (int u = 0; u < EPT; ++u)
+            if (own[u] && ei[u] == ej[u]) dgb[ei[u]] = sv[u];
         __syncthreads();
         double akk = dgb[0];
         bool ok = true;
@@ -1630,22 +1836,28 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
                 break;
             }
             const double inv = rsqrt(akk);
-            if (own && ej == k) {  // column k of L
-                sv = ei == k ? akk * inv : sv * inv;
-                colb[b * QT + ei] = sv;
-            }
-            if (own && ei == k) {  // pivot row of X
-                xv *= inv;
-                xrb[b * QT + ej] = xv;
+#pragma unroll
+            for (int u = 0; u < EPT; ++u) {
+                if (own[u] && ej[u] == k) {  // column k of L
+                    sv[u] = ei[u] == k ? akk * inv : sv[u] * inv;
+                    colb[b * QT + ei[u]] = sv[u];
+                }
+                if (own[u] && ei[u] == k) {  // pivot row of X
+                    xv[u] *= inv;
+                    xrb[b * QT + ej[u]] = xv[u];
+                }
             }
             __syncthreads();
-            if (own && ei > k) {
-                const double ci = colb[b * QT + ei];
-                if (ej > k) {
-                    sv = fma(-ci, colb[b * QT + ej], sv);
-                    if (ei == ej) dgb[(b ^ 1) * QT + ei] = sv;
+#pragma unroll
+            for (int u = 0; u < EPT; ++u) {
+                if (own[u] && ei[u] > k) {
+                    const double ci = colb[b * QT + ei[u]];
+                    if (ej[u] > k) {
+                        sv[u] = fma(-ci, colb[b * QT + ej[u]], sv[u]);
+                        if (ei[u] == ej[u]) dgb[(b ^ 1) * QT + ei[u]] = sv[u];
+                    }
+                    xv[u] = fma(-ci, xrb[b * QT + ej[u]], xv[u]);
                 }
-                xv = fma(-ci, xrb[b * QT + ej], xv);
             }
             if (k + 1 < q) {  // next pivot: the fma its owner has just done, redone here from the published operands
                 const double c1 = colb[b * QT + k + 1];
@@ -1653,7 +1865,9 @@ __global__ void __launch_bounds__(256) large_solve_kernel(uint32_t n, uint32_t r
             }
         }
         if (tid == 0) s_chol_ok = ok ? 1 : 0;
-        if (ok && own) Sinv[ei * QT + ej] = xv;  // W = L^-1 (zero above the diagonal)
+#pragma unroll
+        for (int u = 0; u < EPT; ++u)
+            if (ok && own[u]) Sinv[ei[u] * QT + ej[u]] = xv[u];  // W = L^-1 (zero above the diagonal)
         trace_mark(trace, epoch, 13);
         if (!ok) {
             __syncthreads();
@@ -1825,7 +2039,8 @@ aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, dou
         ASLAM_CUDA(cudaGetLastError());
         return ASLAM_OK;
     }
-    // round-1 chain for q > 20: stream-ordered behind the front through an event
+    // round-1 chain for q > 20: stream-ordered behind the front through an event, in place on h->P
+    h->pending = false;
     ASLAM_CUDA(cudaEventRecord(h->ev_front, h->side));
     ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_front, 0));
     large_predict_kernel<<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A, kq);
@@ -1868,25 +2083,76 @@ static dim3 update_grid(const aslam_large* h, uint32_t nrows, uint32_t rows_per_
 }
 
 static aslam_status large_ekf_phase2_fast(aslam_large* h) {
-    const uint32_t n = h->n, nb = (n + 255) / 256, q_ub = h->q_host;
+    const uint32_t n = h->n, nb = (n + SOLVE_NT - 1) / SOLVE_NT, q_ub = h->q_host;
     const uint32_t nrows = h->row_end - h->row_begin;
     const double kq = (double)h->cfg.ekf_kq;
     const unsigned long long epoch = h->step_epoch;
+    // ---- Overlapped mode (one GPU per shard, DIRECT and PEER): the solve kernel goes to `solve_stream` and reads the
+    // buffer the update IN FLIGHT is reading (P_alt = P_{k-1}) plus that update's K, H_o P and A -- it computes the
+    // entries of P_k it needs itself (PrevUpd) -- so it runs UNDER the update of the previous step; this step's update
+    // then reads h->P (= P_k, complete by stream order) and writes P_{k+1} into P_alt, and the two pointers swap. The
+    // step costs max(update, front + solve) instead of their sum. Not with the NCCL form (the caller's all-reduce sits
+    // between the two halves on `stream`) and not with a peer shard on this same GPU (its update could take every SM
+    // while this shard's solve kernel still waits for it): those run in place on one stream, as before.
+    bool overlap = !h->no_overlap && h->step_mode != LARGE_STEP_EXCH &&
+                   !(h->step_mode == LARGE_STEP_PEER && h->peer_same_device);
+    if (overlap && !h->P_alt) {
+        if (cudaMalloc((void**)&h->P_alt, (size_t)n * h->ldp * sizeof(double)) != cudaSuccess) {
+            cudaGetLastError();
+            h->P_alt = nullptr;
+            overlap = false;  // no room for the second buffer: in place
+        } else {
+            // (the padding rows beyond nrows are carried along by the bulk copies: defined values, once)
+            ASLAM_CUDA(cudaMemsetAsync(h->P_alt, 0, (size_t)n * h->ldp * sizeof(double), h->stream));
+        }
+    }
+    const int kb = h->kbuf ^ 1;  // the halves of K / hp / predA this step writes (the other ones may still be in use)
+    double* Kc = h->K + (size_t)kb * 20 * n;
+    double* hpc = h->hp + (size_t)kb * 20 * n;
+    double* predAc = h->predA + 2 * kb;
+    PrevUpd pu{};
+    const double* Pread = h->P;
+    cudaStream_t ss = h->stream;
+    if (overlap) {
+        ss = h->solve_stream;
+        if (h->pending) {  // update(k-1) may still be running: wait for everything BEFORE it, read its input
+            ASLAM_CUDA(cudaStreamWaitEvent(ss, h->ev_before_upd, 0));
+            pu.K = h->K + (size_t)h->kbuf * 20 * n;
+            pu.hp = h->hp + (size_t)h->kbuf * 20 * n;
+            pu.predA = h->predA + 2 * h->kbuf;
+            pu.kq = kq;
+            Pread = h->P_alt;
+        } else {
+            ASLAM_CUDA(cudaEventRecord(h->ev_now, h->stream));
+            ASLAM_CUDA(cudaStreamWaitEvent(ss, h->ev_now, 0));
+        }
+    } else {
+        h->pending = false;  // everything on `stream`, in order: h->P is final when the kernels below run
+    }
     if (h->step_mode == LARGE_STEP_PEER) {
         const PeerSet ps = peer_set(h, h->peer_epoch);
         const unsigned long long target = (unsigned long long)h->peer_epoch * nb;  // nb solve CTAs per rank and step
-        large_solve_kernel<20, SOLVE_PEER><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A, kq,
-                                                                      h->ctx, q_ub, ps.E[h->peer_rank], h->hp, h->K, h->X,
-                                                                      h->predA, ps, target, h->sync, epoch, h->trace);
+        large_solve_kernel<20, SOLVE_PEER><<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A, kq,
+                                                                    h->ctx, q_ub, ps.E[h->peer_rank], hpc, Kc, h->X,
+                                                                    predAc, ps, target, h->sync, epoch, h->trace, pu);
     } else if (h->step_mode == LARGE_STEP_EXCH) {
-        large_solve_kernel<20, SOLVE_EXCH><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A, kq,
-                                                                      h->ctx, q_ub, h->exch, h->hp, h->K, h->X, h->predA,
-                                                                      PeerSet{}, 0ull, h->sync, epoch, h->trace);
+        large_solve_kernel<20, SOLVE_EXCH><<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A, kq,
+                                                                    h->ctx, q_ub, h->exch, hpc, Kc, h->X, predAc,
+                                                                    PeerSet{}, 0ull, h->sync, epoch, h->trace, pu);
     } else {
-        large_solve_kernel<20, SOLVE_DIRECT><<<nb, 256, 0, h->stream>>>(n, h->row_begin, h->row_end, h->ldp, h->P, h->A,
-                                                                        kq, h->ctx, q_ub, nullptr, h->hp, h->K, h->X,
-                                                                        h->predA, PeerSet{}, 0ull, h->sync, epoch,
-                                                                        h->trace);
+        large_solve_kernel<20, SOLVE_DIRECT><<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A,
+                                                                      kq, h->ctx, q_ub, nullptr, hpc, Kc, h->X, predAc,
+                                                                      PeerSet{}, 0ull, h->sync, epoch, h->trace, pu);
+    }
+    ASLAM_CUDA(cudaGetLastError());
+    const double* Pin = h->P;
+    double* Pout = overlap ? h->P_alt : h->P;
+    if (overlap) {
+        if (h->timed) {  // timing pass: the update's events must not include its wait for the solve kernel
+            ASLAM_CUDA(cudaEventRecord(h->ev_solve, ss));
+            ASLAM_CUDA(cudaStreamWaitEvent(h->stream, h->ev_solve, 0));
+        }
+        ASLAM_CUDA(cudaEventRecord(h->ev_before_upd, h->stream));
     }
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
 #ifndef ASLAM_STREAM_NST
@@ -1922,14 +2188,22 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
     // Early launch needs the two launches to be adjacent in the stream (no timing event between them). With a peer
     // shard on the same GPU the 148 early-resident update CTAs would leave no SM with registers for that peer's solve
     // kernel, which this handle's solve kernel is waiting for: plain stream order there.
-    const bool early = h->pdl && !h->timed && !(h->step_mode == LARGE_STEP_PEER && h->peer_same_device);
+    // (only when both kernels are on one stream; overlapped, the update simply follows the previous update)
+    const bool early = !overlap && h->pdl && !h->timed && !(h->step_mode == LARGE_STEP_PEER && h->peer_same_device);
     lc.numAttrs = early ? 1 : 0;
-    ASLAM_CUDA(cudaLaunchKernelEx(&lc, large_update_stream_kernel<CW, 2, 20, CS, NST>, pl, h->ldp, h->P, (const double*)h->K,
-                                  (const double*)h->hp, (const double*)h->predA, kq,
+    ASLAM_CUDA(cudaLaunchKernelEx(&lc, large_update_stream_kernel<CW, 2, 20, CS, NST>, pl, h->ldp, Pin, Pout,
+                                  (const double*)Kc, (const double*)hpc, (const double*)predAc, kq,
                                   (const unsigned long long*)h->sync, epoch, h->trace));
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev1, h->stream));
     ASLAM_CUDA(cudaGetLastError());
     h->launches += 2;
+    h->kbuf = kb;
+    if (overlap) {
+        double* t = h->P;
+        h->P = h->P_alt;
+        h->P_alt = t;
+        h->pending = true;
+    }
     return ASLAM_OK;
 }
 

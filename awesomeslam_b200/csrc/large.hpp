@@ -46,9 +46,19 @@ struct aslam_large {
     uint32_t row_begin = 0, row_end = 0;
     size_t ldp = 0;                  // leading dimension of the local column-major P (rows, padded to 16)
     double* P = nullptr;             // [n][ldp]: column j at P + j*ldp holds rows row_begin..row_end-1
+    // EKF, overlapped steps (ekf_large.cu: large_ekf_phase2_fast): the streaming update writes OUT of place, P <-> P_alt
+    // swap every step, and the solve kernel of the next step runs on `solve_stream` under the update in flight.
+    // h->P is always the buffer that holds the latest state once everything enqueued on `stream` has completed.
+    double* P_alt = nullptr;         // second covariance buffer (allocated on the first overlapped step)
+    cudaStream_t solve_stream = nullptr;
+    cudaEvent_t ev_before_upd = nullptr;  // recorded on `stream` just before the last update: everything older is done
+    cudaEvent_t ev_now = nullptr, ev_solve = nullptr;
+    bool pending = false;            // an out-of-place update is in flight: P_alt + K/hp/predA[kbuf] describe h->P
+    int kbuf = 0;                    // which half of K / hp / predA the last solve kernel wrote
+    bool no_overlap = false;         // ASLAM_LARGE_NO_OVERLAP: keep solve and update on one stream, in place
     double* X = nullptr;             // [n]
     double* A = nullptr;             // [2]: A(0,0), A(1,0) (ekf.cpp:210-211)
-    double* predA = nullptr;         // [2]: the A entries of the step in flight, for the predict fused into the update
+    double* predA = nullptr;         // [2][2]: the A entries of the last two steps, for the predict fused into the update
     aslam::LargeCtx* ctx = nullptr;
     float* d_obs = nullptr;          // [2][ASLAM_MAX_OBS] range, bearing (UKF; the EKF front takes them as arguments)
     float obs_host[2 * ASLAM_MAX_OBS] = {};   // EKF: the observations of the message in flight
