@@ -272,8 +272,17 @@ aslam_status aslam_large_step_phase2(aslam_large* h, int32_t* assoc_out) {
     return fetch_assoc(h, assoc_out);
 }
 
-static size_t peer_block_bytes(const aslam_large* h) {
+// block = [E parity 0][E parity 1][LARGE_MAX_PEERS arrival counters][UUID of the GPU the block lives on, 16 bytes]
+static size_t peer_uuid_offset(const aslam_large* h) {
     return (size_t)4 * LARGE_QMAX * h->n * sizeof(double) + LARGE_MAX_PEERS * sizeof(unsigned long long);
+}
+static size_t peer_block_bytes(const aslam_large* h) { return peer_uuid_offset(h) + 64; }
+static bool device_uuid(int device, unsigned char (&out)[16]) {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return false;
+    static_assert(sizeof(prop.uuid) == 16, "CUDA device UUIDs are 16 bytes");
+    memcpy(out, &prop.uuid, 16);
+    return true;
 }
 
 aslam_status aslam_large_peer_export(aslam_large* h, void* ipc_handle64, void** block) {
@@ -283,6 +292,14 @@ aslam_status aslam_large_peer_export(aslam_large* h, void* ipc_handle64, void** 
     if (!h->peer_block) {
         ASLAM_CUDA(cudaMalloc((void**)&h->peer_block, peer_block_bytes(h)));
         ASLAM_CUDA(cudaMemset(h->peer_block, 0, peer_block_bytes(h)));
+        // which GPU this block lives on: a peer that maps it (CUDA IPC reports the MAPPING device, not the owner) reads
+        // this to find out whether the two shards share a GPU
+        unsigned char uuid[16];
+        if (!device_uuid(h->device, uuid)) {
+            set_error("peer_export: cudaGetDeviceProperties failed");
+            return ASLAM_ERR_CUDA;
+        }
+        ASLAM_CUDA(cudaMemcpy(h->peer_block + peer_uuid_offset(h), uuid, 16, cudaMemcpyHostToDevice));
         ASLAM_CUDA(cudaDeviceSynchronize());
     }
     if (ipc_handle64) ASLAM_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(ipc_handle64), h->peer_block));
@@ -328,10 +345,14 @@ aslam_status aslam_large_peer_attach(aslam_large* h, uint32_t world, uint32_t ra
         // room while this handle's kernels wait for it, so the streaming update is not made resident early (see
         // large_ekf_phase2_fast).
         if (p != rank) {
-            cudaPointerAttributes pa{};
-            if (cudaPointerGetAttributes(&pa, h->peer_base[p]) == cudaSuccess && pa.device == h->device)
-                h->peer_same_device = true;
-            cudaGetLastError();
+            unsigned char mine[16], theirs[16];
+            if (!device_uuid(h->device, mine) ||
+                !cuda_ok(cudaMemcpy(theirs, h->peer_base[p] + peer_uuid_offset(h), 16, cudaMemcpyDeviceToHost),
+                         "peer_attach: reading the peer block")) {
+                set_error("peer_attach: cannot read the peer's exchange block (exported by this library version?)");
+                return ASLAM_ERR_CUDA;
+            }
+            if (memcmp(mine, theirs, 16) == 0) h->peer_same_device = true;
         }
     }
     h->peer_world = world;

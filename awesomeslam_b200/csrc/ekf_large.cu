@@ -104,41 +104,45 @@ __global__ void __launch_bounds__(FRONT_THREADS) large_front_kernel(FrontArgs a,
         sl[0] = globaltimer();
         sl[2] = ~0ull; sl[3] = 0; sl[4] = ~0ull; sl[5] = 0; sl[6] = ~0ull;
     }
-    if (sync) {  // X of the previous step must be final and its context no longer in use
-        if (threadIdx.x == 0 && !spin_until(sync + SYNC_SOLVE, a.epoch - 1))
-            atomicOr(&ctx->status, (uint32_t)ASLAM_ST_STEP_TIMEOUT);
-        __syncthreads();
-    }
     __shared__ float s_nb[ASLAM_MAX_OBS];
     __shared__ int s_corr[ASLAM_MAX_OBS];
     __shared__ float s_mind[ASLAM_MAX_OBS];
     __shared__ int s_lm[ASLAM_MAX_OBS], s_ob[ASLAM_MAX_OBS];
     __shared__ int s_cnt;
     __shared__ double s_pose[3];
+    __shared__ float2 s_pt[ASLAM_MAX_OBS];
+    __shared__ unsigned long long s_red[ASLAM_MAX_OBS][NW];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t L = (n - 3) / 2;
     const double z0 = a.ox, z1 = a.oy, z2 = (double)a.yaw;
-    // (issued now, used by thread 32 after the association: one memory round trip less on the way)
-    double pa00 = 0.0, pa10 = 0.0, px = 0.0, py = 0.0, pth = 0.0;
-    if (tid == 32) {
-        px = X[0];
-        py = X[1];
-        pth = X[2];
-    } else if (tid == 64) {
-        pa00 = A[0];
-        pa10 = A[1];
-    }
-    // ---- nearest landmark of every observation. Thread o < m projects observation o (structures.h:104-111); then
-    // every thread keeps a few landmarks in registers and scans all observations against them: one pass over X,
-    // one round of warp reductions, one CTA barrier, one final reduction per observation.
-    __shared__ float2 s_pt[ASLAM_MAX_OBS];
-    __shared__ unsigned long long s_red[ASLAM_MAX_OBS][NW];
+    // ---- what depends on the MESSAGE only is done before the wait for the previous step (this kernel is enqueued a
+    // whole step ahead): the observations projected with the odometry pose (structures.h:104-111) and the two entries
+    // of A (ekf.cpp:206-212; they persist when vx or az is zero: the previous front kernel wrote them, stream order).
+    double ja00 = 0.0, ja10 = 0.0;
     if (tid < (int)a.m) {
         const float b = normalize_angle(a.bearing[tid], a.pi);  // ekf.cpp:150
         s_nb[tid] = b;
         s_pt[tid] = to_point(a.range[tid], b, z0, z1, z2);
+    } else if (tid == 64) {
+        ja00 = A[0];
+        ja10 = A[1];
+        motion_jacobian(a.vx, a.az, a.dt, z2, ja00, ja10);
+    }
+    if (sync) {  // X of the previous step must be final and its context no longer in use
+        if (threadIdx.x == 0 && !spin_until(sync + SYNC_SOLVE, a.epoch - 1))
+            atomicOr(&ctx->status, (uint32_t)ASLAM_ST_STEP_TIMEOUT);
     }
     __syncthreads();
+    // (issued now, used by thread 32 after the association: one memory round trip less on the way)
+    double px = 0.0, py = 0.0, pth = 0.0;
+    if (tid == 32) {
+        px = X[0];
+        py = X[1];
+        pth = X[2];
+    }
+    // ---- nearest landmark of every observation: every thread keeps a few landmarks in registers and scans all
+    // observations against them: one pass over X, one round of warp reductions, one CTA barrier, one final reduction
+    // per observation.
     constexpr int LPT = 16;  // landmarks per thread and pass: 4096 landmarks in ONE pass -- every load of X in flight at once, one
                              // round of warp reductions per observation (the kernel is on the critical path of the sharded step)
     if (lane == 0)
@@ -212,11 +216,8 @@ __global__ void __launch_bounds__(FRONT_THREADS) large_front_kernel(FrontArgs a,
         s_cnt = cnt;
         ctx->q = 3 + 2 * cnt;
     } else if (tid == 64) {
-        // ---- A (ekf.cpp:206-212), beside the pose predict of thread 32: two independent chains of two sincos each
-        double a00 = pa00, a10 = pa10;
-        motion_jacobian(a.vx, a.az, a.dt, z2, a00, a10);
-        A[0] = a00;
-        A[1] = a10;
+        A[0] = ja00;  // (the solve kernel of the previous step has read the old values: it is done)
+        A[1] = ja10;
     } else if (tid == 32) {
         // ---- the pose predict (ekf.cpp:295-296)
         double x = px, y = py, th = pth;

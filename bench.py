@@ -391,10 +391,13 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
             torch.cuda.synchronize(dev)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             l0 = f.launch_count
-            KL = max(K, 40)  # steps of 0.1-0.2 ms: enough of them that the fill of the step pipeline does not show
+            KL = max(K, 400)  # steps of 0.05-0.2 ms: enough of them that neither the fill of the step pipeline nor the
+            # skew between the ranks leaving the barrier (~1 ms, inside the slowest rank's window) shows in the figure
             e0.record()
+            th0 = time.perf_counter()
             for _ in range(KL):
                 step()
+            host_ms = (time.perf_counter() - th0) * 1e3 / KL  # host time to ENQUEUE a step (no synchronisation inside)
             e1.record()
             f.sync()
             torch.cuda.synchronize(dev)
@@ -411,14 +414,14 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
             f.set_timing(False)
         if world > 1:
             dist.barrier()
-        return ms, launches, kms
+        return ms, launches, kms, host_ms
 
     exchange, nccl_ms, parity = "none (one GPU)", None, None
     if world == 1:
-        ms, launches, kms = timed(step_single)
+        ms, launches, kms, host_ms = timed(step_single)
     else:
         # comparison point: phase1 -> NCCL all-reduce of the exchange buffer -> phase2
-        nccl_ms, launches, kms = timed(step_nccl)
+        nccl_ms, launches, kms, host_ms = timed(step_nccl)
         ms, exchange = nccl_ms, "NCCL all-reduce of the [2q][n] exchange buffer"
         try:  # the fused exchange: CUDA IPC peer mappings, stores + arrival counters inside the solve kernel
             hd, _ = f.peer_export()
@@ -426,7 +429,22 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
             dist.all_gather_object(handles, hd)
             f.peer_attach(world, rank, ipc_handles=handles)
             dist.barrier()
-            ms, launches, kms = timed(step_fused)
+            ms, launches, kms, host_ms = timed(step_fused)
+            if os.environ.get("ASLAM_LARGE_TRACE"):  # diagnostic: %globaltimer phases of the last steps, to stderr
+                tr = np.zeros((64, 16), np.uint64)
+                A.capi.check(f._lib.aslam_large_trace(f._h, A.capi.ptr(tr)))
+                tr = tr.astype(np.int64)
+                ep = int(np.argmax(tr[:, 2] * (tr[:, 2] < (1 << 62))))
+                rows_ = []
+                for kk in range(ep - 32, ep - 18):  # (the last K steps are the serialised kernel-timing pass)
+                    a_, b_ = tr[kk % 64], tr[(kk + 1) % 64]
+                    rows_.append(dict(solve=(a_[3] - a_[2]) / 1e3, gathered=(a_[8] - a_[2]) / 1e3, psub=(a_[9] - a_[8]) / 1e3,
+                                      upd=(a_[5] - a_[4]) / 1e3, solve_out_to_upd_go=(a_[4] - a_[3]) / 1e3,
+                                      upd_out_to_next_solve_in=(b_[2] - a_[5]) / 1e3, period=(b_[2] - a_[2]) / 1e3))
+                per_ = [int((tr[(kk + 1) % 64][2] - tr[kk % 64][2]) / 1e3) for kk in range(ep - 52, ep)]
+                sys.stderr.write("rank %d periods (us) of the last 52 steps: %s\n" % (rank, per_))
+                sys.stderr.write("rank %d trace: %s\n" % (rank, "  ".join(
+                    "%s %.1f" % (k_, float(np.median([r_[k_] for r_ in rows_]))) for k_ in rows_[0])))
             assert f.status()[0] == 0, "fused exchange timed out"
             exchange = ("fused: peer stores over NVLink + arrival counters inside the solve kernel "
                         "(no collective call, 3 launches per step)")
@@ -453,7 +471,8 @@ def large_leg(args, torch, dist, rank, world, dev, hbm_peak, peak_src):
         "workload": "cfg4: large-map EKF n=8195 (4096 landmarks), q=19 rows of H per step, FP64 P%s"
                     % ("" if world == 1 else ", rows sharded over %d GPUs, one exchange per step" % world),
         "exchange": exchange, "ms_per_step_nccl_exchange": nccl_ms, "parity": parity,
-        "steps_per_s": 1e3 / ms, "ms_per_step": ms, "launches_per_step": launches / K, "steps_timed": max(K, 40),
+        "steps_per_s": 1e3 / ms, "ms_per_step": ms, "launches_per_step": launches / K, "steps_timed": max(K, 400),
+        "host_enqueue_ms_per_step": host_ms,
         "roofline": {"bound": "hbm", "kernel": "large_update_stream_kernel<7,2,20,12,4> (persistent, 1 CTA/SM)", "achieved": achieved,
                      "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                      "traffic": _ncu_traffic() if world == 1 else None,
