@@ -207,7 +207,12 @@ aslam_status aslam_large_get_state(aslam_large* h, double* X, double* P, size_t 
 /* cbSensorLandmark + cbOdom for one message pair. m observations; assoc_out[m] (may be NULL)
  * receives the landmark slot or -1. EKF: row-subset joint update over the pose rows and the
  * rows of the landmarks observed in THIS message; with every
- * landmark observed it equals ekf.cpp:300-310. UKF: the full ukf.cpp:260-392 step. */
+ * landmark observed it equals ekf.cpp:300-310. UKF: the full ukf.cpp:260-392 step.
+ * EKF with at most 8 observed landmarks per message (q <= 20): consecutive steps OVERLAP -- the update streams P out
+ * of place between two covariance buffers (the second one, as large as the first, is allocated on the first such step;
+ * if that fails the steps run in place) and the small kernels of the next step run under it. The calls only enqueue;
+ * everything that reads the state afterwards (get_state, sync, work on aslam_large_stream) is ordered behind the
+ * last update. ASLAM_LARGE_NO_OVERLAP=1 in the environment keeps the steps in place on one stream (same kernels). */
 aslam_status aslam_large_step(aslam_large* h, double x, double y, float yaw, double vx, double az, float dt,
                               const float* range, const float* bearing, uint32_t m, int32_t* assoc_out);
 /* Sharded EKF only (row_end - row_begin < n): the step is split around the one exchange.

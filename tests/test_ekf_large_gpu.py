@@ -239,3 +239,60 @@ def test_large_ekf_fused_step_without_peer_gives_up_cleanly(aslam):
     assert np.array_equal(P[3:, 3:], P0[3:k, 3:])
     for f in (lo, hi):
         f.close()
+
+
+def _with_env(name, value, fn):
+    import os
+    old = os.environ.get(name)
+    os.environ[name] = value
+    try:
+        return fn()
+    finally:
+        if old is None:
+            del os.environ[name]
+        else:
+            os.environ[name] = old
+
+
+@pytest.mark.parametrize("side", [8, 13])
+def test_large_ekf_overlapped_steps_equal_in_place_steps(aslam, orc, side):
+    """The overlapped form of the step (solve kernel of step k+1 under the out-of-place update of step k, computing the
+    entries of P_k it needs from the stored P_{k-1} and the previous K, H_o P, A) against the in-place, one-stream form,
+    on a small map (ASLAM_LARGE_OVERLAP_MIN_BYTES=0 makes the handle overlap whatever its size): X and P BIT-IDENTICAL
+    after every one of 7 consecutive messages (both buffer parities, identity start, a get_state between steps that
+    does not disturb the pipeline), and the final state within 1e-9 of the oracle's row-subset steps."""
+    tx, ty, X0, G, d = aslam.large_map_state(side, seed=6)
+    P0 = aslam.dense_P(G, d)
+    n = X0.size
+    ov = _with_env("ASLAM_LARGE_OVERLAP_MIN_BYTES", "0", lambda: aslam.LargeFilter("ekf", n))
+    ip = _with_env("ASLAM_LARGE_NO_OVERLAP", "1", lambda: aslam.LargeFilter("ekf", n))
+    for f in (ov, ip):
+        f.load_state_colmajor(X0, P0)
+    Xo, Po = X0.copy(), P0.copy()
+    cfg = orc.default_config()
+    a00, a10 = 1.0, 0.0
+    for t, (px, py, pth, v, w) in enumerate(_trajectory(7)):
+        rng, brg, idx = aslam.large_observations(tx, ty, (px, py, pth), m=8, seed=50 + t)
+        a_ov = ov.step(px, py, np.float32(pth), v, w, 1.0, rng, brg)
+        a_ip = ip.step(px, py, np.float32(pth), v, w, 1.0, rng, brg)
+        q, assoc, a00, a10 = orc.ekf_large_step(cfg, Xo, Po, a00, a10, px, py, np.float32(pth), v, w, 1.0, rng, brg)
+        assert np.array_equal(a_ov, a_ip) and np.array_equal(a_ov, assoc)
+        if t in (0, 3, 6):
+            X1, P1 = ov.get_state()
+            X2, P2 = ip.get_state()
+            assert np.array_equal(X1, X2) and np.array_equal(P1, P2), t
+    X1, P1 = ov.get_state()
+    assert ov.status()[0] == 0
+    assert relerr(X1, Xo) <= TOL_F64 and relerr(P1, Po.T) <= TOL_F64
+    # a load_state in the middle of a pipeline: the loaded matrix is final, the next step starts from it
+    ov.load_state_colmajor(X0, P0)
+    ip.load_state_colmajor(X0, P0)
+    rng, brg, idx = aslam.large_observations(tx, ty, (0.0, 0.0, 0.0), m=8, seed=99)
+    for _ in range(2):
+        ov.step(0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
+        ip.step(0.0, 0.0, 0.0, 0.05, 0.1, 1.0, rng, brg, want_assoc=False)
+    X1, P1 = ov.get_state()
+    X2, P2 = ip.get_state()
+    assert np.array_equal(X1, X2) and np.array_equal(P1, P2)
+    ov.close()
+    ip.close()
