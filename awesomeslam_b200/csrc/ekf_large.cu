@@ -1410,133 +1410,9 @@ __device__ __forceinline__ void warp_gauss_jordan(double* bufA, double* bufB, in
     }
 }
 
-// Cholesky factor of the (symmetric positive definite) innovation covariance by ONE warp, in shared memory, with
-// ROLLED loops: S = H_o P H_o' + R with R = 0.2 I, so S >= R > 0 whenever P is positive semi-definite. Lane i owns row i.
-// Right-looking: per column one broadcast load of the pivot, one rsqrt, the column scaled in place, then the
-// trailing rows updated (lane i: S(i, j) -= l_ik l_jk for k < j <= i). About 60 instructions of code: the fully
-// unrolled register version this replaces was 3,500 instructions that each step fetched cold (the kernel runs once per
-// step between two passes of the streaming update, so nothing of it is in the instruction cache): 9 -> 3 us.
-// The reference takes `S.inverse()` (PartialPivLU, ekf.cpp:301); for an SPD S both are backward stable and differ in
-// the last bits only (tests: <= 1e-9, measured ~1e-16). Returns false -- and the caller falls back to the pivoted sweep
-// -- when a pivot is not positive. The factor overwrites the lower triangle of S (row stride ld), invd = 1 / diagonal.
-template <int QT>
-__device__ __forceinline__ bool warp_cholesky(double* S, int ld, int q, int lane, double* invd) {
-    bool ok = true;
-#pragma unroll 1
-    for (int k = 0; k < q; ++k) {
-        const double akk = S[k * ld + k];
-        if (!(akk > 0.0)) ok = false;
-        const double inv = rsqrt(akk);
-        double lik = 0.0;
-        if (lane >= k && lane < q) {
-            lik = lane == k ? akk * inv : S[lane * ld + k] * inv;
-            S[lane * ld + k] = lik;
-        }
-        if (lane == k) invd[k] = inv;
-        __syncwarp();
-        if (lane > k && lane < q) {
-#pragma unroll 4
-            for (int j = k + 1; j <= lane; ++j) S[lane * ld + j] = fma(-lik, S[j * ld + k], S[lane * ld + j]);
-        }
-        __syncwarp();
-    }
-    return ok;
-}
-
-// W = L^-1 (lower triangular) by forward substitution, lane c computing column c in place in W (pitch ldw, zero above
-// the diagonal on entry): W(c, c) = 1 / L(c, c), W(i, c) = -(sum_{c <= j < i} L(i, j) W(j, c)) / L(i, i). Rolled loops
-// (see warp_cholesky); two partial sums halve the dependent chain.
-template <int QT>
-__device__ __forceinline__ void warp_lower_inverse(const double* L, int ld, int q, int lane, const double* invd,
-                                                   double* W, int ldw) {
-    if (lane < q) {
-        W[lane * ldw + lane] = invd[lane];
-#pragma unroll 1
-        for (int i = lane + 1; i < q; ++i) {
-            double acc0 = 0.0, acc1 = 0.0;
-            int j = lane;
-#pragma unroll 2
-            for (; j + 1 < i; j += 2) {
-                acc0 = fma(L[i * ld + j], W[j * ldw + lane], acc0);
-                acc1 = fma(L[i * ld + j + 1], W[(j + 1) * ldw + lane], acc1);
-            }
-            if (j < i) acc0 = fma(L[i * ld + j], W[j * ldw + lane], acc0);
-            W[i * ldw + lane] = -(acc0 + acc1) * invd[i];
-        }
-    }
-}
-
 enum { SOLVE_DIRECT = 0, SOLVE_EXCH = 1, SOLVE_PEER = 2 };
 
-// Everything between the front and the streaming update, one launch, 256 columns t of P per CTA.
-//   DIRECT  one GPU: raw rows and the q x q block of P are read straight from P (no exchange buffer at all)
-//   EXCH    NCCL form, second half: the raw rows come from the summed local exchange buffer E
-//   PEER    fused exchange: every owned raw-row value is stored into the exchange buffer of EVERY rank over NVLink peer
-//           memory, the CTA publishes its stores (system-scope fence) and bumps its rank's arrival counter on every
-//           destination, works on the part that needs no remote data (P H_o' of its own rows), and only then waits
-//           (bounded) for the counters of all sources. On a timeout the step is ABANDONED cleanly: K = 0, X keeps its
-//           predicted value, H_o P = 0 -- the update then applies the predict only -- and ASLAM_ST_PEER_TIMEOUT is
-//           raised (aslam_large_status returns ASLAM_ERR_TIMEOUT).
-// Everything between the front and the streaming update, one launch, 256 columns t of P per CTA.
-//   DIRECT  one GPU: raw rows and the q x q block of P are read straight from P (no exchange buffer at all)
-//   EXCH    NCCL form, second half: the raw rows come from the summed local exchange buffer E
-//   PEER    fused exchange: every owned raw-row value is stored into the exchange buffer of EVERY rank over NVLink peer
-//           memory, the CTA publishes its stores (system-scope fence) and bumps its rank's arrival counter on every
-//           destination, works on the part that needs no remote data (P H_o' of its own rows), and only then waits
-//           (bounded) for the counters of all sources. On a timeout the step is ABANDONED cleanly: K = 0, X keeps its
-//           predicted value, H_o P = 0 -- the update then applies the predict only -- and ASLAM_ST_PEER_TIMEOUT is
-//           raised (aslam_large_status returns ASLAM_ERR_TIMEOUT).
-// Predicted P(rows[k], tc) for the rows this shard owns (raw) and predicted P(t, rows[k]) for its own row t (colv).
-// Columns / rows 0, 1 of the whole grid are the only places where the predict needs more than the stored entry; the
-// two threads with t < 2 take the generic pred_entry(), everybody else the straight loads below.
-template <int QT>
-__device__ __forceinline__ void gather_rows_cols(const double* __restrict__ P, size_t ldp, uint32_t rb, uint32_t re,
-                                                 uint32_t t, bool mine, int q, const int* s_rows, double a00,
-                                                 double a10, double kq, double (&raw)[QT], double (&colv)[QT]) {
-    if (t >= 2) {
-        const double* col = P + (size_t)t * ldp - rb;  // column t, indexed by global row
-        const bool own01 = rb == 0;                    // rows 0, 1, 2 live on the first shard
-        const double p0 = own01 ? col[0] : 0.0;
-        raw[0] = (0 < q && own01) ? a00 * p0 : 0.0;
-        raw[1] = (1 < q && own01) ? a10 * p0 + col[1] : 0.0;
-        raw[2] = (2 < q && own01) ? (t == 2 ? col[2] + kq : col[2]) : 0.0;
-#pragma unroll
-        for (int k = 3; k < QT; ++k) {
-            const uint32_t r = (uint32_t)s_rows[k];
-            raw[k] = (k < q && r >= rb && r < re) ? col[r] : 0.0;
-        }
-        if (mine) {
-            const double c0 = P[t - rb];
-            colv[0] = 0 < q ? c0 * a00 : 0.0;
-            colv[1] = 1 < q ? c0 * a10 + P[ldp + (t - rb)] : 0.0;
-            const double c2 = P[2 * ldp + (t - rb)];
-            colv[2] = 2 < q ? (t == 2 ? c2 + kq : c2) : 0.0;
-#pragma unroll
-            for (int k = 3; k < QT; ++k)
-                colv[k] = k < q ? P[(size_t)s_rows[k] * ldp + (t - rb)] : 0.0;
-        } else {
-#pragma unroll
-            for (int k = 0; k < QT; ++k) colv[k] = 0.0;
-        }
-    } else {
-#pragma unroll 1
-        for (int k = 0; k < QT; ++k) {
-            const uint32_t r = (uint32_t)s_rows[k];
-            const bool in = k < q;
-            // dynamic k only on this cold path: the arrays are written through a switch-free helper below
-            const double rv = (in && r >= rb && r < re) ? pred_entry(P, ldp, rb, r, t, a00, a10, kq) : 0.0;
-            const double cv = (in && mine) ? pred_entry(P, ldp, rb, t, r, a00, a10, kq) : 0.0;
-#pragma unroll
-            for (int kk = 0; kk < QT; ++kk)
-                if (kk == k) {
-                    raw[kk] = rv;
-                    colv[kk] = cv;
-                }
-        }
-    }
-}
-
-// Everything between the front and the streaming update, one launch, 256 columns t of P per CTA.
+// Everything between the front and the streaming update, one launch, SOLVE_NT columns t of P per CTA.
 //   DIRECT  one GPU: raw rows and the q x q block of P are read straight from P (no exchange buffer at all)
 //   EXCH    NCCL form, second half: raw rows and P H_o' come from the summed local exchange buffer E
 //   PEER    fused exchange: every value this rank owns is stored into the exchange buffer of EVERY rank over NVLink peer
@@ -1549,17 +1425,14 @@ __device__ __forceinline__ void gather_rows_cols(const double* __restrict__ P, s
 // on every SM: in the overlapped mode the solve kernel of step k+1 runs under the update of step k, and the update of
 // step k+1 -- which may already hold every SM -- spins until this kernel has finished.
 constexpr int SOLVE_NT = 128;
-template <int QT, int MODE>
-__global__ void __launch_bounds__(SOLVE_NT, 3) large_solve_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp,
-                                                                 const double* __restrict__ P, const double* __restrict__ A,
-                                                                 double kq, LargeCtx* __restrict__ ctx, uint32_t q_ub,
-                                                                 const double* __restrict__ E, double* __restrict__ hp,
-                                                                 double* __restrict__ K, double* __restrict__ X,
-                                                                 double* __restrict__ predA, const PeerSet ps,
-                                                                 unsigned long long target, unsigned long long* sync,
-                                                                 unsigned long long epoch, unsigned long long* trace,
-                                                                 const PrevUpd pu) {
-    constexpr int NT = SOLVE_NT;
+// NT = 256 (one CTA per SM, the faster shape when the kernel has the GPU to itself): the in-place form.
+template <int QT, int MODE, int NT>
+__global__ void __launch_bounds__(NT, NT == SOLVE_NT ? 3 : 1)
+large_solve_kernel(uint32_t n, uint32_t rb, uint32_t re, size_t ldp, const double* __restrict__ P,
+                   const double* __restrict__ A, double kq, LargeCtx* __restrict__ ctx, uint32_t q_ub,
+                   const double* __restrict__ E, double* __restrict__ hp, double* __restrict__ K, double* __restrict__ X,
+                   double* __restrict__ predA, const PeerSet ps, unsigned long long target, unsigned long long* sync,
+                   unsigned long long epoch, unsigned long long* trace, const PrevUpd pu) {
     // let the streaming update become resident and prefetch its first P tiles while this kernel works
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     static_assert(QT <= 32 && QT + 1 <= 32, "one lane per row");
@@ -1724,7 +1597,11 @@ __global__ void __launch_bounds__(SOLVE_NT, 3) large_solve_kernel(uint32_t n, ui
         __syncthreads();
         if (tid == 0) {
             __threadfence_system();
-            for (int p = 0; p < ps.world; ++p) atomicAdd_system(ps.flag[p] + ps.rank, 1ULL);
+            // arrivals are counted in groups of SOLVE_NT columns, so that ranks running different CTA shapes (a shard
+            // above and one below the overlap threshold) agree on the target: epoch x ceil(n / SOLVE_NT)
+            const uint32_t c0 = blockIdx.x * NT;
+            const unsigned long long units = (unsigned long long)((min(n, c0 + (uint32_t)NT) - c0 + SOLVE_NT - 1) / SOLVE_NT);
+            for (int p = 0; p < ps.world; ++p) atomicAdd_system(ps.flag[p] + ps.rank, units);
         }
         if (tid < ps.world) {  // wait for the other ranks' values
             const unsigned long long* flags = ps.flag[ps.rank];
@@ -2010,15 +1887,15 @@ aslam_status large_ekf_phase1(aslam_large* h, double x, double y, float yaw, dou
         if (once_.pending(&dev_)) {
             ASLAM_CUDA(cudaFuncSetAttribute(large_front_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                             (int)cudaSharedmemCarveoutMaxShared));
-            ASLAM_CUDA(cudaFuncSetAttribute(large_solve_kernel<20, SOLVE_DIRECT>,
-                                            cudaFuncAttributePreferredSharedMemoryCarveout,
-                                            (int)cudaSharedmemCarveoutMaxShared));
-            ASLAM_CUDA(cudaFuncSetAttribute(large_solve_kernel<20, SOLVE_EXCH>,
-                                            cudaFuncAttributePreferredSharedMemoryCarveout,
-                                            (int)cudaSharedmemCarveoutMaxShared));
-            ASLAM_CUDA(cudaFuncSetAttribute(large_solve_kernel<20, SOLVE_PEER>,
-                                            cudaFuncAttributePreferredSharedMemoryCarveout,
-                                            (int)cudaSharedmemCarveoutMaxShared));
+            auto carve = [](auto kernel) {
+                return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            (int)cudaSharedmemCarveoutMaxShared);
+            };
+            ASLAM_CUDA(carve(large_solve_kernel<20, SOLVE_DIRECT, SOLVE_NT>));
+            ASLAM_CUDA(carve(large_solve_kernel<20, SOLVE_PEER, SOLVE_NT>));
+            ASLAM_CUDA(carve(large_solve_kernel<20, SOLVE_DIRECT, 256>));
+            ASLAM_CUDA(carve(large_solve_kernel<20, SOLVE_EXCH, 256>));
+            ASLAM_CUDA(carve(large_solve_kernel<20, SOLVE_PEER, 256>));
             once_.mark(dev_);
         }
     }
@@ -2083,6 +1960,31 @@ static dim3 update_grid(const aslam_large* h, uint32_t nrows, uint32_t rows_per_
     return dim3(cx, rblocks);
 }
 
+#ifndef ASLAM_STREAM_NST
+#define ASLAM_STREAM_NST 4
+#endif
+#ifndef ASLAM_STREAM_CS
+#define ASLAM_STREAM_CS 12
+#endif
+// Can a CTA of the solve kernel live on an SM that already holds a CTA of the persistent streaming update? The
+// overlapped mode depends on it (the update of step k+1 may hold every SM while it waits for the solve kernel of step
+// k+1): checked from the compiled kernels' own resource figures, per SM sub-partition for the registers (allocation
+// unit: 256 registers per warp), once per process -- a build whose register counts had grown would otherwise only show
+// as step timeouts.
+template <class KU, class KS>
+static bool solve_fits_beside_update(KU update_kernel, KS solve_kernel, int update_threads, size_t update_dyn_smem) {
+    cudaFuncAttributes fu{}, fs{};
+    if (cudaFuncGetAttributes(&fu, update_kernel) != cudaSuccess || cudaFuncGetAttributes(&fs, solve_kernel) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    auto per_warp = [](int regs) { return (size_t)((regs * 32 + 255) / 256) * 256; };
+    const int wu = (update_threads / 32 + 3) / 4, ws = (SOLVE_NT / 32 + 3) / 4;  // warps per sub-partition
+    const bool regs_ok = wu * per_warp(fu.numRegs) + ws * per_warp(fs.numRegs) <= 16384;
+    const size_t smem = update_dyn_smem + fu.sharedSizeBytes + fs.sharedSizeBytes + 2 * 1024;  // + 1 KB reserved per CTA
+    return regs_ok && smem <= (size_t)228 * 1024 && update_threads + SOLVE_NT <= 2048;
+}
+
 static aslam_status large_ekf_phase2_fast(aslam_large* h) {
     const uint32_t n = h->n, nb = (n + SOLVE_NT - 1) / SOLVE_NT, q_ub = h->q_host;
     const uint32_t nrows = h->row_end - h->row_begin;
@@ -2103,6 +2005,15 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
     bool overlap = !h->no_overlap && h->step_mode != LARGE_STEP_EXCH &&
                    !(h->step_mode == LARGE_STEP_PEER && h->peer_same_device) &&
                    (size_t)nrows * n * sizeof(double) * 2 >= h->overlap_min_bytes;
+    if (overlap) {
+        using GU = StreamGeo<7, 2, 20, ASLAM_STREAM_CS, ASLAM_STREAM_NST>;
+        static const bool fits =
+            solve_fits_beside_update(large_update_stream_kernel<7, 2, 20, ASLAM_STREAM_CS, ASLAM_STREAM_NST>,
+                                     large_solve_kernel<20, SOLVE_PEER, SOLVE_NT>, GU::THREADS, GU::SMEM) &&
+            solve_fits_beside_update(large_update_stream_kernel<7, 2, 20, ASLAM_STREAM_CS, ASLAM_STREAM_NST>,
+                                     large_solve_kernel<20, SOLVE_DIRECT, SOLVE_NT>, GU::THREADS, GU::SMEM);
+        if (!fits) overlap = false;
+    }
     if (overlap && !h->P_alt) {
         if (cudaMalloc((void**)&h->P_alt, (size_t)n * h->ldp * sizeof(double)) != cudaSuccess) {
             cudaGetLastError();
@@ -2136,20 +2047,27 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
     } else {
         h->pending = false;  // everything on `stream`, in order: h->P is final when the kernels below run
     }
+    // CTA shape: SOLVE_NT threads under the update (overlapped), 256 when the kernel has the GPU to itself (in place)
+    auto launch_solve = [&](auto k128, auto k256, const double* E, const PeerSet& ps, unsigned long long target) {
+        if (overlap)
+            k128<<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A, kq, h->ctx, q_ub, E, hpc, Kc, h->X,
+                                          predAc, ps, target, h->sync, epoch, h->trace, pu);
+        else
+            k256<<<(n + 255) / 256, 256, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A, kq, h->ctx, q_ub, E, hpc, Kc,
+                                                  h->X, predAc, ps, target, h->sync, epoch, h->trace, pu);
+    };
     if (h->step_mode == LARGE_STEP_PEER) {
         const PeerSet ps = peer_set(h, h->peer_epoch);
-        const unsigned long long target = (unsigned long long)h->peer_epoch * nb;  // nb solve CTAs per rank and step
-        large_solve_kernel<20, SOLVE_PEER><<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A, kq,
-                                                                    h->ctx, q_ub, ps.E[h->peer_rank], hpc, Kc, h->X,
-                                                                    predAc, ps, target, h->sync, epoch, h->trace, pu);
+        // arrivals are counted in groups of SOLVE_NT columns whatever the CTA shape (see the kernel)
+        const unsigned long long target = (unsigned long long)h->peer_epoch * nb;
+        launch_solve(large_solve_kernel<20, SOLVE_PEER, SOLVE_NT>, large_solve_kernel<20, SOLVE_PEER, 256>,
+                     ps.E[h->peer_rank], ps, target);
     } else if (h->step_mode == LARGE_STEP_EXCH) {
-        large_solve_kernel<20, SOLVE_EXCH><<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A, kq,
-                                                                    h->ctx, q_ub, h->exch, hpc, Kc, h->X, predAc,
-                                                                    PeerSet{}, 0ull, h->sync, epoch, h->trace, pu);
+        launch_solve(large_solve_kernel<20, SOLVE_EXCH, 256>, large_solve_kernel<20, SOLVE_EXCH, 256>, h->exch, PeerSet{},
+                     0ull);  // (never overlapped)
     } else {
-        large_solve_kernel<20, SOLVE_DIRECT><<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A,
-                                                                      kq, h->ctx, q_ub, nullptr, hpc, Kc, h->X, predAc,
-                                                                      PeerSet{}, 0ull, h->sync, epoch, h->trace, pu);
+        launch_solve(large_solve_kernel<20, SOLVE_DIRECT, SOLVE_NT>, large_solve_kernel<20, SOLVE_DIRECT, 256>, nullptr,
+                     PeerSet{}, 0ull);
     }
     ASLAM_CUDA(cudaGetLastError());
     const double* Pin = h->P;
@@ -2162,12 +2080,6 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
         ASLAM_CUDA(cudaEventRecord(h->ev_before_upd, h->stream));
     }
     if (h->timed) ASLAM_CUDA(cudaEventRecord(h->ev0, h->stream));
-#ifndef ASLAM_STREAM_NST
-#define ASLAM_STREAM_NST 4
-#endif
-#ifndef ASLAM_STREAM_CS
-#define ASLAM_STREAM_CS 12
-#endif
     constexpr int NST = ASLAM_STREAM_NST, CW = 7, CS = ASLAM_STREAM_CS;
     using G = StreamGeo<CW, 2, 20, CS, NST>;
     constexpr size_t WS_SMEM = G::SMEM;
