@@ -8,12 +8,20 @@
 // but the last product is O(q n); the last one streams P once: read + write 2*8*n^2 bytes.
 //
 // Kernels of the path cfg4 takes (q <= 20), in launch order
-//   large_front_kernel      1 CTA, side stream, under the previous step's update: association (float math,
-//                           first-minimum ties), pose predict, A, H_o, y
-//   large_solve_kernel      gather of the q rows / columns of P (with the predict P = A P A' + Q applied on the fly),
-//                           exchange over peer memory when sharded, S, S^-1 (one warp, in registers), H_o P, K, X += K y
-//   large_update_ws_kernel  P_local -= K_local (H_o P): the HBM-bound streaming kernel, predict fused into the tiles,
-//                           launched with programmatic stream serialization behind the solve kernel
+//   large_front_kernel          1 CTA, side stream, under the previous step's update: association (float math,
+//                               first-minimum ties), pose predict, A, H_o, y; what depends on the message only
+//                               (observation projection, A) before it waits for the previous step
+//   large_solve_kernel          gather of the q rows / columns of P (with the predict P = A P A' + Q applied on the fly),
+//                               exchange over peer memory when sharded, S, Cholesky + inverse by the whole CTA,
+//                               H_o P, K, X += K y. Two CTA shapes: 128 threads (co-resident with the update), 256
+//   large_update_stream_kernel  P_out = P_in - K_local (H_o P): the HBM-bound kernel, persistent (1 CTA per SM), predict
+//                               fused into the tiles
+// Two forms of the step (large_ekf_phase2_fast):
+//   overlapped  the update writes OUT of place (P <-> P_alt) and the solve kernel of step k+1 runs on its own stream
+//               under the update of step k, computing the entries of P_k it needs from P_{k-1} and the previous K,
+//               H_o P, A (PrevUpd / pv_entry): a step costs max(update, front + solve). Shards that stream >= 192 MB.
+//   in place    solve and update on one stream, the update launched programmatically behind the solve kernel
+//               (NCCL form, small shards, a peer shard on the same GPU, ASLAM_LARGE_NO_OVERLAP)
 // 20 < q <= 131 (more than 8 observed landmarks; no BASELINE config) keeps the round-1 chain
 //   large_predict_kernel -> large_gather[_fast]_kernel -> large_gain[_fast]_kernel -> large_update_{bulk,generic}_kernel
 #include <cuda_runtime.h>
