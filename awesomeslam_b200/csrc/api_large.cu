@@ -89,6 +89,8 @@ aslam_status create_large(int kind, const aslam_config* cfg, uint32_t n, uint32_
             if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(e, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
         h->no_overlap = std::getenv("ASLAM_LARGE_NO_OVERLAP") != nullptr;  // diagnostic switch, same kernels either way
         if (const char* e = std::getenv("ASLAM_LARGE_OVERLAP_MIN_BYTES")) h->overlap_min_bytes = (size_t)std::strtoull(e, nullptr, 10);
+        if (const char* e = std::getenv("ASLAM_LARGE_RESERVE_MIN_BYTES")) h->reserve_min_bytes = (size_t)std::strtoull(e, nullptr, 10);
+        if (const char* e = std::getenv("ASLAM_LARGE_RESERVE_SMS")) h->reserve_sms = std::atoi(e);
     }
     if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(&h->ev_ctx_free, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;
     if (rc == ASLAM_OK && !cuda_ok(cudaEventCreateWithFlags(&h->ev_front, cudaEventDisableTiming), "cudaEventCreate")) rc = ASLAM_ERR_CUDA;

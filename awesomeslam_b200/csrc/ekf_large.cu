@@ -2013,7 +2013,27 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
     bool overlap = !h->no_overlap && h->step_mode != LARGE_STEP_EXCH &&
                    !(h->step_mode == LARGE_STEP_PEER && h->peer_same_device) &&
                    (size_t)nrows * n * sizeof(double) * 2 >= h->overlap_min_bytes;
-    if (overlap) {
+    // Short shards (below the threshold, above 32 MB): still overlapped, but with SMs set aside for the solve kernel
+    // instead of sharing them. Measured on two GPUs with shards of the N = 8 size (131 MB): in place 0.0548 ms, sharing
+    // the SMs 0.0570, 17 / 33 / 48 SMs set aside 0.0492 / 0.0476 / 0.0480; at the N = 4 size (272 MB) 33 SMs aside
+    // equal sharing (0.0772 vs 0.0781), at the N = 2 size they lose (0.1387 vs 0.1117: the update needs the SMs).
+    int sms_ = 148;
+    cudaDeviceGetAttribute(&sms_, cudaDevAttrMultiProcessorCount, h->device);
+    const size_t shard_bytes = (size_t)nrows * n * sizeof(double) * 2;
+    const int reserve_want = (int)((n + 255) / 256) + 2;
+    bool reserve = false;
+    if (!overlap && !h->no_overlap && h->reserve_sms != 0 && h->step_mode != LARGE_STEP_EXCH &&
+        !(h->step_mode == LARGE_STEP_PEER && h->peer_same_device) && shard_bytes >= h->reserve_min_bytes &&
+        reserve_want <= sms_ / 3) {
+        overlap = true;
+        reserve = true;
+    }
+    const int reserve_sms = reserve ? (h->reserve_sms > 0 ? h->reserve_sms : reserve_want) : 0;
+    if (reserve && reserve_sms < reserve_want - 2) {  // (an override too small for one wave of the solve grid)
+        overlap = false;
+        reserve = false;
+    }
+    if (overlap && !reserve) {
         using GU = StreamGeo<7, 2, 20, ASLAM_STREAM_CS, ASLAM_STREAM_NST>;
         static const bool fits =
             solve_fits_beside_update(large_update_stream_kernel<7, 2, 20, ASLAM_STREAM_CS, ASLAM_STREAM_NST>,
@@ -2027,6 +2047,7 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
             cudaGetLastError();
             h->P_alt = nullptr;
             overlap = false;  // no room for the second buffer: in place
+            reserve = false;
         } else {
             // (the padding rows beyond nrows are carried along by the bulk copies: defined values, once)
             ASLAM_CUDA(cudaMemsetAsync(h->P_alt, 0, (size_t)n * h->ldp * sizeof(double), h->stream));
@@ -2056,8 +2077,12 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
         h->pending = false;  // everything on `stream`, in order: h->P is final when the kernels below run
     }
     // CTA shape: SOLVE_NT threads under the update (overlapped), 256 when the kernel has the GPU to itself (in place)
+    // `reserve`: the overlapped form for SHORT shards (decided above): the update grid leaves R SMs free and the solve
+    // kernel runs in its 256-thread shape, which does not fit beside an update CTA -- so it lands on the free SMs and
+    // runs at full speed. R covers the whole solve grid: its CTAs wait for the peers' arrivals, which need ALL of a
+    // rank's CTAs to have run, so a second wave could never start.
     auto launch_solve = [&](auto k128, auto k256, const double* E, const PeerSet& ps, unsigned long long target) {
-        if (overlap)
+        if (overlap && !reserve)
             k128<<<nb, SOLVE_NT, 0, ss>>>(n, h->row_begin, h->row_end, h->ldp, Pread, h->A, kq, h->ctx, q_ub, E, hpc, Kc, h->X,
                                           predAc, ps, target, h->sync, epoch, h->trace, pu);
         else
@@ -2101,10 +2126,9 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
     pl.blk_rows = (((nrows + pl.nblk - 1) / pl.nblk + 15) / 16) * 16;
     while ((pl.nblk - 1) * pl.blk_rows >= (uint32_t)h->ldp) pl.nblk -= 1;  // (padding can make the last block empty)
     pl.last_rows = (uint32_t)h->ldp - (pl.nblk - 1) * pl.blk_rows;           // padded to 16 rows, like ldp
-    int sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    const int sms = sms_;
     cudaLaunchConfig_t lc{};
-    lc.gridDim = dim3((unsigned)sms);  // persistent: one CTA per SM
+    lc.gridDim = dim3((unsigned)(reserve ? sms - reserve_sms : sms));  // persistent: one CTA per SM
     lc.blockDim = dim3(G::THREADS);
     lc.dynamicSmemBytes = WS_SMEM;
     lc.stream = h->stream;

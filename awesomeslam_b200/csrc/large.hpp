@@ -56,7 +56,9 @@ struct aslam_large {
     bool pending = false;            // an out-of-place update is in flight: P_alt + K/hp/predA[kbuf] describe h->P
     int kbuf = 0;                    // which half of K / hp / predA the last solve kernel wrote
     bool no_overlap = false;         // ASLAM_LARGE_NO_OVERLAP: keep solve and update on one stream, in place
-    size_t overlap_min_bytes = (size_t)192 << 20;  // shards whose update streams less than this stay in place
+    size_t overlap_min_bytes = (size_t)192 << 20;  // shards whose update streams less than this do not share SMs ...
+    size_t reserve_min_bytes = (size_t)32 << 20;   // ... but, above this, overlap with SMs set aside for the solve kernel
+    int reserve_sms = -1;            // -1: ceil(n / 256) + 2; 0: never; > 0: that many (ASLAM_LARGE_RESERVE_SMS)
     double* X = nullptr;             // [n]
     double* A = nullptr;             // [2]: A(0,0), A(1,0) (ekf.cpp:210-211)
     double* predA = nullptr;         // [2][2]: the A entries of the last two steps, for the predict fused into the update

@@ -254,8 +254,8 @@ def _with_env(name, value, fn):
             os.environ[name] = old
 
 
-@pytest.mark.parametrize("side", [8, 13])
-def test_large_ekf_overlapped_steps_equal_in_place_steps(aslam, orc, side):
+@pytest.mark.parametrize("side,form", [(8, "share"), (13, "share"), (13, "aside")])
+def test_large_ekf_overlapped_steps_equal_in_place_steps(aslam, orc, side, form):
     """The overlapped form of the step (solve kernel of step k+1 under the out-of-place update of step k, computing the
     entries of P_k it needs from the stored P_{k-1} and the previous K, H_o P, A) against the in-place, one-stream form,
     on a small map (ASLAM_LARGE_OVERLAP_MIN_BYTES=0 makes the handle overlap whatever its size): X and P BIT-IDENTICAL
@@ -264,7 +264,9 @@ def test_large_ekf_overlapped_steps_equal_in_place_steps(aslam, orc, side):
     tx, ty, X0, G, d = aslam.large_map_state(side, seed=6)
     P0 = aslam.dense_P(G, d)
     n = X0.size
-    ov = _with_env("ASLAM_LARGE_OVERLAP_MIN_BYTES", "0", lambda: aslam.LargeFilter("ekf", n))
+    # "share": the solve kernel shares the SMs with the update (large shards); "aside": SMs are set aside for it (short shards)
+    ov = _with_env("ASLAM_LARGE_OVERLAP_MIN_BYTES" if form == "share" else "ASLAM_LARGE_RESERVE_MIN_BYTES", "0",
+                   lambda: aslam.LargeFilter("ekf", n))
     ip = _with_env("ASLAM_LARGE_NO_OVERLAP", "1", lambda: aslam.LargeFilter("ekf", n))
     for f in (ov, ip):
         f.load_state_colmajor(X0, P0)

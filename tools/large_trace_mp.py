@@ -19,7 +19,7 @@ if os.environ.get("BACKEND") == "nccl":
 else:
     dist.init_process_group("gloo")
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 40
-tx, ty, X0, G, d = A.large_map_state(64)
+tx, ty, X0, G, d = A.large_map_state(int(os.environ.get('SIDE', '64')))
 P0 = A.dense_P(G, d)
 n = X0.size
 rb = 0 if rank == 0 else max(3, (n * rank) // world)
