@@ -2007,7 +2007,8 @@ static aslam_status large_ekf_phase2_fast(aslam_large* h) {
     // while this shard's solve kernel still waits for it): those run in place on one stream, as before.
     // ... and only where the update is long enough to hide the small kernels, which run 3-4x slower under it: measured
     // on the cfg4 map (n = 8195) split over N GPUs, overlapped vs in place: N = 1 0.200 vs 0.225 ms, N = 2 0.112 vs 0.139,
-    // N = 4 0.077 vs ~0.080, N = 8 (1,024-row shards, update 39 us) 0.0614 vs 0.0575 -- so shards that stream less than 192 MB stay in place.
+    // N = 4 0.077 vs 0.089, N = 8 (1,024-row shards, update 39 us) 0.0614 vs 0.0575 -- so shards that stream less than
+    // 192 MB do not share their SMs with the solve kernel (they set some aside for it, below).
     // (h->overlap_min_bytes: 192 MB, or ASLAM_LARGE_OVERLAP_MIN_BYTES from the environment -- the tests set 0 to run the
     // overlapped form on small maps)
     bool overlap = !h->no_overlap && h->step_mode != LARGE_STEP_EXCH &&
